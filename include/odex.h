@@ -1,0 +1,195 @@
+/* odex.h -- C ABI of libodex.so: the sm_100a kernels behind the ODE-RL latent Neural-ODE rollout.
+ *
+ * The reference (jithendaraa/ODE-RL) has NO FFI / plugin interface on this path: its boundary is four Python
+ * nn.Module classes (modules/DiffEqSolver.py:12-80, modules/ODEConvGRUCell.py:9-78, modules/ConvGRUCell.py:11-86)
+ * whose forward() bodies are chains of ATen library calls.  Each entry point below names the reference call
+ * site(s) (file:line under the reference root) whose ATen op chain it replaces.  The Python package
+ * `ode_rl_b200` mirrors the four classes and binds these symbols with ctypes.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its name ends in _host;
+ *   - activations are fp32 NHWC ("pixel rows"): element (b, y, x, c) of a tensor with row stride ld lives at
+ *     ((b*H + y)*W + x)*ld + c; ld >= channels lets a kernel read/write a channel slice of a wider tensor;
+ *   - times / step sizes / error ratios are fp64 and live in device memory so no entry point needs a host sync;
+ *   - every entry takes the CUDA stream to enqueue on (cudaStream_t passed as void*), is re-entrant, never
+ *     synchronises and never throws: it returns 0 on success, a negative cudaError_t on a CUDA failure and a
+ *     positive ODEX_E_* code on an argument error.  odex_last_error() returns the message of the last failure
+ *     on the calling thread;
+ *   - `skip` (nullable) is a device int: when *skip != 0 at kernel start the whole launch is a no-op.  The
+ *     adaptive solver enqueues attempts speculatively and sets it when the integration is finished.
+ */
+#ifndef ODEX_H
+#define ODEX_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ODEX_VERSION 100
+
+enum {
+    ODEX_E_ARG = 1,         /* bad argument (null pointer, negative size ...) */
+    ODEX_E_SHAPE = 2,       /* shape not supported by the kernels (see each entry) */
+    ODEX_E_ALIGN = 3,       /* pointer / stride not 16-byte aligned */
+    ODEX_E_UNSUPPORTED = 4, /* requested implementation not available for this shape */
+    ODEX_E_DRIVER = 5       /* cuTensorMapEncodeTiled could not be resolved / failed */
+};
+
+enum { ODEX_ACT_NONE = 0, ODEX_ACT_RELU = 1, ODEX_ACT_TANH = 2 };
+enum { ODEX_CONV_AUTO = 0, ODEX_CONV_SIMT = 1, ODEX_CONV_TC = 2 };
+
+typedef void* odex_stream_t; /* cudaStream_t */
+
+int odex_version(void);
+const char* odex_last_error(void);
+/* number of kernels this library has launched in the calling process (bench.py's `gpu_launches`). */
+long long odex_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------------ weights
+ * Repack a torch Conv2d weight (OIHW, [N][C][R][R], fp32) for the kernels.
+ *   dgrad == 0: the forward operator.
+ *   dgrad != 0: the operator of the input gradient (channels swapped, taps flipped), so the data-gradient of a
+ *               convolution is computed by the same forward kernels.
+ * SIMT layout: [tap][c_in][n_out] fp32.
+ * TC layout  : per k-block (64-channel group, tap, 32-channel half): 2*n_out rows of 32 floats =
+ *              [tf32 hi rows ; tf32 lo rows] (3xTF32 split), ready for SWIZZLE_128B TMA boxes.
+ * Sizes are in floats.  Replaces: nothing in the reference (cuDNN/oneDNN do their own packing). */
+size_t odex_packed_weight_floats(int n_out, int c_in, int R, int tc);
+int odex_pack_weights(const float* w_oihw, int N, int C, int R, int dgrad, int tc, float* out, odex_stream_t s);
+
+/* ------------------------------------------------------------------------------------------------ conv
+ * out[p, n] = epi( bias[n] + sum_{r,s,c} X[p + (r,s) - pad, c] * W[n, c, r, s] ),  stride 1, pad (R-1)/2,
+ * where X is the channel concatenation of up to two NHWC sources (torch.cat((x, h), 1) folded in) and
+ *   v = act(acc + bias);  v *= act'(dact) if dact != NULL;  out = res + alpha * v if res != NULL else v,
+ * alpha = alpha_host * (alpha_dev ? (float)*alpha_dev : 1).
+ * Replaces: conv2d (+ReLU) of helpers/utils.py:167-177 via modules/DiffEqSolver.py:77; conv2d of
+ * modules/ConvGRUCell.py:41-43,47-49 with the torch.cat of :72,79; the Euler increment of
+ * modules/ODEConvGRUCell.py:54,57 (res/alpha epilogue); the 1x1 convs of modules/ODEConvGRUCell.py:27-30;
+ * and, with dgrad-packed weights + dact, the autograd conv backward-data of all of those.
+ * Shapes: R in {1,3,5}; W % 16 == 0, H % 8 == 0; c0, c1, N multiples of 4 (SIMT).  TC additionally needs
+ * c0 (== c1 if present) % 64 == 0, N in {64, 128}, W a power of two <= 128 with (128/W) | H. */
+typedef struct odex_conv_desc {
+    const float* x0; int ld0; int c0;
+    const float* x1; int ld1; int c1;       /* x1 == NULL: single source */
+    int B, H, W, R, N;
+    const float* w_simt;                    /* odex_pack_weights(tc=0) or NULL */
+    const float* w_tc;                      /* odex_pack_weights(tc=1) or NULL */
+    const float* bias;                      /* [N] or NULL */
+    int act;                                /* ODEX_ACT_* applied to acc + bias */
+    const float* dact; int ldd; int dact_kind; /* saved activation a: v *= (a > 0) [RELU] / (1 - a*a) [TANH] */
+    const float* res; int ldr;              /* optional residual */
+    float alpha; const double* alpha_dev;
+    float* out; int ldo;
+    const int* skip;
+    int impl;                               /* ODEX_CONV_* */
+} odex_conv_desc;
+int odex_conv2d(const odex_conv_desc* d, odex_stream_t s);
+
+/* Weight / bias gradient of the same convolution: dw[n,c,r,s] += sum_p dy[p,n] * X[p + (r,s) - pad, c]
+ * (OIHW, torch layout, ACCUMULATED into dw) and db[n] += sum_p dy[p,n] (db nullable).
+ * Replaces: autograd conv backward-weight / bias of the call sites listed for odex_conv2d. */
+int odex_conv2d_wgrad(const float* x0, int ld0, int c0, const float* x1, int ld1, int c1, const float* dy, int ldy,
+                      int B, int H, int W, int R, int N, float* dw, float* db, odex_stream_t s);
+
+/* ------------------------------------------------------------------------------------------------ ConvGRU gates
+ * GroupNorm (groups of 32 channels, biased variance, eps, affine) fused with the gate non-linearities.
+ * g: conv_gates output [B,H,W,2C] (bias included).  z = sigmoid(GN(g)[:, :C]); r = sigmoid(GN(g)[:, C:]);
+ * rh = r * h.  stats[b][group][2] = (mean, rstd) is saved for the backward.
+ * Replaces: GroupNorm of modules/ConvGRUCell.py:44 + split/sigmoid/mul of :75-79. */
+int odex_gru_gates_fwd(const float* g, const float* h, int ldh, const float* gamma, const float* beta, float eps,
+                       int B, int HW, int C, float* z, float* rh, float* stats, odex_stream_t s);
+/* c = tanh(GN(cpre)); hnew = (1 - z) * h + z * c.  Replaces modules/ConvGRUCell.py:50,80,82. */
+int odex_gru_out_fwd(const float* cpre, const float* z, const float* h, int ldh, const float* gamma,
+                     const float* beta, float eps, int B, int HW, int C, float* hnew, float* cand, float* stats,
+                     odex_stream_t s);
+/* backward of odex_gru_out_fwd: given dhnew -> dcpre, dz, dh (dh = dhnew * (1 - z), written), dgamma/dbeta +=. */
+int odex_gru_out_bwd(const float* dhnew, const float* cpre, const float* cand, const float* z, const float* h,
+                     int ldh, const float* gamma, const float* stats, int B, int HW, int C, float* dcpre,
+                     float* dz, float* dh, float* dgamma, float* dbeta, odex_stream_t s);
+/* backward of odex_gru_gates_fwd: given dz, drh (row stride lddrh) -> dg [B,H,W,2C];
+ * dh_out[p*lddh + c] = dh_in[p*C + c] + drh * r (dh_out may alias drh); dgamma/dbeta +=. */
+int odex_gru_gates_bwd(const float* dz, const float* drh, int lddrh, const float* dh_in, const float* g,
+                       const float* h, int ldh, const float* gamma, const float* beta, const float* stats,
+                       int B, int HW, int C, float* dg, float* dh_out, int lddh, float* dgamma, float* dbeta,
+                       odex_stream_t s);
+
+/* ------------------------------------------------------------------------------------------------ Runge-Kutta
+ * out = sum_{j<nin} c_j * in_j,  c_j = (float)coef_host[j] * (dtmask>>j & 1 ? (float)*dt_dev : 1).
+ * Operands are summed j ascending in fp32 (torchdiffeq `k[..., :i+1].matmul(beta_i * dt)` order).
+ * The stage planes are separate contiguous buffers (stage-major), never the reference's [...,7] interleave.
+ * Replaces: every stage combination of torchdiffeq 0.2.1 rk_common._runge_kutta_step / fixed_grid
+ * (euler `y + dt*f`, rk4_alt_step_func) called from modules/DiffEqSolver.py:45-46, and their transposes in
+ * the backward.  nin <= 8; n % 4 == 0. */
+int odex_lincomb(float* out, int nin, const float* const* in_host, const double* coef_host, uint32_t dtmask,
+                 const double* dt_dev, long long n, const int* skip, odex_stream_t s);
+
+/* Device-resident controller of the adaptive solver: t, dt and the accept/reject decision never leave the GPU.
+ * Layout is part of the ABI (the host only reads it back, once per forward, or polls a pinned copy).
+ * The buffer the caller allocates must be odex_dopri_state_bytes() long: this header (padded to
+ * ODEX_STATE_HEAD_BYTES) is followed by the reduction scratch of the norm kernels. */
+#define ODEX_STATE_HEAD_BYTES 256
+#define ODEX_RED_BLOCKS 592 /* 4 x 148 SMs */
+typedef struct odex_dopri_state {
+    double t0;          /* start of the last accepted step */
+    double t1;          /* current time (end of the last accepted step) */
+    double dt;          /* size of the next attempt */
+    double dt_try;      /* size of the attempt being evaluated */
+    double rtol, atol;
+    double red[4];      /* reduction slots {sum of squares, aux, aux, element count}: per-rank partial sums; a
+                           multi-GPU caller all-reduces (SUM) these 4 doubles between a norm kernel and the
+                           controller kernel so every rank takes the step sequence of the global batch */
+    double ratio;       /* error ratio of the last attempt */
+    double h0, d0, d1, d2; /* initial-step heuristic scratch */
+    int accept;         /* last attempt accepted */
+    int done;           /* every output time has been produced -- this is what `skip` points at */
+    int done_next;      /* latched into done after the dense-output kernel of the final step */
+    int jnext;          /* next output index to produce */
+    int jlo, jhi;       /* outputs [jlo, jhi) lie inside the step accepted by the last attempt */
+    int n_out;          /* number of output times */
+    int n_accept, n_reject, n_feval, n_attempt;
+    int status;         /* bit0: underflow in dt, bit1: non-finite state, bit2: max attempts exceeded */
+    int max_attempts;
+    int pad_;
+} odex_dopri_state;
+size_t odex_dopri_state_bytes(void);
+
+/* state <- zeros, t0 = t1 = t[0], tolerances, n_out; done if n_out <= 1.  (torchdiffeq solvers.py setup) */
+int odex_dopri_init(odex_dopri_state* st, const double* t_dev, int n_out, double rtol, double atol,
+                    int max_attempts, odex_stream_t s);
+/* phase 0: red <- {sum (y0/scale)^2, sum (f0/scale)^2, 0, n}; scale = atol + rtol*|y0|.
+ * phase 1: red <- {sum ((f1 - f0)/scale)^2, 0, 0, n}.
+ * Replaces torchdiffeq misc._select_initial_step's three RMS norms. */
+int odex_dopri_initnorm(odex_dopri_state* st, int phase, const float* y0, const float* f0, const float* f1,
+                        long long n, odex_stream_t s);
+/* phase 0: h0 from d0, d1 (st->h0; the host then forms y0 + h0*f0 with odex_lincomb(dt_dev = &st->h0)).
+ * phase 1: dt from d1, d2, h0.  fp32 arithmetic like the reference. */
+int odex_dopri_initctrl(odex_dopri_state* st, int phase, odex_stream_t s);
+/* latch dt_try = dt for the attempt and check `t + dt > t` / max attempts (rk_common._adaptive_step asserts). */
+int odex_dopri_begin(odex_dopri_state* st, odex_stream_t s);
+/* red <- {sum_i (err_i / (atol + rtol*max(|y0_i|,|y1_i|)))^2, #non-finite y0 vectors, 0, n},
+ * err = dt_try * sum_j c_error[j] k_j.  k[1] is never read (c_error[1] == 0).
+ * Replaces rk_common._runge_kutta_step's error estimate + misc._compute_error_ratio (8 launches + a D2H sync). */
+int odex_dopri_errnorm(odex_dopri_state* st, const float* y0, const float* y1, const float* const* k7_host,
+                       long long n, odex_stream_t s);
+/* accept = ratio <= 1 with ratio = sqrt(red[0]/red[3]); t/dt update (misc._optimal_step_size), counters, the
+ * range [jlo, jhi) of output times inside the accepted step, done_next, attempt log (4 doubles per attempt:
+ * t0, dt, ratio, accept) into log_dev when non-NULL. */
+int odex_dopri_ctrl(odex_dopri_state* st, const double* t_dev, double* log_dev, int log_cap, odex_stream_t s);
+/* On accept: quartic dense output (interp._interp_fit/_interp_evaluate) for every output j in [jlo, jhi)
+ * into sol + j*n, then advance the state y0 <- y1, k[0] <- k[6] (FSAL) and latch `done`.  On reject: no-op.
+ * ysave/fsave (nullable, together): [save_cap][n] checkpoints of (y, f) at the start of every accepted step
+ * (for the backward replay). */
+int odex_dopri_advance(odex_dopri_state* st, const double* t_dev, float* y0, const float* y1,
+                       float* const* k7_host, float* sol, long long n, float* ysave, float* fsave, int save_cap,
+                       odex_stream_t s);
+
+/* fp32 NCHW <-> NHWC repack of [B, C, HW] planes (tiled transpose). */
+int odex_nchw_to_nhwc(const float* in, float* out, int B, int C, int HW, odex_stream_t s);
+int odex_nhwc_to_nchw(const float* in, float* out, int B, int C, int HW, odex_stream_t s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ODEX_H */
