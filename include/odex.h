@@ -125,6 +125,10 @@ int odex_gru_gates_bwd(const float* dz, const float* drh, int lddrh, const float
 int odex_lincomb(float* out, int nin, const float* const* in_host, const double* coef_host, uint32_t dtmask,
                  const double* dt_dev, long long n, const int* skip, odex_stream_t s);
 
+/* out = dy * act'(a) with a the saved OUTPUT of the activation (ODEX_ACT_*): gradient through a trailing Tanh of
+ * helpers/utils.py:179-181 (create_convnet final_act).  n % 4 == 0. */
+int odex_act_bwd(float* out, const float* dy, const float* a, int kind, long long n, odex_stream_t s);
+
 /* Device-resident controller of the adaptive solver: t, dt and the accept/reject decision never leave the GPU.
  * Layout is part of the ABI (the host only reads it back, once per forward, or polls a pinned copy).
  * The buffer the caller allocates must be odex_dopri_state_bytes() long: this header (padded to

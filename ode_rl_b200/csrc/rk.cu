@@ -49,6 +49,25 @@ __global__ void __launch_bounds__(256) lincomb_kernel(float* __restrict__ out, c
     }
 }
 
+
+// out = dy * act'(a): gradient through a trailing activation of a conv stack (a = saved activation output)
+__global__ void __launch_bounds__(256) act_bwd_kernel(float* __restrict__ out, const float* __restrict__ dy,
+                                                      const float* __restrict__ a, int kind, long n4) {
+    for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n4;
+         i += static_cast<long>(gridDim.x) * blockDim.x) {
+        const float4 d = ld4(dy + 4 * i), v = ld4(a + 4 * i);
+        float4 o;
+        if (kind == ODEX_ACT_RELU) {
+            o = make_float4(v.x > 0.f ? d.x : 0.f, v.y > 0.f ? d.y : 0.f, v.z > 0.f ? d.z : 0.f, v.w > 0.f ? d.w : 0.f);
+        } else if (kind == ODEX_ACT_TANH) {
+            o = make_float4(d.x * (1.f - v.x * v.x), d.y * (1.f - v.y * v.y), d.z * (1.f - v.z * v.z), d.w * (1.f - v.w * v.w));
+        } else {
+            o = d;
+        }
+        st4(out + 4 * i, o);
+    }
+}
+
 // ------------------------------------------------------------------------------------------------- reductions
 // Each block writes up to 3 double partials; the last block to finish sums them in block order (deterministic)
 // into st->red[0..2] and resets the ticket.
@@ -333,6 +352,14 @@ extern "C" int odex_lincomb(float* out, int nin, const float* const* in, const d
         default: lincomb_kernel<8><<<blocks, 256, 0, s>>>(out, a, dt_dev, n4, skip); break;
     }
     return launched("lincomb_kernel");
+}
+
+
+extern "C" int odex_act_bwd(float* out, const float* dy, const float* a, int kind, long long n, odex_stream_t s) {
+    if (!out || !dy || !a || n <= 0 || n % 4) return fail(ODEX_E_ARG, "act_bwd: bad argument");
+    if (!aligned16(out) || !aligned16(dy) || !aligned16(a)) return fail(ODEX_E_ALIGN, "act_bwd: pointers must be 16-byte aligned");
+    act_bwd_kernel<<<ew_blocks(n / 4), 256, 0, static_cast<cudaStream_t>(s)>>>(out, dy, a, kind, n / 4);
+    return launched("act_bwd_kernel");
 }
 
 extern "C" size_t odex_dopri_state_bytes(void) {

@@ -1,0 +1,275 @@
+"""Tensor-level wrappers over the C-ABI of libodex.so -- the ONLY module that touches ctypes pointers.
+
+Everything above this file (ops.py, solver.py, modules.py) talks to a ``Backend`` object in terms of torch
+tensors that merely own device memory; every method below enqueues hand-written sm_100a kernels on the
+current CUDA stream and returns immediately (no host sync).  There is no CPU implementation here: calling
+any method with the library missing or with non-CUDA tensors raises.
+
+Layout conventions (include/odex.h):
+  * activations are fp32 NHWC tensors ``[B, H, W, C']`` whose last dim is dense; a channel slice of a wider
+    buffer is passed as a view (its pixel-row stride becomes the kernel's ``ld``);
+  * RK planes are dense fp32 tensors of any shape, addressed flat;
+  * device scalars (dt, alpha, skip flag) are 1-element views into the solver's state buffer.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import _lib
+from ._lib import ACT_NONE, ACT_RELU, ACT_TANH, CONV_AUTO, CONV_SIMT, CONV_TC  # noqa: F401 (re-export)
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _rows(t: torch.Tensor):
+    """(pointer, pixel-row stride) of an NHWC view [B,H,W,C'] that a kernel can address as p*ld + c."""
+    assert t.dim() == 4 and t.dtype == torch.float32, "expected an fp32 NHWC tensor [B,H,W,C]"
+    B, H, W, Cc = t.shape
+    ld = t.stride(2)
+    assert t.stride(3) == 1 and (W == 1 or True), "channel dim must be dense"
+    assert (H == 1 or t.stride(1) == W * ld) and (B == 1 or t.stride(0) == H * W * ld), \
+        "NHWC view must have uniform pixel stride (got strides %s for shape %s)" % (t.stride(), tuple(t.shape))
+    return t.data_ptr(), ld
+
+
+def _flat(t: torch.Tensor) -> int:
+    assert t.dtype == torch.float32 and t.is_contiguous(), "RK planes must be dense fp32"
+    return t.data_ptr()
+
+
+class PackedConv:
+    """Kernel-ready copies of one Conv2d weight: forward and data-gradient operators."""
+
+    __slots__ = ("N", "C", "R", "fwd_simt", "fwd_tc", "dgrad_simt", "dgrad_tc")
+
+    def __init__(self, N, Cin, R):
+        self.N, self.C, self.R = N, Cin, R
+        self.fwd_simt = self.fwd_tc = self.dgrad_simt = self.dgrad_tc = None
+
+
+def tc_shape_ok(N: int, c0: int, c1: int, H: int, W: int, R: int) -> bool:
+    """Mirror of conv_tc_supported() in csrc/conv_tc.cu."""
+    if N not in (64, 128) or R not in (1, 3, 5):
+        return False
+    if c0 % 64 != 0 or (c1 and c1 != c0):
+        return False
+    if W < 8 or W > 128 or (W & (W - 1)) != 0:
+        return False
+    return H % (128 // W) == 0
+
+
+class Backend:
+    """The CUDA backend (libodex.so).  tests/ substitutes a torch-CPU emulation of the same methods to check
+    the host-side solver / backward logic without a GPU; the product never does."""
+
+    name = "libodex"
+
+    def __init__(self):
+        self.lib = _lib.lib()
+
+    # ------------------------------------------------------------------ memory helpers
+    @staticmethod
+    def require(t: torch.Tensor):
+        if not t.is_cuda:
+            raise _lib.OdexError("ode_rl_b200 runs on CUDA tensors only (got %s); there is no CPU fallback" % t.device)
+
+    # ------------------------------------------------------------------ weights
+    def pack_weights(self, w: torch.Tensor, dgrad: bool, tc: bool) -> torch.Tensor:
+        """odex_pack_weights: OIHW fp32 -> SIMT [tap][c][n] or TC (3xTF32 hi/lo k-blocks) layout."""
+        self.require(w)
+        w = w.detach()
+        assert w.dtype == torch.float32 and w.is_contiguous() and w.dim() == 4 and w.shape[2] == w.shape[3]
+        N, Cc, R, _ = w.shape
+        n_out, c_in = (Cc, N) if dgrad else (N, Cc)
+        nfl = self.lib.odex_packed_weight_floats(n_out, c_in, R, 1 if tc else 0)
+        out = torch.empty(nfl, dtype=torch.float32, device=w.device)
+        _lib.check(self.lib.odex_pack_weights(w.data_ptr(), N, Cc, R, 1 if dgrad else 0, 1 if tc else 0,
+                                              out.data_ptr(), _stream()), "odex_pack_weights")
+        return out
+
+    # ------------------------------------------------------------------ convolution
+    def conv2d(self, x0: torch.Tensor, x1: Optional[torch.Tensor], w_simt: Optional[torch.Tensor],
+               w_tc: Optional[torch.Tensor], N: int, R: int, bias: Optional[torch.Tensor], act: int,
+               out: torch.Tensor, dact: Optional[torch.Tensor] = None, dact_kind: int = 0,
+               res: Optional[torch.Tensor] = None, alpha: float = 1.0, alpha_dev: Optional[torch.Tensor] = None,
+               skip: Optional[torch.Tensor] = None, impl: int = CONV_AUTO) -> torch.Tensor:
+        """odex_conv2d: out = res + alpha * (act(conv(cat(x0,x1)) + bias) * act'(dact))."""
+        self.require(x0)
+        d = _lib.ConvDesc()
+        B, H, W, c0 = x0.shape
+        d.x0, d.ld0 = _rows(x0)
+        d.c0 = c0
+        if x1 is not None:
+            assert x1.shape[:3] == x0.shape[:3]
+            d.x1, d.ld1 = _rows(x1)
+            d.c1 = x1.shape[3]
+        d.B, d.H, d.W, d.R, d.N = B, H, W, R, N
+        d.w_simt, d.w_tc = _ptr(w_simt), _ptr(w_tc)
+        d.bias = _ptr(bias.detach()) if bias is not None else None
+        d.act = act
+        if dact is not None:
+            d.dact, d.ldd = _rows(dact)
+            d.dact_kind = dact_kind
+        if res is not None:
+            d.res, d.ldr = _rows(res)
+        d.alpha = float(alpha)
+        d.alpha_dev = _ptr(alpha_dev)
+        assert tuple(out.shape) == (B, H, W, N), "conv2d: out shape %s != %s" % (tuple(out.shape), (B, H, W, N))
+        d.out, d.ldo = _rows(out)
+        d.skip = _ptr(skip)
+        d.impl = impl
+        _lib.check(self.lib.odex_conv2d(C.byref(d), _stream()), "odex_conv2d")
+        return out
+
+    def conv2d_wgrad(self, x0: torch.Tensor, x1: Optional[torch.Tensor], dy: torch.Tensor, R: int,
+                     dw: torch.Tensor, db: Optional[torch.Tensor]) -> None:
+        """odex_conv2d_wgrad: dw (OIHW) += X^T dy, db += colsum(dy)."""
+        B, H, W, c0 = x0.shape
+        p0, ld0 = _rows(x0)
+        p1, ld1, c1 = None, 0, 0
+        if x1 is not None:
+            p1, ld1 = _rows(x1)
+            c1 = x1.shape[3]
+        pdy, ldy = _rows(dy)
+        N = dy.shape[3]
+        assert dw.is_contiguous() and tuple(dw.shape) == (N, c0 + c1, R, R)
+        _lib.check(self.lib.odex_conv2d_wgrad(p0, ld0, c0, p1, ld1, c1, pdy, ldy, B, H, W, R, N, dw.data_ptr(),
+                                              _ptr(db), _stream()), "odex_conv2d_wgrad")
+
+    # ------------------------------------------------------------------ ConvGRU gates (+GroupNorm)
+    def gru_gates_fwd(self, g, h, gamma, beta, eps, z, rh, stats) -> None:
+        B, H, W, C2 = g.shape
+        Cc = C2 // 2
+        assert g.is_contiguous() and z.is_contiguous() and rh.is_contiguous()
+        ph, ldh = _rows(h)
+        _lib.check(self.lib.odex_gru_gates_fwd(g.data_ptr(), ph, ldh, gamma.detach().data_ptr(), beta.detach().data_ptr(),
+                                               float(eps), B, H * W, Cc, z.data_ptr(), rh.data_ptr(), stats.data_ptr(),
+                                               _stream()), "odex_gru_gates_fwd")
+
+    def gru_out_fwd(self, cpre, z, h, gamma, beta, eps, hnew, cand, stats) -> None:
+        B, H, W, Cc = cpre.shape
+        assert cpre.is_contiguous() and z.is_contiguous() and hnew.is_contiguous()
+        ph, ldh = _rows(h)
+        _lib.check(self.lib.odex_gru_out_fwd(cpre.data_ptr(), z.data_ptr(), ph, ldh, gamma.detach().data_ptr(),
+                                             beta.detach().data_ptr(), float(eps), B, H * W, Cc, hnew.data_ptr(),
+                                             _ptr(cand), stats.data_ptr(), _stream()), "odex_gru_out_fwd")
+
+    def gru_out_bwd(self, dhnew, cpre, cand, z, h, gamma, stats, dcpre, dz, dh, dgamma, dbeta) -> None:
+        B, H, W, Cc = cpre.shape
+        assert dhnew.is_contiguous() and dcpre.is_contiguous() and dz.is_contiguous() and dh.is_contiguous()
+        ph, ldh = _rows(h)
+        _lib.check(self.lib.odex_gru_out_bwd(dhnew.data_ptr(), cpre.data_ptr(), cand.data_ptr(), z.data_ptr(), ph, ldh,
+                                             gamma.detach().data_ptr(), stats.data_ptr(), B, H * W, Cc, dcpre.data_ptr(),
+                                             dz.data_ptr(), dh.data_ptr(), dgamma.data_ptr(), dbeta.data_ptr(),
+                                             _stream()), "odex_gru_out_bwd")
+
+    def gru_gates_bwd(self, dz, drh, dh_in, g, h, gamma, beta, stats, dg, dh_out, dgamma, dbeta) -> None:
+        B, H, W, C2 = g.shape
+        Cc = C2 // 2
+        assert dz.is_contiguous() and dh_in.is_contiguous() and dg.is_contiguous()
+        pdrh, lddrh = _rows(drh)
+        ph, ldh = _rows(h)
+        pdo, lddh = _rows(dh_out)
+        _lib.check(self.lib.odex_gru_gates_bwd(dz.data_ptr(), pdrh, lddrh, dh_in.data_ptr(), g.data_ptr(), ph, ldh,
+                                               gamma.detach().data_ptr(), beta.detach().data_ptr(), stats.data_ptr(),
+                                               B, H * W, Cc, dg.data_ptr(), pdo, lddh, dgamma.data_ptr(),
+                                               dbeta.data_ptr(), _stream()), "odex_gru_gates_bwd")
+
+    # ------------------------------------------------------------------ Runge-Kutta planes
+    def lincomb(self, out: torch.Tensor, ins: Sequence[torch.Tensor], coefs: Sequence[float], dtmask: int = 0,
+                dt_dev: Optional[torch.Tensor] = None, skip: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """odex_lincomb: out = sum_j c_j * in_j, c_j = coef_j * (dt if bit j of dtmask else 1), j ascending."""
+        n = out.numel()
+        nin = len(ins)
+        assert 1 <= nin <= 8 and len(coefs) == nin
+        arr = (C.c_void_p * nin)(*[_flat(t) for t in ins])
+        cf = (C.c_double * nin)(*[float(c) for c in coefs])
+        for t in ins:
+            assert t.numel() == n
+        _lib.check(self.lib.odex_lincomb(_flat(out), nin, arr, cf, dtmask, _ptr(dt_dev), n, _ptr(skip), _stream()),
+                   "odex_lincomb")
+        return out
+
+    def act_bwd(self, out: torch.Tensor, dy: torch.Tensor, a: torch.Tensor, kind: int) -> torch.Tensor:
+        """out = dy * act'(a) elementwise (final-activation gradient of a conv stack)."""
+        _lib.check(self.lib.odex_act_bwd(_flat(out), _flat(dy), _flat(a), kind, out.numel(), _stream()), "odex_act_bwd")
+        return out
+
+    # ------------------------------------------------------------------ dopri5 controller (device resident)
+    def dopri_state_bytes(self) -> int:
+        return int(self.lib.odex_dopri_state_bytes())
+
+    def dopri_init(self, st, t_dev, n_out, rtol, atol, max_attempts) -> None:
+        _lib.check(self.lib.odex_dopri_init(st.data_ptr(), t_dev.data_ptr(), n_out, rtol, atol, max_attempts, _stream()),
+                   "odex_dopri_init")
+
+    def dopri_initnorm(self, st, phase, y0, f0, f1) -> None:
+        _lib.check(self.lib.odex_dopri_initnorm(st.data_ptr(), phase, _flat(y0), _flat(f0), _ptr(f1), y0.numel(),
+                                                _stream()), "odex_dopri_initnorm")
+
+    def dopri_initctrl(self, st, phase) -> None:
+        _lib.check(self.lib.odex_dopri_initctrl(st.data_ptr(), phase, _stream()), "odex_dopri_initctrl")
+
+    def dopri_begin(self, st) -> None:
+        _lib.check(self.lib.odex_dopri_begin(st.data_ptr(), _stream()), "odex_dopri_begin")
+
+    def dopri_errnorm(self, st, y0, y1, k7: List[torch.Tensor]) -> None:
+        arr = (C.c_void_p * 7)(*[_flat(t) for t in k7])
+        _lib.check(self.lib.odex_dopri_errnorm(st.data_ptr(), _flat(y0), _flat(y1), arr, y0.numel(), _stream()),
+                   "odex_dopri_errnorm")
+
+    def dopri_ctrl(self, st, t_dev, log, log_cap) -> None:
+        _lib.check(self.lib.odex_dopri_ctrl(st.data_ptr(), t_dev.data_ptr(), _ptr(log), log_cap, _stream()),
+                   "odex_dopri_ctrl")
+
+    def dopri_advance(self, st, t_dev, y0, y1, k7: List[torch.Tensor], sol, ysave, fsave, save_cap) -> None:
+        arr = (C.c_void_p * 7)(*[_flat(t) for t in k7])
+        _lib.check(self.lib.odex_dopri_advance(st.data_ptr(), t_dev.data_ptr(), _flat(y0), _flat(y1), arr, _flat(sol),
+                                               y0.numel(), _ptr(ysave), _ptr(fsave), save_cap, _stream()),
+                   "odex_dopri_advance")
+
+    # ------------------------------------------------------------------ layout
+    def nchw_to_nhwc(self, x: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+        """x: [..., C, H, W] dense -> out: [..., H, W, C] dense."""
+        Cc, H, W = x.shape[-3:]
+        Bn = x.numel() // (Cc * H * W)
+        assert x.is_contiguous() and out.is_contiguous() and x.dtype == torch.float32
+        _lib.check(self.lib.odex_nchw_to_nhwc(x.data_ptr(), out.data_ptr(), Bn, Cc, H * W, _stream()), "odex_nchw_to_nhwc")
+        return out
+
+    def nhwc_to_nchw(self, x: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+        H, W, Cc = x.shape[-3:]
+        Bn = x.numel() // (Cc * H * W)
+        assert x.is_contiguous() and out.is_contiguous() and x.dtype == torch.float32
+        _lib.check(self.lib.odex_nhwc_to_nchw(x.data_ptr(), out.data_ptr(), Bn, Cc, H * W, _stream()), "odex_nhwc_to_nchw")
+        return out
+
+    def launch_count(self) -> int:
+        return _lib.launch_count()
+
+
+_backend: Optional[Backend] = None
+
+
+def backend() -> Backend:
+    """The process-wide backend; created on first use (loads libodex.so, raises if it is missing)."""
+    global _backend
+    if _backend is None:
+        _backend = Backend()
+    return _backend
+
+
+def set_backend(b: Optional[Backend]) -> Optional[Backend]:
+    """Test hook: swap the backend object (tests/fake_backend.py); returns the previous one."""
+    global _backend
+    prev, _backend = _backend, b
+    return prev

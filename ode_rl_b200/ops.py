@@ -1,0 +1,337 @@
+"""Host-side operators of the hot path, each with an explicit forward and a hand-written backward that
+enqueue libodex kernels (through kernels.Backend) on the current stream.  No torch compute ops here:
+torch only owns the device buffers.
+
+  ConvNetOp  -- the ODE function `gradient_net` (helpers/utils.py:158-183 via modules/DiffEqSolver.py:71-80)
+                and `transform_z0` (modules/ODEConvGRUCell.py:27-30): a chain of stride-1 "same" convolutions
+                with ReLU / Tanh in between, optionally fused with `res + alpha * f(x)` (the Euler increment of
+                modules/ODEConvGRUCell.py:54-57).
+  GruOp      -- one ConvGRU update (modules/ConvGRUCell.py:72-82): conv5x5(cat(x,h)) -> GroupNorm -> sigmoid
+                gates -> conv5x5(cat(x, r*h)) -> GroupNorm -> tanh -> blend.
+"""
+from __future__ import annotations
+
+import os
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import torch
+import torch.nn as nn
+
+from . import kernels as K
+from .kernels import ACT_NONE, ACT_RELU, ACT_TANH, CONV_AUTO, CONV_SIMT, CONV_TC, PackedConv
+
+# "auto": tcgen05 implicit GEMM where the shape allows it, exact-fp32 FFMA kernel otherwise;
+# "simt": force the FFMA kernel (cross-check / debugging); "tc": require the tensor-core kernel.
+CONV_IMPL = os.environ.get("ODEX_CONV_IMPL", "auto").lower()
+
+
+def set_conv_impl(name: str) -> str:
+    global CONV_IMPL
+    assert name in ("auto", "simt", "tc")
+    prev, CONV_IMPL = CONV_IMPL, name
+    return prev
+
+
+def _use_tc(N: int, c0: int, c1: int, H: int, W: int, R: int) -> bool:
+    if CONV_IMPL == "simt":
+        return False
+    ok = K.tc_shape_ok(N, c0, c1, H, W, R)
+    if CONV_IMPL == "tc" and not ok:
+        raise ValueError("ODEX_CONV_IMPL=tc but shape N=%d c0=%d c1=%d HxW=%dx%d R=%d is not supported by the "
+                         "tcgen05 kernel" % (N, c0, c1, H, W, R))
+    return ok
+
+
+def to_nhwc(x: torch.Tensor) -> torch.Tensor:
+    """[..., C, H, W] (any strides) -> dense [..., H, W, C]; zero-copy when x already is channels-last."""
+    xp = x.movedim(-3, -1)
+    if xp.is_contiguous():
+        return xp
+    be = K.backend()
+    if not x.is_contiguous():
+        x = x.contiguous()
+    out = torch.empty(xp.shape, dtype=x.dtype, device=x.device)
+    return be.nchw_to_nhwc(x, out)
+
+
+def from_nhwc(x: torch.Tensor, dense_nchw: bool = False) -> torch.Tensor:
+    """dense [..., H, W, C] -> logical [..., C, H, W].  By default a zero-copy channels-last view (what cuDNN
+    prefers for the torch-side ConvDecode); dense_nchw=True materialises NCHW memory with the transpose kernel."""
+    if not dense_nchw:
+        return x.movedim(-1, -3)
+    out = torch.empty(x.movedim(-1, -3).shape, dtype=x.dtype, device=x.device)
+    return K.backend().nhwc_to_nchw(x, out)
+
+
+class GradSink:
+    """fp32 accumulators for parameter gradients, keyed by parameter identity (kernels accumulate with +=)."""
+
+    def __init__(self):
+        self._g: Dict[int, torch.Tensor] = {}
+
+    def get(self, p: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+        if p is None or not p.requires_grad:
+            return None
+        g = self._g.get(id(p))
+        if g is None:
+            g = torch.zeros(p.shape, dtype=torch.float32, device=p.device)
+            self._g[id(p)] = g
+        return g
+
+    def result(self, params: Sequence[torch.Tensor]) -> Tuple[Optional[torch.Tensor], ...]:
+        return tuple(self._g.get(id(p)) if p.requires_grad else None for p in params)
+
+
+class _PackCache:
+    """Kernel-layout copies of a Conv2d weight, refreshed when the parameter changes (optimizer step / load)."""
+
+    def __init__(self, conv: nn.Conv2d):
+        self.conv = conv
+        self.key = None
+        self.pk: Optional[PackedConv] = None
+        self.shape_key = None
+
+    def get(self, H: int, W: int, c0: int, c1: int, need_dgrad: bool) -> PackedConv:
+        w = self.conv.weight
+        key = (w.data_ptr(), w._version, w.device, CONV_IMPL)
+        skey = (H, W, c0, c1)
+        if self.pk is None or key != self.key or skey != self.shape_key:
+            self.pk = PackedConv(w.shape[0], w.shape[1], w.shape[2])
+            self.key, self.shape_key = key, skey
+        pk = self.pk
+        be = K.backend()
+        N, Cin, R = pk.N, pk.C, pk.R
+        if _use_tc(N, c0, c1, H, W, R):
+            if pk.fwd_tc is None:
+                pk.fwd_tc = be.pack_weights(w, dgrad=False, tc=True)
+        elif pk.fwd_simt is None:
+            pk.fwd_simt = be.pack_weights(w, dgrad=False, tc=False)
+        if need_dgrad:
+            # the data-gradient operator maps N channels of dy to Cin channels (one source)
+            if _use_tc(Cin, N, 0, H, W, R):
+                if pk.dgrad_tc is None:
+                    pk.dgrad_tc = be.pack_weights(w, dgrad=True, tc=True)
+            elif pk.dgrad_simt is None:
+                pk.dgrad_simt = be.pack_weights(w, dgrad=True, tc=False)
+        return pk
+
+    def invalidate(self):
+        self.key = None
+        self.pk = None
+
+
+def _check_conv(conv: nn.Conv2d, what: str) -> int:
+    k = conv.kernel_size
+    if not (isinstance(conv, nn.Conv2d) and k[0] == k[1] and k[0] in (1, 3, 5) and conv.stride == (1, 1)
+            and conv.padding == ((k[0] - 1) // 2,) * 2 and conv.dilation == (1, 1) and conv.groups == 1
+            and conv.padding_mode == "zeros"):
+        raise NotImplementedError(
+            "%s: the CUDA path takes stride-1 'same' Conv2d with a square 1/3/5 kernel only (got %r)" % (what, conv))
+    return k[0]
+
+
+def _act_kind(m: nn.Module) -> int:
+    if isinstance(m, nn.ReLU):
+        return ACT_RELU
+    if isinstance(m, nn.Tanh):
+        return ACT_TANH
+    raise NotImplementedError("activation %r is not supported by the CUDA path (ReLU / Tanh only)" % (m,))
+
+
+def parse_sequential(seq: nn.Sequential, what: str) -> List[Tuple[nn.Conv2d, int]]:
+    """[Conv2d, act, Conv2d, act, ..., Conv2d(, act)] -> [(conv, act_after)]."""
+    layers: List[Tuple[nn.Conv2d, int]] = []
+    mods = list(seq)
+    i = 0
+    while i < len(mods):
+        conv = mods[i]
+        if not isinstance(conv, nn.Conv2d):
+            raise NotImplementedError("%s: expected Conv2d at position %d of %r" % (what, i, seq))
+        _check_conv(conv, what)
+        act = ACT_NONE
+        if i + 1 < len(mods) and not isinstance(mods[i + 1], nn.Conv2d):
+            act = _act_kind(mods[i + 1])
+            i += 1
+        layers.append((conv, act))
+        i += 1
+    if not layers:
+        raise NotImplementedError("%s: empty conv stack" % what)
+    return layers
+
+
+class ConvNetOp:
+    """f(x) = conv_{L-1}(act(... act(conv_0(x)))) (+ trailing act), NHWC in / NHWC out."""
+
+    def __init__(self, seq: nn.Sequential, what: str = "gradient_net"):
+        self.layers = parse_sequential(seq, what)
+        self.caches = [_PackCache(c) for c, _ in self.layers]
+        self.c_in = self.layers[0][0].in_channels
+        self.c_out = self.layers[-1][0].out_channels
+
+    def params(self) -> List[torch.Tensor]:
+        ps = []
+        for conv, _ in self.layers:
+            ps.append(conv.weight)
+            if conv.bias is not None:
+                ps.append(conv.bias)
+        return ps
+
+    def flops(self, B: int, H: int, W: int) -> int:
+        return sum(2 * B * H * W * c.out_channels * c.in_channels * c.kernel_size[0] ** 2 for c, _ in self.layers)
+
+    def invalidate(self):
+        for c in self.caches:
+            c.invalidate()
+
+    # out = res + alpha * f(x)   (res None: out = f(x))
+    def fwd(self, x: torch.Tensor, save: bool = False, out: Optional[torch.Tensor] = None,
+            res: Optional[torch.Tensor] = None, alpha: float = 1.0, alpha_dev: Optional[torch.Tensor] = None,
+            skip: Optional[torch.Tensor] = None, need_dgrad: bool = False):
+        be = K.backend()
+        B, H, W, _ = x.shape
+        L = len(self.layers)
+        saved = [x] if save else None
+        a = x
+        for l, (conv, act) in enumerate(self.layers):
+            last = l == L - 1
+            pk = self.caches[l].get(H, W, a.shape[3], 0, need_dgrad or save)
+            fuse = last and (res is not None) and act == ACT_NONE
+            if last and out is not None and (res is None or fuse):
+                o = out
+            else:
+                o = torch.empty((B, H, W, pk.N), dtype=torch.float32, device=x.device)
+            be.conv2d(a, None, pk.fwd_simt, pk.fwd_tc, pk.N, pk.R, conv.bias, act, o,
+                      res=res if fuse else None, alpha=alpha if fuse else 1.0, alpha_dev=alpha_dev if fuse else None,
+                      skip=skip)
+            if save and (not last or act != ACT_NONE):
+                saved.append(o)
+            a = o
+        if res is not None and self.layers[-1][1] != ACT_NONE:
+            # trailing activation: the residual cannot ride in the conv epilogue (the saved activation is needed)
+            o = out if out is not None else torch.empty_like(a)
+            if alpha_dev is not None:
+                be.lincomb(o, [res, a], [1.0, alpha], dtmask=2, dt_dev=alpha_dev, skip=skip)
+            else:
+                be.lincomb(o, [res, a], [1.0, alpha], skip=skip)
+            a = o
+        return (a, saved) if save else a
+
+    # dx = res + J_f(x)^T dy ; parameter gradients accumulated into `sink`
+    def bwd(self, saved: List[torch.Tensor], dy: torch.Tensor, sink: GradSink, out: Optional[torch.Tensor] = None,
+            res: Optional[torch.Tensor] = None, need_dx: bool = True) -> Optional[torch.Tensor]:
+        be = K.backend()
+        x = saved[0]
+        B, H, W, _ = x.shape
+        L = len(self.layers)
+        d = dy
+        last_act = self.layers[-1][1]
+        if last_act != ACT_NONE:
+            assert d.is_contiguous() and saved[L].is_contiguous()
+            d = be.act_bwd(torch.empty_like(saved[L]), d, saved[L], last_act)
+        for l in range(L - 1, -1, -1):
+            conv, _ = self.layers[l]
+            a_l = saved[l]
+            gw, gb = sink.get(conv.weight), sink.get(conv.bias)
+            if gw is not None or gb is not None:
+                if gw is None:   # bias-only gradient: still needs a dw target for the kernel
+                    gw = torch.zeros_like(conv.weight)
+                be.conv2d_wgrad(a_l, None, d, conv.kernel_size[0], gw, gb)
+            if l == 0 and not need_dx:
+                return None
+            pk = self.caches[l].get(H, W, a_l.shape[3], 0, True)
+            if l > 0:
+                nd = torch.empty((B, H, W, pk.C), dtype=torch.float32, device=x.device)
+                be.conv2d(d, None, pk.dgrad_simt, pk.dgrad_tc, pk.C, pk.R, None, ACT_NONE, nd,
+                          dact=a_l, dact_kind=self.layers[l - 1][1])
+                d = nd
+            else:
+                dx = out if out is not None else torch.empty((B, H, W, pk.C), dtype=torch.float32, device=x.device)
+                be.conv2d(d, None, pk.dgrad_simt, pk.dgrad_tc, pk.C, pk.R, None, ACT_NONE, dx, res=res, alpha=1.0)
+                return dx
+        return None
+
+
+class GruOp:
+    """One ConvGRU update with GroupNorm gates (modules/ConvGRUCell.py:72-82; update gate first, reset second)."""
+
+    def __init__(self, conv_gates: nn.Sequential, conv_can: nn.Sequential, hidden_dim: int, input_dim: int):
+        self.cg, self.gn_g = conv_gates[0], conv_gates[1]
+        self.cc, self.gn_c = conv_can[0], conv_can[1]
+        self.C, self.Cx = hidden_dim, input_dim
+        self.R = _check_conv(self.cg, "ConvGRUCell.conv_gates")
+        if _check_conv(self.cc, "ConvGRUCell.conv_can") != self.R:
+            raise NotImplementedError("ConvGRUCell: conv_gates and conv_can must share the kernel size")
+        for gn, ch in ((self.gn_g, 2 * hidden_dim), (self.gn_c, hidden_dim)):
+            if not isinstance(gn, nn.GroupNorm) or gn.num_channels != ch or ch % 32 != 0 or gn.num_groups * 32 != ch \
+                    or not gn.affine:
+                raise NotImplementedError("ConvGRUCell: the CUDA path needs affine GroupNorm with 32-channel groups "
+                                          "(got %r for %d channels)" % (gn, ch))
+        if self.cg.bias is None or self.cc.bias is None:
+            raise NotImplementedError("ConvGRUCell: bias=False is not supported by the CUDA path")
+        self.pc_g, self.pc_c = _PackCache(self.cg), _PackCache(self.cc)
+
+    def params(self) -> List[torch.Tensor]:
+        return [self.cg.weight, self.cg.bias, self.gn_g.weight, self.gn_g.bias,
+                self.cc.weight, self.cc.bias, self.gn_c.weight, self.gn_c.bias]
+
+    def flops(self, B: int, H: int, W: int) -> int:
+        return 2 * B * H * W * (self.Cx + self.C) * self.R * self.R * 3 * self.C
+
+    def fwd(self, x: torch.Tensor, h: torch.Tensor, save: bool = False, out: Optional[torch.Tensor] = None):
+        be = K.backend()
+        B, H, W, Cx = x.shape
+        C, R = self.C, self.R
+        dev = x.device
+        f32 = torch.float32
+        pg = self.pc_g.get(H, W, Cx, C, save)
+        g = torch.empty((B, H, W, 2 * C), dtype=f32, device=dev)
+        be.conv2d(x, h, pg.fwd_simt, pg.fwd_tc, 2 * C, R, self.cg.bias, ACT_NONE, g)
+        z = torch.empty((B, H, W, C), dtype=f32, device=dev)
+        rh = torch.empty((B, H, W, C), dtype=f32, device=dev)
+        st_g = torch.empty((B * (2 * C // 32) * 2,), dtype=f32, device=dev)
+        be.gru_gates_fwd(g, h, self.gn_g.weight, self.gn_g.bias, self.gn_g.eps, z, rh, st_g)
+        pc = self.pc_c.get(H, W, Cx, C, save)
+        cpre = torch.empty((B, H, W, C), dtype=f32, device=dev)
+        be.conv2d(x, rh, pc.fwd_simt, pc.fwd_tc, C, R, self.cc.bias, ACT_NONE, cpre)
+        hnew = out if out is not None else torch.empty((B, H, W, C), dtype=f32, device=dev)
+        cand = torch.empty((B, H, W, C), dtype=f32, device=dev) if save else None
+        st_c = torch.empty((B * (C // 32) * 2,), dtype=f32, device=dev)
+        be.gru_out_fwd(cpre, z, h, self.gn_c.weight, self.gn_c.bias, self.gn_c.eps, hnew, cand, st_c)
+        if save:
+            return hnew, (x, h, g, z, rh, st_g, cpre, cand, st_c)
+        return hnew
+
+    def bwd(self, saved, dhnew: torch.Tensor, sink: GradSink, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Returns D = [dx | dh] as one [B,H,W,Cx+C] buffer (channel slices are the two gradients)."""
+        be = K.backend()
+        x, h, g, z, rh, st_g, cpre, cand, st_c = saved
+        B, H, W, Cx = x.shape
+        C, R = self.C, self.R
+        dev, f32 = x.device, torch.float32
+
+        def grad_or_scratch(p):
+            t = sink.get(p)
+            return t if t is not None else torch.zeros_like(p)
+
+        dcpre = torch.empty((B, H, W, C), dtype=f32, device=dev)
+        dz = torch.empty((B, H, W, C), dtype=f32, device=dev)
+        dh_a = torch.empty((B, H, W, C), dtype=f32, device=dev)
+        be.gru_out_bwd(dhnew, cpre, cand, z, h, self.gn_c.weight, st_c, dcpre, dz, dh_a,
+                       grad_or_scratch(self.gn_c.weight), grad_or_scratch(self.gn_c.bias))
+        gw, gb = sink.get(self.cc.weight), sink.get(self.cc.bias)
+        if gw is not None or gb is not None:
+            be.conv2d_wgrad(x, rh, dcpre, R, gw if gw is not None else torch.zeros_like(self.cc.weight), gb)
+        pc = self.pc_c.get(H, W, Cx, C, True)
+        D1 = torch.empty((B, H, W, Cx + C), dtype=f32, device=dev)            # [dx_can | drh]
+        be.conv2d(dcpre, None, pc.dgrad_simt, pc.dgrad_tc, Cx + C, R, None, ACT_NONE, D1)
+        dg = torch.empty((B, H, W, 2 * C), dtype=f32, device=dev)
+        drh = D1[..., Cx:]
+        be.gru_gates_bwd(dz, drh, dh_a, g, h, self.gn_g.weight, self.gn_g.bias, st_g, dg, drh,
+                         grad_or_scratch(self.gn_g.weight), grad_or_scratch(self.gn_g.bias))   # D1[..., Cx:] <- dh_a + drh*r
+        gw, gb = sink.get(self.cg.weight), sink.get(self.cg.bias)
+        if gw is not None or gb is not None:
+            be.conv2d_wgrad(x, h, dg, R, gw if gw is not None else torch.zeros_like(self.cg.weight), gb)
+        pg = self.pc_g.get(H, W, Cx, C, True)
+        D2 = out if out is not None else torch.empty((B, H, W, Cx + C), dtype=f32, device=dev)
+        be.conv2d(dg, None, pg.dgrad_simt, pg.dgrad_tc, Cx + C, R, None, ACT_NONE, D2, res=D1, alpha=1.0)
+        return D2
