@@ -1,0 +1,354 @@
+"""Drop-in mirrors of the reference's four hot-path modules -- same constructor / forward signatures, attribute
+names and parameter (state_dict) names, so models/ODEConvGRU.py and models/VidODE.py use them unchanged:
+
+  DiffEqSolver    modules/DiffEqSolver.py:12-52
+  ODEFunc         modules/DiffEqSolver.py:57-80   (gradient_net stays a real nn.Sequential of nn.Conv2d)
+  ODEConvGRUCell  modules/ODEConvGRUCell.py:9-78
+  ConvGRUCell     modules/ConvGRUCell.py:11-86
+  create_convnet  helpers/utils.py:158-183
+
+Parameters live in ordinary nn.Conv2d / nn.GroupNorm modules (checkpoints and optimizers see no difference);
+forward() never calls them -- it hands their tensors to the libodex kernels through ops.py / solver.py.
+Tensors cross the boundary in the reference's logical layout ([B,C,H,W], time-first [T,B,C,H,W]); results are
+channels-last in memory (a zero-copy view of the kernels' NHWC buffers).
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import torch
+import torch.nn as nn
+
+from . import kernels as K
+from .ops import ConvNetOp, GradSink, GruOp, from_nhwc, to_nhwc
+from .solver import FIXED, odeint_dopri5, odeint_fixed
+
+
+def create_convnet(n_inputs, n_outputs, n_layers=1, n_units=128, downsize=False, nonlinear='tanh', final_act=True):
+    """helpers/utils.py:158-183: Conv3x3, n_layers x [act, Conv3x3], act, Conv3x3 (, Tanh)."""
+    if nonlinear == 'tanh':
+        act = nn.Tanh
+    elif nonlinear == 'relu':
+        act = nn.ReLU
+    else:
+        raise NotImplementedError('Wrong activation function')
+    layers: List[nn.Module] = [nn.Conv2d(n_inputs, n_units, 3, 1, 1, dilation=1)]
+    for _ in range(n_layers):
+        layers.append(act())
+        if downsize is False:
+            layers.append(nn.Conv2d(n_units, n_units, 3, 1, 1, dilation=1))
+        else:
+            layers.append(nn.Conv2d(n_units, n_units, 4, 2, 1, dilation=1))
+    layers.append(act())
+    layers.append(nn.Conv2d(n_units, n_outputs, 3, 1, 1, dilation=1))
+    if final_act is True:
+        layers.append(nn.Tanh())
+    return nn.Sequential(*layers)
+
+
+class _ConvNetFn(torch.autograd.Function):
+    """y = f(x) for a conv stack, logical NCHW in/out."""
+
+    @staticmethod
+    def forward(ctx, op: ConvNetOp, x: torch.Tensor, *params):
+        K.backend().require(x)
+        xn = to_nhwc(x.detach().float())
+        save = any(ctx.needs_input_grad)
+        if save:
+            y, saved = op.fwd(xn, save=True)
+            ctx.op, ctx.saved, ctx.params = op, saved, params
+        else:
+            y = op.fwd(xn)
+        return from_nhwc(y)
+
+    @staticmethod
+    def backward(ctx, dy):
+        d = to_nhwc(dy.float())
+        if not d.is_contiguous():
+            d = d.contiguous()
+        sink = GradSink()
+        dx = ctx.op.bwd(ctx.saved, d, sink, need_dx=ctx.needs_input_grad[1])
+        return (None, from_nhwc(dx) if dx is not None else None) + sink.result(ctx.params)
+
+
+class ODEFunc(nn.Module):
+    def __init__(self, n_inputs=3, n_outputs=3, n_layers=4, n_units=256, downsize=False, nonlinear='relu',
+                 final_act=True, net=None, device=torch.device("cpu")):
+        super(ODEFunc, self).__init__()
+        self.device = device
+        self.n_outputs = n_outputs
+        if net is None:
+            self.gradient_net = create_convnet(n_inputs, n_outputs, n_layers, n_units, downsize, nonlinear,
+                                               final_act=final_act).to(device)
+        else:
+            self.gradient_net = net
+        self._op: Optional[ConvNetOp] = None
+
+    def op(self) -> ConvNetOp:
+        """Kernel-side view of gradient_net (built lazily; raises NotImplementedError for unsupported stacks)."""
+        if self._op is None or self._op.layers[0][0] is not self.gradient_net[0]:
+            self._op = ConvNetOp(self.gradient_net, "ODEFunc.gradient_net")
+        return self._op
+
+    def forward(self, t_local, y, backwards=False):
+        """dy/dt at y; autonomous: t_local is ignored (modules/DiffEqSolver.py:71-80)."""
+        op = self.op()
+        grad = _ConvNetFn.apply(op, y, *op.params())
+        if backwards:
+            grad = -grad
+        return grad
+
+
+class DiffEqSolver(nn.Module):
+    def __init__(self, ode_func, method, odeint_rtol=1e-4, odeint_atol=1e-5, device=torch.device("cpu"), memory=False):
+        super(DiffEqSolver, self).__init__()
+        self.ode_func = ode_func
+        self.ode_method = method
+        self.device = device
+        self.memory = memory
+        self.odeint_rtol = odeint_rtol
+        self.odeint_atol = odeint_atol
+        # dopri5 plumbing (not part of the reference surface)
+        self.reduce_fn = None            # set by parallel.shard_solver(): all-reduce of the error-norm partial sums
+        self.max_attempts = 4096
+        self.save_budget_bytes = 8 << 30
+        self.last_stats = None
+        self._chunk_hint = 8
+
+    def _odeint(self, y0, t):
+        method = self.ode_method
+        if t.dim() != 1:
+            raise AssertionError("t must be one dimensional")
+        if not isinstance(self.ode_func, ODEFunc):
+            raise NotImplementedError("DiffEqSolver: the CUDA path integrates ode_rl_b200.ODEFunc conv stacks only")
+        op = self.ode_func.op()
+        if method in FIXED:
+            return odeint_fixed(op, y0, t, method)
+        if method == 'dopri5':
+            return odeint_dopri5(op, self, y0, t, self.odeint_rtol, self.odeint_atol)
+        raise ValueError('Invalid method "{}" (euler, rk4 and dopri5 are supported)'.format(method))
+
+    def forward(self, first_point, time_steps_to_predict, backwards=False):
+        """Decode the trajectory through the ODE solver; returns time-first [T,B,C,H,W] (modules/DiffEqSolver.py:24-52)."""
+        if self.memory is True:
+            # modules/DiffEqSolver.py:30-42: odeint over a single time point returns y0, so h_next = 2*h_prev.
+            y_is = [first_point]
+            b, c, h, w = first_point.size()
+            for i in range(len(time_steps_to_predict)):
+                h_prev = y_is[-1]
+                pred_m = self._odeint(h_prev, time_steps_to_predict[i:i + 1]).reshape(b, c, h, w)
+                y_is.append(h_prev + pred_m)
+            return torch.stack(y_is[1:]).permute(1, 0, 2, 3, 4)
+        if first_point.dim() != 4:
+            # the reference returns None for vector states (modules/DiffEqSolver.py:48-51); nothing to integrate here
+            return None
+        return self._odeint(first_point, time_steps_to_predict)
+
+
+class _GruStepFn(torch.autograd.Function):
+    """h' = ConvGRU(x, h), logical NCHW in/out (one step of modules/ConvGRUCell.py:66-84)."""
+
+    @staticmethod
+    def forward(ctx, op: GruOp, x: torch.Tensor, h: torch.Tensor, *params):
+        K.backend().require(x)
+        xn, hn = to_nhwc(x.detach().float()), to_nhwc(h.detach().float())
+        save = any(ctx.needs_input_grad)
+        if save:
+            hnew, saved = op.fwd(xn, hn, save=True)
+            ctx.op, ctx.saved, ctx.params = op, saved, params
+        else:
+            hnew = op.fwd(xn, hn)
+        return from_nhwc(hnew)
+
+    @staticmethod
+    def backward(ctx, dh):
+        d = to_nhwc(dh.float())
+        if not d.is_contiguous():
+            d = d.contiguous()
+        op = ctx.op
+        sink = GradSink()
+        D = op.bwd(ctx.saved, d, sink)
+        dx = from_nhwc(D[..., :op.Cx]) if ctx.needs_input_grad[1] else None
+        dhp = from_nhwc(D[..., op.Cx:]) if ctx.needs_input_grad[2] else None
+        return (None, dx, dhp) + sink.result(ctx.params)
+
+
+class ConvGRUCell(nn.Module):
+    def __init__(self, input_size, input_dim, hidden_dim, kernel_size, bias=True, dtype=None, padding=None):
+        """ConvGRU cell with GroupNorm gates -- modules/ConvGRUCell.py:12-50 (same submodule / parameter names)."""
+        super(ConvGRUCell, self).__init__()
+        self.height, self.width = input_size
+        self.input_channels = input_dim
+        self.hidden_dim = hidden_dim
+        self.device = torch.device("cuda" if torch.cuda.is_available() else "cpu")
+        if padding is None:
+            self.padding = (kernel_size - 1) // 2
+        else:
+            self.padding = padding
+        if dtype is None:
+            dtype = torch.cuda.FloatTensor if self.device == 'cuda' else torch.FloatTensor
+        self.bias = bias
+        self.dtype = dtype
+        self.conv_gates = nn.Sequential(
+            nn.Conv2d(input_dim + hidden_dim, 2 * self.hidden_dim, kernel_size, 1, self.padding),
+            nn.GroupNorm(2 * self.hidden_dim // 32, 2 * self.hidden_dim))
+        self.conv_can = nn.Sequential(
+            nn.Conv2d(input_dim + hidden_dim, self.hidden_dim, kernel_size, 1, self.padding),
+            nn.GroupNorm(self.hidden_dim // 32, self.hidden_dim))
+        self._op: Optional[GruOp] = None
+
+    def op(self) -> GruOp:
+        if self._op is None or self._op.cg is not self.conv_gates[0]:
+            self._op = GruOp(self.conv_gates, self.conv_can, self.hidden_dim, self.input_channels)
+        return self._op
+
+    def init_hidden(self, batch_size):
+        return (torch.zeros(batch_size, self.hidden_dim, self.height, self.width)).type(self.dtype)
+
+    def forward(self, input_tensor=None, h_cur=None, seq_len=10, mask=None, dim=0):
+        """Returns (stack(h_1..h_seq_len, dim), h_seq_len); `mask` is accepted and ignored like the reference."""
+        op = self.op()
+        dev = self.conv_gates[0].weight.device
+        if h_cur is None:
+            h_cur = torch.zeros(input_tensor.size(1), self.hidden_dim, self.height, self.width, device=dev)
+        output_inner = []
+        h_next = h_cur
+        for index in range(seq_len):
+            if input_tensor is None:
+                x = torch.zeros(h_cur.size(0), self.input_channels, self.height, self.width, device=dev)
+            else:
+                x = input_tensor[index, ...]
+            h_next = _GruStepFn.apply(op, x, h_cur, *op.params())
+            output_inner.append(h_next)
+            h_cur = h_next
+        return torch.stack(output_inner, dim=dim), h_next
+
+
+class _EncoderFn(torch.autograd.Function):
+    """The ODE-ConvGRU recurrence of modules/ODEConvGRUCell.py:53-74 as one autograd node: for every observed
+    frame, walked in `order`, h~ = h + f(h)*dt_i (explicit Euler, fused into the last conv's epilogue) and
+    h = ConvGRU(x_i, h~).  Returns all hidden states, iteration-major [T,B,C,H,W]."""
+
+    @staticmethod
+    def forward(ctx, f_op: ConvNetOp, g_op: GruOp, n_f: int, order, inputs: torch.Tensor, deltas: torch.Tensor, *params):
+        be = K.backend()
+        be.require(inputs)
+        x = to_nhwc(inputs.detach().float())                 # [T,B,H,W,C]
+        if not x.is_contiguous():
+            x = x.contiguous()
+        T, B, H, W, Cx = x.shape
+        C = g_op.C
+        save = any(ctx.needs_input_grad)
+        hs = torch.empty((T, B, H, W, C), dtype=torch.float32, device=x.device)
+        h = torch.zeros((B, H, W, C), dtype=torch.float32, device=x.device)
+        saved = []
+        for n, i in enumerate(order):
+            ht = torch.empty_like(h)
+            r = f_op.fwd(h, save=save, out=ht, res=h, alpha=1.0, alpha_dev=deltas[n:n + 1])
+            g = g_op.fwd(x[i], ht, save=save, out=hs[n])
+            if save:
+                saved.append((r[1], g[1]))
+            h = hs[n]
+        if save:
+            ctx.f_op, ctx.g_op, ctx.n_f, ctx.order, ctx.deltas, ctx.saved, ctx.params = f_op, g_op, n_f, order, deltas, saved, params
+            ctx.x_shape = (T, B, H, W, Cx)
+        return from_nhwc(hs)
+
+    @staticmethod
+    def backward(ctx, dhs):
+        be = K.backend()
+        f_op, g_op, order, deltas, saved = ctx.f_op, ctx.g_op, ctx.order, ctx.deltas, ctx.saved
+        d = to_nhwc(dhs.float())
+        if not d.is_contiguous():
+            d = d.contiguous()
+        T, B, H, W, Cx = ctx.x_shape
+        C = g_op.C
+        sink = GradSink()
+        DX = torch.empty((T, B, H, W, Cx + C), dtype=torch.float32, device=d.device)   # [dx_i | dh~] per frame
+        a = None                                              # adjoint of h after iteration n
+        for n in range(T - 1, -1, -1):
+            i = order[n]
+            if a is None:
+                dh = d[n]
+            else:
+                dh = torch.empty_like(a)
+                be.lincomb(dh, [a, d[n]], [1.0, 1.0])
+            sv_f, sv_g = saved[n]
+            D = g_op.bwd(sv_g, dh, sink, out=DX[i])
+            dht = D[..., Cx:]                                 # adjoint of h~ (row stride Cx+C)
+            if n == 0:
+                # h_0 = 0 is a constant: only the parameter gradients of f(0) remain
+                dk = _scaled_copy(be, dht, deltas[n:n + 1])
+                f_op.bwd(sv_f, dk, sink, need_dx=False)
+                a = None
+            else:
+                dk = _scaled_copy(be, dht, deltas[n:n + 1])
+                a = f_op.bwd(sv_f, dk, sink, res=dht)
+            saved[n] = None
+        ctx.saved = None
+        dx = from_nhwc(DX[..., :Cx]) if ctx.needs_input_grad[4] else None
+        return (None, None, None, None, dx, None) + sink.result(ctx.params)
+
+
+def _scaled_copy(be, view: torch.Tensor, dt_dev: torch.Tensor) -> torch.Tensor:
+    """dense copy of an NHWC channel-slice view scaled by *dt_dev: the adjoint of `f(h) * dt` w.r.t. f(h)."""
+    dense = view.contiguous() if not view.is_contiguous() else view
+    out = torch.empty_like(dense)
+    be.lincomb(out, [dense], [1.0], dtmask=1, dt_dev=dt_dev)
+    return out
+
+
+class ODEConvGRUCell(nn.Module):
+    def __init__(self, ode_func, opt, resolution, ch, out_ch=None, device=None, kernel_size=5):
+        super(ODEConvGRUCell, self).__init__()
+        self.ode_func = ode_func
+        self.device = device
+        self.z0_diffeq_solver = None
+        if out_ch is None:
+            out_ch = ch
+        self.cgru_cell = ConvGRUCell(input_size=resolution, input_dim=ch, hidden_dim=ch,
+                                     kernel_size=kernel_size, bias=True).to(device)
+        # last conv layer for generating mu, sigma
+        self.z0_dim = out_ch
+        z = ch
+        self.transform_z0 = nn.Sequential(
+            nn.Conv2d(z, z, 1, 1, 0),
+            nn.ReLU(),
+            nn.Conv2d(z, out_ch * 2, 1, 1, 0)).to(device)
+        self._z0_op: Optional[ConvNetOp] = None
+
+    def _transform_op(self) -> ConvNetOp:
+        if self._z0_op is None or self._z0_op.layers[0][0] is not self.transform_z0[0]:
+            self._z0_op = ConvNetOp(self.transform_z0, "ODEConvGRUCell.transform_z0")
+        return self._z0_op
+
+    def forward(self, inputs, timesteps, mask=None):    # inputs has time dim first
+        last_yi, _ = self.run_ode_conv_gru(inputs, timesteps, mask=mask)
+        op = self._transform_op()
+        trans_last_yi = _ConvNetFn.apply(op, last_yi, *op.params())     # (b, self.z0_dim*2, h, w)
+        mean_z0, std_z0 = torch.split(trans_last_yi, self.z0_dim, dim=1)
+        std_z0 = std_z0.abs()
+        return mean_z0, std_z0
+
+    def run_ode_conv_gru(self, inputs, timesteps, run_backwards=True, mask=None):
+        t, b, c, h, w = inputs.size()
+        assert (t == len(timesteps)), "Sequence length should be same as time_steps"
+        if not isinstance(self.ode_func, ODEFunc):
+            raise NotImplementedError("ODEConvGRUCell: the CUDA path needs an ode_rl_b200.ODEFunc")
+        order = list(range(t))
+        if run_backwards:
+            order = order[::-1]
+        # step sizes exactly as the reference forms them (fp64): prev_t, t_i = t[-1]+0.01, t[-1]; then
+        # prev_t, t_i = t[i], t[i-1] after visiting frame i (modules/ODEConvGRUCell.py:48,73)
+        ts = timesteps.detach().to(device=inputs.device, dtype=torch.float64)
+        deltas = torch.empty(t, dtype=torch.float64, device=inputs.device)
+        deltas[0] = ts[-1] - (ts[-1] + 0.01)
+        if t > 1:
+            idx = torch.tensor(order[:-1], device=inputs.device)
+            deltas[1:] = ts[idx - 1] - ts[idx]
+        f_op, g_op = self.ode_func.op(), self.cgru_cell.op()
+        params = f_op.params() + g_op.params()
+        hs = _EncoderFn.apply(f_op, g_op, len(f_op.params()), order, inputs, deltas, *params)   # [T,B,C,H,W]
+        yi = hs[t - 1]
+        latent_ys = hs.permute(1, 0, 2, 3, 4)   # (b, t, c, h, w)
+        return yi, latent_ys

@@ -1,0 +1,354 @@
+"""TEST INFRASTRUCTURE ONLY -- a torch-CPU emulation of kernels.Backend (the C-ABI semantics of
+include/odex.h), so the HOST-side logic of the product (solver loops, speculative dopri5 chunks, hand-written
+backward replay, layout handling) can be checked against the oracle on a box without a GPU.  It is injected
+with kernels.set_backend() by the `fake_backend` fixture only; the product never imports this file and has no
+CPU path of its own.  What this cannot check -- the CUDA kernels themselves -- is covered by the `-m gpu` tests.
+"""
+from __future__ import annotations
+
+import ctypes
+import math
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+from ode_rl_b200 import _lib
+from ode_rl_b200.kernels import ACT_NONE, ACT_RELU, ACT_TANH
+
+C_ERROR = [35 / 384 - 1951 / 21600, 0.0, 500 / 1113 - 22642 / 50085, 125 / 192 - 451 / 720,
+           -2187 / 6784 - -12231 / 42400, 11 / 84 - 649 / 6300, -1.0 / 60.0]
+C_MID = [6025192743 / 30085553152 / 2, 0.0, 51252292925 / 65400821598 / 2, -2691868925 / 45128329728 / 2,
+         187940372067 / 1594534317056 / 2, -1776094331 / 19743644256 / 2, 11237099 / 235043384 / 2]
+
+f32 = np.float32
+
+
+def _skipped(skip):
+    return skip is not None and int(skip.reshape(-1)[0]) != 0
+
+
+def _act(v, kind):
+    if kind == ACT_RELU:
+        return torch.relu(v)
+    if kind == ACT_TANH:
+        return torch.tanh(v)
+    return v
+
+
+def _dact(a, kind):
+    if kind == ACT_RELU:
+        return (a > 0).to(a.dtype)
+    if kind == ACT_TANH:
+        return 1 - a * a
+    return torch.ones_like(a)
+
+
+class _State:
+    """ctypes view of the odex_dopri_state header living in a CPU uint8 tensor."""
+
+    def __init__(self, st: torch.Tensor):
+        self.arr = st.numpy()
+        self.s = _lib.DopriState.from_buffer(self.arr)
+
+
+class FakeBackend:
+    name = "fake-cpu"
+
+    def __init__(self):
+        self.launches = 0
+
+    @staticmethod
+    def require(t):
+        return None
+
+    # ------------------------------------------------------------------ weights / conv
+    def pack_weights(self, w, dgrad, tc):
+        p = w.detach().clone()
+        p._odex_dgrad = bool(dgrad)
+        return p
+
+    def conv2d(self, x0, x1, w_simt, w_tc, N, R, bias, act, out, dact=None, dact_kind=0, res=None, alpha=1.0,
+               alpha_dev=None, skip=None, impl=0):
+        self.launches += 1
+        if _skipped(skip):
+            return out
+        w = w_tc if w_tc is not None else w_simt
+        assert w is not None, "conv2d: no packed weights"
+        wt = w
+        if w._odex_dgrad:
+            wt = w.transpose(0, 1).flip(2, 3)
+        x = x0 if x1 is None else torch.cat((x0, x1), 3)
+        assert wt.shape[0] == N and wt.shape[1] == x.shape[3], (wt.shape, N, x.shape)
+        v = F.conv2d(x.permute(0, 3, 1, 2), wt, None if bias is None else bias.detach(), padding=(R - 1) // 2)
+        v = _act(v, act).permute(0, 2, 3, 1)
+        if dact is not None:
+            v = v * _dact(dact, dact_kind)
+        if res is not None:
+            a = f32(alpha)
+            if alpha_dev is not None:
+                a = f32(a * f32(float(alpha_dev.reshape(-1)[0])))
+            v = res + float(a) * v
+        out.copy_(v)
+        return out
+
+    def conv2d_wgrad(self, x0, x1, dy, R, dw, db):
+        self.launches += 1
+        x = x0 if x1 is None else torch.cat((x0, x1), 3)
+        g = torch.nn.grad.conv2d_weight(x.permute(0, 3, 1, 2).contiguous(), dw.shape, dy.permute(0, 3, 1, 2).contiguous(),
+                                        padding=(R - 1) // 2)
+        dw += g
+        if db is not None:
+            db += dy.sum((0, 1, 2))
+
+    # ------------------------------------------------------------------ ConvGRU gates
+    @staticmethod
+    def _gn(x, gamma, beta, eps):
+        B, H, W, Cc = x.shape
+        xg = x.reshape(B, H * W, Cc // 32, 32)
+        mean = xg.mean((1, 3), keepdim=True)
+        var = xg.var((1, 3), unbiased=False, keepdim=True)
+        rstd = 1 / torch.sqrt(var + eps)
+        y = ((xg - mean) * rstd).reshape(B, H, W, Cc) * gamma + beta
+        return y, mean.reshape(B, -1), rstd.reshape(B, -1)
+
+    def gru_gates_fwd(self, g, h, gamma, beta, eps, z, rh, stats):
+        self.launches += 1
+        Cc = g.shape[3] // 2
+        y, mean, rstd = self._gn(g, gamma.detach(), beta.detach(), eps)
+        a = torch.sigmoid(y)
+        z.copy_(a[..., :Cc])
+        rh.copy_(a[..., Cc:] * h)
+        stats.copy_(torch.stack((mean, rstd), -1).reshape(-1))
+
+    def gru_out_fwd(self, cpre, z, h, gamma, beta, eps, hnew, cand, stats):
+        self.launches += 1
+        y, mean, rstd = self._gn(cpre, gamma.detach(), beta.detach(), eps)
+        c = torch.tanh(y)
+        if cand is not None:
+            cand.copy_(c)
+        hnew.copy_((1 - z) * h + z * c)
+        stats.copy_(torch.stack((mean, rstd), -1).reshape(-1))
+
+    def gru_out_bwd(self, dhnew, cpre, cand, z, h, gamma, stats, dcpre, dz, dh, dgamma, dbeta):
+        self.launches += 1
+        # exact: use saved stats (mean, rstd) like the kernel does
+        B, H, W, Cc = cpre.shape
+        st = stats.reshape(B, Cc // 32, 2)
+        mean, rstd = st[..., 0], st[..., 1]
+        xg = cpre.reshape(B, H * W, Cc // 32, 32)
+        xh = ((xg - mean[:, None, :, None]) * rstd[:, None, :, None]).reshape(B, H, W, Cc)
+        dy = dhnew * z * (1 - cand * cand)
+        dgamma += (dy * xh).sum((0, 1, 2))
+        dbeta += dy.sum((0, 1, 2))
+        dxh = (dy * gamma.detach()).reshape(B, H * W, Cc // 32, 32)
+        xhg = xh.reshape(B, H * W, Cc // 32, 32)
+        m1 = dxh.mean((1, 3), keepdim=True)
+        m2 = (dxh * xhg).mean((1, 3), keepdim=True)
+        dcpre.copy_((rstd[:, None, :, None] * (dxh - m1 - xhg * m2)).reshape(B, H, W, Cc))
+        dz.copy_(dhnew * (cand - h))
+        dh.copy_(dhnew * (1 - z))
+
+    def gru_gates_bwd(self, dz, drh, dh_in, g, h, gamma, beta, stats, dg, dh_out, dgamma, dbeta):
+        self.launches += 1
+        B, H, W, C2 = g.shape
+        Cc = C2 // 2
+        st = stats.reshape(B, C2 // 32, 2)
+        mean, rstd = st[..., 0], st[..., 1]
+        xg = g.reshape(B, H * W, C2 // 32, 32)
+        xh = ((xg - mean[:, None, :, None]) * rstd[:, None, :, None]).reshape(B, H, W, C2)
+        a = torch.sigmoid(xh * gamma.detach() + beta.detach())
+        drh_v = drh.clone()
+        da = torch.cat((dz, drh_v * h), 3)
+        dy = da * a * (1 - a)
+        dgamma += (dy * xh).sum((0, 1, 2))
+        dbeta += dy.sum((0, 1, 2))
+        dxh = (dy * gamma.detach()).reshape(B, H * W, C2 // 32, 32)
+        xhg = xh.reshape(B, H * W, C2 // 32, 32)
+        m1 = dxh.mean((1, 3), keepdim=True)
+        m2 = (dxh * xhg).mean((1, 3), keepdim=True)
+        dg.copy_((rstd[:, None, :, None] * (dxh - m1 - xhg * m2)).reshape(B, H, W, C2))
+        dh_out.copy_(dh_in + drh_v * a[..., Cc:])
+
+    # ------------------------------------------------------------------ RK planes
+    def lincomb(self, out, ins, coefs, dtmask=0, dt_dev=None, skip=None):
+        self.launches += 1
+        if _skipped(skip):
+            return out
+        dt = f32(float(dt_dev.reshape(-1)[0])) if dt_dev is not None else f32(1)
+        acc = None
+        for j, (t, c) in enumerate(zip(ins, coefs)):
+            cj = f32(c) * dt if (dtmask >> j) & 1 else f32(c)
+            term = t.reshape(out.shape) * float(cj)
+            acc = term if acc is None else acc + term
+        out.copy_(acc)
+        return out
+
+    def act_bwd(self, out, dy, a, kind):
+        self.launches += 1
+        out.copy_(dy * _dact(a, kind))
+        return out
+
+    # ------------------------------------------------------------------ dopri5 controller
+    def dopri_state_bytes(self):
+        return _lib.STATE_HEAD_BYTES + 3 * 592 * 8 + 64
+
+    def dopri_init(self, st, t_dev, n_out, rtol, atol, max_attempts):
+        self.launches += 1
+        st.zero_()
+        s = _State(st).s
+        s.t0 = s.t1 = float(t_dev[0])
+        s.rtol, s.atol = rtol, atol
+        s.n_out, s.jnext, s.max_attempts = n_out, 1, max_attempts
+        s.done = 1 if n_out <= 1 else 0
+
+    def dopri_initnorm(self, st, phase, y0, f0, f1):
+        self.launches += 1
+        s = _State(st).s
+        if s.done:
+            return
+        scale = f32(s.atol) + y0.abs() * float(f32(s.rtol))
+        if phase == 0:
+            s.red[0] = float(((y0 / scale) ** 2).double().sum())
+            s.red[1] = float(((f0 / scale) ** 2).double().sum())
+        else:
+            s.red[0] = float((((f1 - f0) / scale) ** 2).double().sum())
+            s.red[1] = 0.0
+        s.red[2] = 0.0
+        s.red[3] = float(y0.numel())
+
+    def dopri_initctrl(self, st, phase):
+        self.launches += 1
+        s = _State(st).s
+        if s.done:
+            return
+        if phase == 0:
+            d0 = f32(math.sqrt(s.red[0] / s.red[3]))
+            d1 = f32(math.sqrt(s.red[1] / s.red[3]))
+            s.d0, s.d1 = float(d0), float(d1)
+            h0 = f32(1e-6) if (d0 < f32(1e-5) or d1 < f32(1e-5)) else f32(0.01) * d0 / d1
+            s.h0 = float(h0)
+            s.n_feval += 2
+        else:
+            h0, d1 = f32(s.h0), f32(s.d1)
+            d2 = f32(math.sqrt(s.red[0] / s.red[3])) / h0
+            s.d2 = float(d2)
+            if d1 <= f32(1e-15) and d2 <= f32(1e-15):
+                h1 = max(f32(1e-6), h0 * f32(1e-3))
+            else:
+                h1 = f32(np.power(f32(0.01) / max(d1, d2), f32(0.2)))
+            s.dt = float(min(f32(100) * h0, h1))
+
+    def dopri_begin(self, st):
+        self.launches += 1
+        s = _State(st).s
+        if s.done:
+            return
+        s.dt_try = s.dt
+        if not (s.t1 + s.dt > s.t1):
+            s.status |= 1
+            s.done = 1
+        if s.n_attempt >= s.max_attempts:
+            s.status |= 4
+            s.done = 1
+
+    def dopri_errnorm(self, st, y0, y1, k7):
+        self.launches += 1
+        s = _State(st).s
+        if s.done:
+            return
+        dt = f32(s.dt_try)
+        err = None
+        for j in (0, 2, 3, 4, 5, 6):
+            term = k7[j] * float(dt * f32(C_ERROR[j]))
+            err = term if err is None else err + term
+        tol = float(f32(s.atol)) + float(f32(s.rtol)) * torch.max(y0.abs(), y1.abs())
+        r = err / tol
+        s.red[0] = float((r * r).double().sum())
+        s.red[1] = float((~torch.isfinite(y0)).sum())
+        s.red[2] = 0.0
+        s.red[3] = float(y0.numel())
+
+    def dopri_ctrl(self, st, t_dev, log, log_cap):
+        self.launches += 1
+        s = _State(st).s
+        if s.done:
+            return
+        dt = s.dt_try
+        if s.red[1] > 0:
+            s.status |= 2
+            s.done = 1
+            return
+        ratio = float(f32(math.sqrt(s.red[0] / s.red[3])))
+        s.ratio = ratio
+        accept = 1 if ratio <= 1.0 else 0
+        s.accept = accept
+        s.n_feval += 6
+        a = s.n_attempt
+        if log is not None and a < log_cap:
+            log[a, 0], log[a, 1], log[a, 2], log[a, 3] = s.t1, dt, ratio, accept
+        s.n_attempt = a + 1
+        if accept:
+            s.t0 = s.t1
+            s.t1 = s.t1 + dt
+            s.n_accept += 1
+            j = s.jnext
+            s.jlo = j
+            while j < s.n_out and not (float(t_dev[j]) > s.t1):
+                j += 1
+            s.jhi = j
+            s.jnext = j
+            if j >= s.n_out:
+                s.done_next = 1
+        else:
+            s.n_reject += 1
+            s.jlo = s.jhi = s.jnext
+        if ratio == 0.0:
+            factor = 10.0
+        else:
+            dfactor = 1.0 if ratio < 1.0 else 0.2
+            factor = min(10.0, max(0.9 / ratio ** 0.2, dfactor))
+        s.dt = dt * factor
+
+    def dopri_advance(self, st, t_dev, y0, y1, k7, sol, ysave, fsave, save_cap):
+        self.launches += 2
+        s = _State(st).s
+        if s.done or not s.accept:
+            return
+        dt = float(f32(s.dt_try))
+        step = s.n_accept - 1
+        f0, f1 = k7[0].clone(), k7[6].clone()
+        if ysave is not None and step < save_cap:
+            ysave[step].copy_(y0)
+            fsave[step].copy_(f0)
+        if s.jhi > s.jlo:
+            m = None
+            for j in (0, 2, 3, 4, 5, 6):
+                term = k7[j] * float(f32(dt) * f32(C_MID[j]))
+                m = term if m is None else m + term
+            ymid = y0 + m
+            ca = 2 * dt * (f1 - f0) - 8 * (y1 + y0) + 16 * ymid
+            cb = dt * (5 * f0 - 3 * f1) + 18 * y0 + 14 * y1 - 32 * ymid
+            cc = dt * (f1 - 4 * f0) - 11 * y0 - 5 * y1 + 16 * ymid
+            cd = dt * f0
+            for j in range(s.jlo, s.jhi):
+                x = float(f32((float(t_dev[j]) - s.t0) / (s.t1 - s.t0)))
+                sol[j].copy_((((y0 + x * cd) + x * x * cc) + x * x * x * cb) + x * x * x * x * ca)
+        y0.copy_(y1)
+        k7[0].copy_(f1)
+        if s.done_next:
+            s.done = 1
+
+    # ------------------------------------------------------------------ layout
+    def nchw_to_nhwc(self, x, out):
+        self.launches += 1
+        out.copy_(x.movedim(-3, -1))
+        return out
+
+    def nhwc_to_nchw(self, x, out):
+        self.launches += 1
+        out.copy_(x.movedim(-1, -3))
+        return out
+
+    def launch_count(self):
+        return self.launches

@@ -1,0 +1,140 @@
+"""Host-side logic of the product (solver loops, speculative dopri5 chunks, hand-written backward replay, layout
+handling, drop-in surface) checked on CPU against the oracle, with the CUDA backend replaced by the torch-CPU
+emulation of tests/fake_backend.py.  The kernels themselves are checked by the `-m gpu` tests."""
+import pytest
+import torch
+
+import ode_rl_b200 as odex
+from oracle import refmodel, torchdiffeq_021 as tde
+from tests.util import make_ode_func, rel_err, timesteps
+
+
+def _sd(m):
+    return {k: v.detach().clone() for k, v in m.state_dict().items()}
+
+
+@pytest.mark.parametrize("method", ["euler", "rk4"])
+def test_fixed_grid_forward_and_grad(fake_backend, method):
+    f = make_ode_func(odex, C=32, n_units=32)
+    solver = odex.DiffEqSolver(f, method)
+    _, tp = timesteps(3, 4)
+    torch.manual_seed(1)
+    z0 = torch.randn(2, 32, 8, 16, requires_grad=True)
+    sol = solver(z0, tp)
+    assert sol.shape == (4, 2, 32, 8, 16)
+    w = torch.randn_like(sol)
+    (sol * w).sum().backward()
+    got = {n: p.grad.clone() for n, p in solver.named_parameters()}
+    gz = z0.grad.clone()
+    # oracle: autograd through the restated odeint over the same weights
+    sd = _sd(solver)
+    ps = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    z1 = z0.detach().clone().requires_grad_(True)
+    ref = refmodel.diffeq_solver(ps, z1, tp, method)
+    (ref * w).sum().backward()
+    assert rel_err(sol, ref) < 1e-5
+    assert rel_err(gz, z1.grad) < 1e-4
+    for n, g in got.items():
+        assert rel_err(g, ps[n].grad) < 1e-4, n
+
+
+def test_dopri5_forward_matches_oracle_step_for_step(fake_backend):
+    f = make_ode_func(odex, C=32, n_units=32, scale=3.0)
+    solver = odex.DiffEqSolver(f, "dopri5", odeint_rtol=1e-3, odeint_atol=1e-4)
+    solver._chunk_hint = 2                         # force several speculative chunks
+    _, tp = timesteps(10, 10)
+    torch.manual_seed(2)
+    z0 = torch.randn(2, 32, 8, 16)
+    with torch.no_grad():
+        sol = solver(z0, tp)
+    log = tde.StepLog()
+    ref = refmodel.diffeq_solver(_sd(solver), z0, tp, "dopri5", 1e-3, 1e-4, log=log)
+    st = solver.last_stats
+    assert (st.n_accept, st.n_reject) == (log.n_accept, log.n_reject)
+    assert st.n_feval == log.n_feval
+    assert st.host_syncs >= 2
+    for a, b in zip(st.attempts, log.attempts):
+        assert abs(a[1] - b[1]) <= 2e-5 * abs(b[1]) and bool(a[3]) == b[3]
+    assert rel_err(sol, ref) < 1e-5
+    # second call: the chunk hint makes it a single host sync
+    with torch.no_grad():
+        solver(z0, tp)
+    assert solver.last_stats.host_syncs == 1
+
+
+def test_dopri5_gradients(fake_backend):
+    f = make_ode_func(odex, C=32, n_units=32, scale=3.0)
+    solver = odex.DiffEqSolver(f, "dopri5", odeint_rtol=1e-3, odeint_atol=1e-4)
+    _, tp = timesteps(4, 6)
+    torch.manual_seed(3)
+    z0 = torch.randn(2, 32, 8, 16, requires_grad=True)
+    sol = solver(z0, tp)
+    w = torch.randn_like(sol)
+    (sol * w).sum().backward()
+    ps = {k: v.clone().requires_grad_(True) for k, v in _sd(solver).items()}
+    z1 = z0.detach().clone().requires_grad_(True)
+    ref = refmodel.diffeq_solver(ps, z1, tp, "dopri5", 1e-3, 1e-4)
+    (ref * w).sum().backward()
+    assert rel_err(sol, ref) < 1e-5
+    assert rel_err(z0.grad, z1.grad) < 1e-3
+    for n, p in solver.named_parameters():
+        assert rel_err(p.grad, ps[n].grad) < 1e-3, n
+
+
+def test_encoder_recurrence_forward_and_grad(fake_backend):
+    torch.manual_seed(0)
+    f = make_ode_func(odex, C=32, n_units=32)
+    cell = odex.ODEConvGRUCell(f, None, (8, 16), 32, device=torch.device("cpu"))
+    obs, _ = timesteps(5, 5)
+    torch.manual_seed(4)
+    x = torch.randn(5, 2, 32, 8, 16, requires_grad=True)
+    mean, std = cell(x, obs)
+    w1, w2 = torch.randn_like(mean), torch.randn_like(std)
+    ((mean * w1).sum() + (std * w2).sum()).backward()
+    ps = {k: v.clone().requires_grad_(True) for k, v in _sd(cell).items()}
+    x1 = x.detach().clone().requires_grad_(True)
+    rm, rs = refmodel.encoder_z0(ps, x1, obs)
+    ((rm * w1).sum() + (rs * w2).sum()).backward()
+    assert rel_err(mean, rm) < 1e-5 and rel_err(std, rs) < 1e-5
+    assert rel_err(x.grad, x1.grad) < 1e-4
+    for n, p in cell.named_parameters():
+        assert rel_err(p.grad, ps[n].grad) < 2e-4, n
+    yi, lat = cell.run_ode_conv_gru(x.detach(), obs)
+    ry, rl = refmodel.run_ode_conv_gru(_sd(cell), x.detach(), obs)
+    assert lat.shape == rl.shape and rel_err(lat, rl) < 1e-5 and rel_err(yi, ry) < 1e-5
+
+
+def test_convgru_cell_multi_step(fake_backend):
+    torch.manual_seed(0)
+    cell = odex.ConvGRUCell((8, 16), 32, 32, 5)
+    x = torch.randn(3, 2, 32, 8, 16)
+    h = torch.randn(2, 32, 8, 16)
+    out, hn = cell(x, h, seq_len=3)
+    sd = _sd(cell)
+    hh = h
+    for i in range(3):
+        hh = refmodel.convgru_step(sd, x[i], hh)
+    assert out.shape == (3, 2, 32, 8, 16)
+    assert rel_err(hn, hh) < 1e-5 and rel_err(out[-1], hh) < 1e-5
+
+
+def test_memory_mode_and_errors(fake_backend):
+    f = make_ode_func(odex, C=32, n_units=32)
+    _, tp = timesteps(2, 3)
+    z0 = torch.randn(1, 32, 8, 16)
+    y = odex.DiffEqSolver(f, "euler", memory=True)(z0, tp)     # degenerate 2^i * z0
+    assert y.shape == (1, 3, 32, 8, 16)
+    assert rel_err(y[:, 2], 8 * z0) < 1e-6
+    with pytest.raises(ValueError):
+        odex.DiffEqSolver(f, "adams")(z0, tp)
+    cell = odex.ODEConvGRUCell(f, None, (8, 16), 32)
+    with pytest.raises(AssertionError):
+        cell(torch.randn(4, 1, 32, 8, 16), tp)
+
+
+def test_product_has_no_cpu_path():
+    """Without the fake backend the product refuses CPU tensors (no silent fallback)."""
+    f = make_ode_func(odex, C=32, n_units=32)
+    _, tp = timesteps(2, 3)
+    with pytest.raises(odex.OdexError):
+        odex.DiffEqSolver(f, "euler")(torch.randn(1, 32, 8, 16), tp)
