@@ -62,8 +62,14 @@ def test_dopri5_forward_matches_oracle_step_for_step(fake_backend):
     assert solver.last_stats.host_syncs == 1
 
 
-def test_dopri5_gradients(fake_backend):
-    f = make_ode_func(odex, C=32, n_units=32, scale=3.0)
+@pytest.mark.parametrize("nonlinear", ["tanh", "relu"])
+def test_dopri5_gradients(fake_backend, nonlinear):
+    """Gradient through accepted steps + dense output.  With a smooth activation the hand-written replay matches
+    autograd through the oracle to fp32 rounding; with ReLU a pre-activation within rounding noise of 0 can take
+    the other branch (both are valid sub-gradients), so that case is held to an L2 bound instead of max-abs."""
+    import torch.nn.functional as F
+
+    f = make_ode_func(odex, C=32, n_units=32, scale=2.0, nonlinear=nonlinear)
     solver = odex.DiffEqSolver(f, "dopri5", odeint_rtol=1e-3, odeint_atol=1e-4)
     _, tp = timesteps(4, 6)
     torch.manual_seed(3)
@@ -73,12 +79,26 @@ def test_dopri5_gradients(fake_backend):
     (sol * w).sum().backward()
     ps = {k: v.clone().requires_grad_(True) for k, v in _sd(solver).items()}
     z1 = z0.detach().clone().requires_grad_(True)
-    ref = refmodel.diffeq_solver(ps, z1, tp, "dopri5", 1e-3, 1e-4)
+
+    def fn(t, y):
+        for n, i in enumerate((0, 2, 4, 6, 8)):
+            if n:
+                y = F.relu(y) if nonlinear == "relu" else torch.tanh(y)
+            y = F.conv2d(y, ps["ode_func.gradient_net.%d.weight" % i], ps["ode_func.gradient_net.%d.bias" % i], padding=1)
+        return y
+
+    ref = tde.odeint(fn, z1, tp, rtol=1e-3, atol=1e-4, method="dopri5")
     (ref * w).sum().backward()
     assert rel_err(sol, ref) < 1e-5
-    assert rel_err(z0.grad, z1.grad) < 1e-3
-    for n, p in solver.named_parameters():
-        assert rel_err(p.grad, ps[n].grad) < 1e-3, n
+    from tests.util import rel_l2
+    if nonlinear == "tanh":
+        assert rel_err(z0.grad, z1.grad) < 1e-5
+        for n, p in solver.named_parameters():
+            assert rel_err(p.grad, ps[n].grad) < 1e-5, n
+    else:
+        assert rel_l2(z0.grad, z1.grad) < 1e-3
+        for n, p in solver.named_parameters():
+            assert rel_l2(p.grad, ps[n].grad) < 1e-3, n
 
 
 def test_encoder_recurrence_forward_and_grad(fake_backend):
