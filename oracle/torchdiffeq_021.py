@@ -156,7 +156,7 @@ def _interp_evaluate(coeffs, t0, t1, t):
     return total
 
 
-def _dopri5(func, y0, t, rtol, atol, log, detach_dt0=True, max_num_steps=2 ** 31 - 1):
+def _dopri5(func, y0, t, rtol, atol, log, detach_dt0=True, max_num_steps=2 ** 31 - 1):  # noqa
     dtype = y0.dtype
     t = t.to(torch.float64)
     f0 = func(t[0], y0)

@@ -1,0 +1,211 @@
+"""-m gpu: every libodex kernel, called through the C-ABI (kernels.Backend -> ctypes), against the torch-CPU
+emulation of the same entry point (tests/fake_backend.py) on identical seeded inputs.
+Tolerances: the FFMA convolution and all elementwise / reduction kernels are fp32-exact up to summation order
+(<= 2e-6 of the output scale); the tcgen05 3xTF32 convolution keeps fp32-level accuracy (<= 5e-6)."""
+import pytest
+import torch
+
+from ode_rl_b200 import kernels as K
+from ode_rl_b200.kernels import ACT_NONE, ACT_RELU, ACT_TANH, CONV_SIMT, CONV_TC
+from tests.fake_backend import FakeBackend
+from tests.util import rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def be():
+    return K.Backend()
+
+
+@pytest.fixture(scope="module")
+def fb():
+    return FakeBackend()
+
+
+def g(t):
+    return None if t is None else t.cuda()
+
+
+CONV_CASES = [
+    # B, H, W, c0, c1, N, R
+    (2, 16, 16, 64, 0, 64, 3),
+    (3, 16, 16, 64, 64, 128, 5),
+    (2, 16, 16, 64, 64, 64, 5),
+    (2, 16, 16, 64, 0, 128, 1),
+    (2, 16, 16, 64, 0, 64, 1),
+    (1, 32, 32, 128, 0, 64, 3),
+    (1, 32, 32, 64, 0, 128, 3),
+    (1, 8, 8, 64, 0, 64, 3),
+    (2, 16, 16, 128, 0, 128, 5),
+]
+
+
+@pytest.mark.parametrize("impl", ["simt", "tc"])
+@pytest.mark.parametrize("case", CONV_CASES, ids=lambda c: "B%d_%dx%d_c%d+%d_N%d_R%d" % c)
+def test_conv2d_forward(be, fb, impl, case):
+    B, H, W, c0, c1, N, R = case
+    if impl == "simt" and (W % 16 or H % 8):
+        pytest.skip("FFMA kernel tiles 8x16")
+    if impl == "tc" and not K.tc_shape_ok(N, c0, c1, H, W, R):
+        pytest.skip("shape not taken by the tcgen05 kernel")
+    torch.manual_seed(hash(case) % 1000)
+    x0 = torch.randn(B, H, W, c0)
+    x1 = torch.randn(B, H, W, c1) if c1 else None
+    w = torch.randn(N, c0 + c1, R, R) / (R * (c0 + c1) ** 0.5)
+    bias = torch.randn(N)
+    ref = fb.conv2d(x0, x1, fb.pack_weights(w, False, False), None, N, R, bias, ACT_RELU, torch.empty(B, H, W, N))
+    tc = impl == "tc"
+    wp = be.pack_weights(g(w), False, tc)
+    out = torch.empty(B, H, W, N, device="cuda")
+    be.conv2d(g(x0), g(x1), None if tc else wp, wp if tc else None, N, R, g(bias), ACT_RELU, out,
+              impl=CONV_TC if tc else CONV_SIMT)
+    torch.cuda.synchronize()
+    e = rel_err(out, ref)
+    assert e < (5e-6 if tc else 2e-6), "conv %s %s: rel err %.3e" % (impl, case, e)
+
+
+@pytest.mark.parametrize("impl", ["simt", "tc"])
+def test_conv2d_epilogues_strides_dgrad_skip(be, fb, impl):
+    """dgrad-packed weights, activation-derivative mask, residual + alpha (host and device scalar), channel-slice
+    views (ld > channels) on every operand, and the skip flag."""
+    tc = impl == "tc"
+    B, H, W, Cn, N, R = 2, 16, 16, 64, 64, 3
+    torch.manual_seed(5)
+    wide_x = torch.randn(B, H, W, 2 * Cn)
+    wide_res = torch.randn(B, H, W, 3 * Cn)
+    wide_dact = torch.randn(B, H, W, 2 * N)
+    wide_out = torch.zeros(B, H, W, 2 * N)
+    w = torch.randn(Cn, N, R, R) / 24.0          # forward weight [n_out_fwd=Cn][c_in_fwd=N]: dgrad maps Cn -> N
+    alpha_dev = torch.tensor([0.37], dtype=torch.float64)
+    for kind in (ACT_RELU, ACT_TANH):
+        dact = torch.tanh(wide_dact) if kind == ACT_TANH else wide_dact
+        ref_out = wide_out.clone()
+        fb.conv2d(wide_x[..., Cn:], None, fb.pack_weights(w, True, False), None, N, R, None, ACT_NONE, ref_out[..., N:],
+                  dact=dact[..., :N], dact_kind=kind, res=wide_res[..., Cn:2 * Cn], alpha=-0.5, alpha_dev=alpha_dev)
+        wp = be.pack_weights(g(w), True, tc)
+        gx, gres, gd, gout = g(wide_x), g(wide_res), g(dact), g(wide_out)
+        be.conv2d(gx[..., Cn:], None, None if tc else wp, wp if tc else None, N, R, None, ACT_NONE, gout[..., N:],
+                  dact=gd[..., :N], dact_kind=kind, res=gres[..., Cn:2 * Cn], alpha=-0.5, alpha_dev=g(alpha_dev),
+                  impl=CONV_TC if tc else CONV_SIMT)
+        torch.cuda.synchronize()
+        assert rel_err(gout, ref_out) < 5e-6, "kind %d" % kind
+        assert float(gout[..., :N].abs().max()) == 0.0, "wrote outside its channel slice"
+    # skip flag: launch is a no-op
+    skip = torch.ones(1, dtype=torch.int32, device="cuda")
+    gout2 = torch.full((B, H, W, N), 7.0, device="cuda")
+    wp = be.pack_weights(g(w), True, tc)
+    be.conv2d(g(wide_x)[..., Cn:], None, None if tc else wp, wp if tc else None, N, R, None, ACT_NONE, gout2, skip=skip,
+              impl=CONV_TC if tc else CONV_SIMT)
+    torch.cuda.synchronize()
+    assert float((gout2 - 7.0).abs().max()) == 0.0
+
+
+def test_conv_tc_matches_simt_at_config_shapes(be):
+    """K1 at config-A shape (B=16, 64ch, 16x16, 3x3) and K2 (5x5, two sources, N=128): tcgen05 vs exact FFMA."""
+    torch.manual_seed(1)
+    for (B, c0, c1, N, R) in ((16, 64, 0, 64, 3), (16, 64, 64, 128, 5), (16, 64, 64, 64, 5)):
+        x0 = torch.randn(B, 16, 16, c0, device="cuda")
+        x1 = torch.randn(B, 16, 16, c1, device="cuda") if c1 else None
+        w = torch.randn(N, c0 + c1, R, R, device="cuda") / (R * (c0 + c1) ** 0.5)
+        b = torch.randn(N, device="cuda")
+        o1 = torch.empty(B, 16, 16, N, device="cuda")
+        o2 = torch.empty_like(o1)
+        be.conv2d(x0, x1, be.pack_weights(w, False, False), None, N, R, b, ACT_NONE, o1, impl=CONV_SIMT)
+        be.conv2d(x0, x1, None, be.pack_weights(w, False, True), N, R, b, ACT_NONE, o2, impl=CONV_TC)
+        torch.cuda.synchronize()
+        assert rel_err(o2, o1) < 5e-6
+
+
+@pytest.mark.parametrize("case", [(2, 16, 16, 64, 0, 64, 3), (2, 16, 16, 64, 64, 128, 5), (2, 16, 16, 64, 64, 64, 5),
+                                  (2, 16, 16, 64, 0, 128, 1), (1, 32, 32, 128, 0, 64, 3)],
+                         ids=lambda c: "B%d_%dx%d_c%d+%d_N%d_R%d" % c)
+def test_conv2d_wgrad(be, fb, case):
+    B, H, W, c0, c1, N, R = case
+    torch.manual_seed(3)
+    x0 = torch.randn(B, H, W, c0)
+    x1 = torch.randn(B, H, W, c1) if c1 else None
+    dy = torch.randn(B, H, W, N)
+    dw0 = torch.randn(N, c0 + c1, R, R)
+    db0 = torch.randn(N)
+    rw, rb = dw0.clone(), db0.clone()
+    fb.conv2d_wgrad(x0, x1, dy, R, rw, rb)
+    gw, gb = g(dw0), g(db0)
+    be.conv2d_wgrad(g(x0), g(x1), g(dy), R, gw, gb)
+    torch.cuda.synchronize()
+    assert rel_err(gw, rw) < 5e-6 and rel_err(gb, rb) < 5e-6
+
+
+def test_gru_gate_kernels(be, fb):
+    B, H, W, Cn = 3, 16, 16, 64
+    torch.manual_seed(7)
+    gpre = torch.randn(B, H, W, 2 * Cn) * 2 + 0.3
+    hwide = torch.randn(B, H, W, 2 * Cn)
+    h = hwide[..., Cn:]
+    gam_g, bet_g = torch.rand(2 * Cn) + 0.5, torch.randn(2 * Cn) * 0.1
+    gam_c, bet_c = torch.rand(Cn) + 0.5, torch.randn(Cn) * 0.1
+    cpre = torch.randn(B, H, W, Cn) * 1.5
+    # forward
+    z, rh, stg = torch.empty(B, H, W, Cn), torch.empty(B, H, W, Cn), torch.empty(B * 4 * 2)
+    fb.gru_gates_fwd(gpre, h, gam_g, bet_g, 1e-5, z, rh, stg)
+    hn, cand, stc = torch.empty(B, H, W, Cn), torch.empty(B, H, W, Cn), torch.empty(B * 2 * 2)
+    fb.gru_out_fwd(cpre, z, h, gam_c, bet_c, 1e-5, hn, cand, stc)
+    gz, grh, gstg = torch.empty(B, H, W, Cn, device="cuda"), torch.empty(B, H, W, Cn, device="cuda"), torch.empty(B * 8, device="cuda")
+    ghw = g(hwide)
+    be.gru_gates_fwd(g(gpre), ghw[..., Cn:], g(gam_g), g(bet_g), 1e-5, gz, grh, gstg)
+    ghn, gcand, gstc = torch.empty(B, H, W, Cn, device="cuda"), torch.empty(B, H, W, Cn, device="cuda"), torch.empty(B * 4, device="cuda")
+    be.gru_out_fwd(g(cpre), gz, ghw[..., Cn:], g(gam_c), g(bet_c), 1e-5, ghn, gcand, gstc)
+    torch.cuda.synchronize()
+    for a, b, n in ((gz, z, "z"), (grh, rh, "rh"), (gstg, stg, "stats_g"), (ghn, hn, "hnew"), (gcand, cand, "cand"), (gstc, stc, "stats_c")):
+        assert rel_err(a, b) < 3e-6, n
+    # backward
+    dhn = torch.randn(B, H, W, Cn)
+    dcp, dz, dh = torch.empty(B, H, W, Cn), torch.empty(B, H, W, Cn), torch.empty(B, H, W, Cn)
+    dgam_c, dbet_c = torch.zeros(Cn), torch.zeros(Cn)
+    fb.gru_out_bwd(dhn, cpre, cand, z, h, gam_c, stc, dcp, dz, dh, dgam_c, dbet_c)
+    D1 = torch.randn(B, H, W, 2 * Cn)
+    D1r = D1.clone()
+    dgp = torch.empty(B, H, W, 2 * Cn)
+    dgam_g, dbet_g = torch.zeros(2 * Cn), torch.zeros(2 * Cn)
+    fb.gru_gates_bwd(dz, D1r[..., Cn:], dh, gpre, h, gam_g, bet_g, stg, dgp, D1r[..., Cn:], dgam_g, dbet_g)
+    gdcp, gdz, gdh = (torch.empty(B, H, W, Cn, device="cuda") for _ in range(3))
+    gdgam_c, gdbet_c = torch.zeros(Cn, device="cuda"), torch.zeros(Cn, device="cuda")
+    be.gru_out_bwd(g(dhn), g(cpre), gcand, gz, ghw[..., Cn:], g(gam_c), gstc, gdcp, gdz, gdh, gdgam_c, gdbet_c)
+    gD1 = g(D1)
+    gdgp = torch.empty(B, H, W, 2 * Cn, device="cuda")
+    gdgam_g, gdbet_g = torch.zeros(2 * Cn, device="cuda"), torch.zeros(2 * Cn, device="cuda")
+    be.gru_gates_bwd(gdz, gD1[..., Cn:], gdh, g(gpre), ghw[..., Cn:], g(gam_g), g(bet_g), gstg, gdgp, gD1[..., Cn:],
+                     gdgam_g, gdbet_g)
+    torch.cuda.synchronize()
+    for a, b, n in ((gdcp, dcp, "dcpre"), (gdz, dz, "dz"), (gdh, dh, "dh"), (gdgam_c, dgam_c, "dgamma_c"),
+                    (gdbet_c, dbet_c, "dbeta_c"), (gdgp, dgp, "dg"), (gD1, D1r, "D1"), (gdgam_g, dgam_g, "dgamma_g"),
+                    (gdbet_g, dbet_g, "dbeta_g")):
+        assert rel_err(a, b) < 2e-5, n
+
+
+def test_lincomb_actbwd_layout(be, fb):
+    torch.manual_seed(9)
+    n = 3 * 16 * 16 * 64
+    ins = [torch.randn(n) for _ in range(8)]
+    coefs = [1.0, 35 / 384, -0.7, 500 / 1113, 125 / 192, -2187 / 6784, 11 / 84, 0.3]
+    dt = torch.tensor([0.0421], dtype=torch.float64)
+    for nin in (1, 2, 5, 8):
+        ref = fb.lincomb(torch.empty(n), ins[:nin], coefs[:nin], dtmask=0xFE & ((1 << nin) - 1), dt_dev=dt)
+        out = be.lincomb(torch.empty(n, device="cuda"), [g(t) for t in ins[:nin]], coefs[:nin],
+                         dtmask=0xFE & ((1 << nin) - 1), dt_dev=g(dt))
+        torch.cuda.synchronize()
+        assert rel_err(out, ref) < 1e-6, nin
+    skip = torch.ones(1, dtype=torch.int32, device="cuda")
+    out = torch.full((n,), 3.0, device="cuda")
+    be.lincomb(out, [g(ins[0])], [1.0], skip=skip)
+    assert float((out - 3).abs().max()) == 0.0
+    a = torch.tanh(ins[1])
+    for kind in (ACT_RELU, ACT_TANH):
+        ref = fb.act_bwd(torch.empty(n), ins[0], a, kind)
+        out = be.act_bwd(torch.empty(n, device="cuda"), g(ins[0]), g(a), kind)
+        assert rel_err(out, ref) < 1e-6
+    x = torch.randn(5, 3, 64, 16, 16)
+    o = be.nchw_to_nhwc(g(x), torch.empty(5, 3, 16, 16, 64, device="cuda"))
+    assert torch.equal(o.cpu(), x.movedim(-3, -1).contiguous())
+    back = be.nhwc_to_nchw(o, torch.empty(5, 3, 64, 16, 16, device="cuda"))
+    assert torch.equal(back.cpu(), x)
