@@ -1,0 +1,63 @@
+"""The torch-side CALLER of the hot path, for bench.py, smoke() and the parity tests: the same wiring as the
+reference's models/ODEConvGRU.py:12-99 (ConvEncode -> ODEConvGRUCell -> DiffEqSolver -> ConvDecode -> sigmoid)
+with identical submodule / parameter names, so a reference state_dict loads with strict=True.  ConvEncode /
+ConvDecode stay plain torch (north_star); only the two starred modules are ode_rl_b200's.  Where the reference
+tree is available, models/ODEConvGRU.py itself can be used instead: this class exists because
+/root/reference does not travel to the GPU box.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+
+from .modules import DiffEqSolver, ODEConvGRUCell, ODEFunc
+
+
+class _Encoder(nn.Module):          # models/ODEConvGRU.py:101-119 with n_downs == 2
+    def __init__(self, n_inputs, out_ch):
+        super().__init__()
+        act = nn.LeakyReLU(negative_slope=0.2, inplace=True)
+        self.encoder = nn.Sequential(nn.Conv2d(n_inputs, 16, 3, 2, 1), act, nn.Conv2d(16, out_ch, 3, 2, 1), act)
+
+    def forward(self, x):
+        return self.encoder(x)
+
+
+class _Decoder(nn.Module):          # models/ODEConvGRU.py:122-140 with n_ups == 2
+    def __init__(self, n_inputs, out_ch):
+        super().__init__()
+        act = nn.LeakyReLU(negative_slope=0.2, inplace=True)
+        self.decoder = nn.Sequential(nn.ConvTranspose2d(n_inputs, 32, 4, 2, 1), act, nn.ConvTranspose2d(32, out_ch, 4, 2, 1))
+
+    def forward(self, x):
+        return self.decoder(x)
+
+
+class ODEConvGRUHarness(nn.Module):
+    def __init__(self, method="euler", rtol=1e-4, atol=1e-5, in_channels=1, resolution=64, ch=64, n_units=64,
+                 n_ode_layers=3, device=torch.device("cpu")):
+        super().__init__()
+        self.device = device
+        hw = (resolution // 4, resolution // 4)
+        self.conv_encoder = _Encoder(in_channels, ch).to(device)
+        self.ode_encoder_func = ODEFunc(n_inputs=ch, n_outputs=ch, n_layers=n_ode_layers, n_units=n_units,
+                                        downsize=False, nonlinear='relu', device=device, final_act=False)
+        self.ode_convgru_cell = ODEConvGRUCell(self.ode_encoder_func, None, hw, ch, device=device)
+        self.ode_decoder_func = ODEFunc(n_inputs=ch, n_outputs=ch, n_layers=n_ode_layers, n_units=n_units,
+                                        downsize=False, nonlinear='relu', device=device, final_act=False)
+        self.diffeq_solver = DiffEqSolver(self.ode_decoder_func, method, odeint_rtol=rtol, odeint_atol=atol, device=device)
+        self.conv_decoder = _Decoder(ch, in_channels).to(device)
+
+    def forward(self, inputs, observed_tp, tp_to_predict, return_latents=True):
+        b, t, c, h, w = inputs.size()
+        enc = self.conv_encoder(inputs.view(b * t, c, h, w))
+        _, c_, h_, w_ = enc.size()
+        enc = enc.view(b, -1, c_, h_, w_).permute(1, 0, 2, 3, 4)             # time first
+        mean_z0, std_z0 = self.ode_convgru_cell(enc, observed_tp)
+        sol_y = self.diffeq_solver(mean_z0, tp_to_predict)                  # [T,B,C,H,W]
+        T, B, C, H, W = sol_y.size()
+        pred = torch.sigmoid(self.conv_decoder(sol_y.reshape(B * T, C, H, W)))
+        pred = pred.view(T, B, *pred.shape[1:]).permute(1, 0, 2, 3, 4)
+        if return_latents:
+            return {"pred": pred, "sol": sol_y, "mean_z0": mean_z0, "std_z0": std_z0}
+        return pred

@@ -1,0 +1,144 @@
+"""-m gpu: the product modules on cuda:0 (every op through libodex's C-ABI) against the committed golden
+fixtures of the real reference modules and against the CPU oracle on the same seeded inputs.
+Bars (north_star): fixed-step methods <= 1e-5 relative per predicted latent; dopri5: same accepted/rejected step
+sequence and final state within rtol; gradients of euler/rk4 match autograd through the oracle."""
+import pytest
+import torch
+
+import ode_rl_b200 as odex
+from ode_rl_b200 import _lib
+from oracle import refmodel, torchdiffeq_021 as tde
+from tests.dropin import build_product_model
+from tests.test_golden import CASES, load_case
+from tests.util import make_ode_func, rel_err, rel_l2, timesteps
+
+pytestmark = pytest.mark.gpu
+DEV = torch.device("cuda:0")
+
+
+def _sd_cpu(m):
+    return {k: v.detach().cpu().clone() for k, v in m.state_dict().items()}
+
+
+@pytest.mark.parametrize("impl", ["auto", "simt"])
+@pytest.mark.parametrize("name", CASES)
+def test_golden_rollout(name, impl):
+    rec, sd, frames = load_case(name)
+    prev = odex.set_conv_impl(impl)
+    try:
+        model = build_product_model(rec["method"], rec["rtol"], rec["atol"], sd, DEV)
+        obs, tp = timesteps(rec["T"], rec["T"], device=DEV)
+        n0 = _lib.launch_count()
+        with torch.no_grad():
+            out = model(frames.to(DEV), obs, tp)
+        torch.cuda.synchronize()
+        assert _lib.launch_count() > n0, "no libodex kernel launched"
+    finally:
+        odex.set_conv_impl(prev)
+    tol = 1e-5 if rec["method"] != "dopri5" else rec["rtol"]
+    errs = {k: rel_err(out[k], rec[k]) for k in ("mean_z0", "std_z0", "pred")}
+    errs["sol_last"] = rel_err(out["sol"][-1], rec["sol_last"])
+    errs["sol_mid"] = rel_err(out["sol"][rec["T"] // 2], rec["sol_mid"])
+    print(name, impl, errs, model.diffeq_solver.last_stats)
+    assert errs["mean_z0"] < 1e-5 and errs["std_z0"] < 1e-5, errs
+    assert errs["sol_last"] < tol and errs["sol_mid"] < tol and errs["pred"] < tol, errs
+    if rec["method"] == "dopri5":
+        st = model.diffeq_solver.last_stats
+        assert [bool(a[3]) for a in st.attempts] == [a[3] for a in rec["attempts"]]
+        assert st.n_feval == rec["n_feval"]
+        for a, b in zip(st.attempts, rec["attempts"]):
+            assert abs(a[1] - b[1]) <= 1e-4 * abs(b[1]), (a, b)
+
+
+@pytest.mark.parametrize("method", ["euler", "rk4"])
+def test_fixed_grid_gradients_vs_oracle(method):
+    f = make_ode_func(odex, C=64, n_units=64).to(DEV)
+    solver = odex.DiffEqSolver(f, method)
+    _, tp = timesteps(6, 4)
+    torch.manual_seed(11)
+    z0c = torch.randn(3, 64, 16, 16)
+    z0 = z0c.to(DEV).requires_grad_(True)
+    sol = solver(z0, tp.to(DEV))
+    w = torch.randn(sol.shape)
+    (sol * w.to(DEV)).sum().backward()
+    ps = {k: v.requires_grad_(True) for k, v in _sd_cpu(solver).items()}
+    z1 = z0c.clone().requires_grad_(True)
+    ref = refmodel.diffeq_solver(ps, z1, tp, method)
+    (ref * w).sum().backward()
+    assert rel_err(sol, ref) < 1e-5
+    assert rel_l2(z0.grad, z1.grad) < 1e-4
+    for n, p in solver.named_parameters():
+        assert rel_l2(p.grad, ps[n].grad) < 1e-4, n
+
+
+def test_encoder_recurrence_gradients_vs_oracle():
+    torch.manual_seed(0)
+    f = make_ode_func(odex, C=64, n_units=64)
+    cell = odex.ODEConvGRUCell(f, None, (16, 16), 64).to(DEV)
+    obs, _ = timesteps(5, 5)
+    torch.manual_seed(4)
+    xc = torch.randn(5, 2, 64, 16, 16)
+    x = xc.to(DEV).requires_grad_(True)
+    mean, std = cell(x, obs.to(DEV))
+    w1, w2 = torch.randn(mean.shape), torch.randn(std.shape)
+    ((mean * w1.to(DEV)).sum() + (std * w2.to(DEV)).sum()).backward()
+    ps = {k: v.requires_grad_(True) for k, v in _sd_cpu(cell).items()}
+    x1 = xc.clone().requires_grad_(True)
+    rm, rs = refmodel.encoder_z0(ps, x1, obs)
+    ((rm * w1).sum() + (rs * w2).sum()).backward()
+    assert rel_err(mean, rm) < 1e-5 and rel_err(std, rs) < 1e-5
+    assert rel_l2(x.grad, x1.grad) < 1e-4
+    for n, p in cell.named_parameters():
+        assert rel_l2(p.grad, ps[n].grad) < 2e-4, n
+
+
+def test_dopri5_step_sequence_and_gradients():
+    f = make_ode_func(odex, C=64, n_units=64, scale=3.0, nonlinear="tanh").to(DEV)
+    solver = odex.DiffEqSolver(f, "dopri5", odeint_rtol=1e-3, odeint_atol=1e-4)
+    solver._chunk_hint = 2
+    _, tp = timesteps(10, 10)
+    torch.manual_seed(2)
+    z0c = torch.randn(4, 64, 16, 16)
+    z0 = z0c.to(DEV).requires_grad_(True)
+    sol = solver(z0, tp.to(DEV))
+    w = torch.randn(sol.shape)
+    (sol * w.to(DEV)).sum().backward()
+    st = solver.last_stats
+    ps = {k: v.requires_grad_(True) for k, v in _sd_cpu(solver).items()}
+    z1 = z0c.clone().requires_grad_(True)
+    import torch.nn.functional as F
+
+    def fn(t, y):
+        for n, i in enumerate((0, 2, 4, 6, 8)):
+            if n:
+                y = torch.tanh(y)
+            y = F.conv2d(y, ps["ode_func.gradient_net.%d.weight" % i], ps["ode_func.gradient_net.%d.bias" % i], padding=1)
+        return y
+
+    log = tde.StepLog()
+    ref = tde.odeint(fn, z1, tp, rtol=1e-3, atol=1e-4, method="dopri5", log=log)
+    (ref * w).sum().backward()
+    print(st, log.attempts)
+    assert (st.n_accept, st.n_reject, st.n_feval) == (log.n_accept, log.n_reject, log.n_feval)
+    assert rel_err(sol, ref) < 1e-3
+    assert rel_l2(z0.grad, z1.grad) < 1e-3
+    for n, p in solver.named_parameters():
+        assert rel_l2(p.grad, ps[n].grad) < 1e-3, n
+
+
+def test_size_independent_properties_at_full_batch():
+    """BASELINE configs[1]-sized batch (B=128): linearity of the RK combine through the solver is not available
+    (f is non-linear), so use exact structural properties instead: sol[0] == z0 bit-for-bit, batch independence
+    (sample i of a B=128 run == the same sample run alone, bitwise for fixed-step methods) and determinism."""
+    f = make_ode_func(odex, C=64, n_units=64).to(DEV)
+    solver = odex.DiffEqSolver(f, "rk4")
+    _, tp = timesteps(10, 10, device=DEV)
+    torch.manual_seed(5)
+    z0 = torch.randn(128, 64, 16, 16, device=DEV)
+    with torch.no_grad():
+        a = solver(z0, tp)
+        b = solver(z0, tp)
+        one = solver(z0[17:18], tp)
+    assert torch.equal(a[0], z0)
+    assert torch.equal(a, b)
+    assert torch.equal(a[:, 17:18], one)
