@@ -171,6 +171,8 @@ def main():
     from ode_rl_b200.harness import ODEConvGRUHarness
 
     assert torch.cuda.is_available(), "bench.py (odex arm) needs a CUDA device; there is no CPU fallback"
+    torch.backends.cudnn.allow_tf32 = False          # torch-side ConvEncode/ConvDecode stay fp32 like the CPU reference
+    torch.backends.cuda.matmul.allow_tf32 = False
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:

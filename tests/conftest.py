@@ -10,6 +10,11 @@ if ROOT not in sys.path:
 sys.dont_write_bytecode = True
 
 
+# the torch-side ConvEncode / ConvDecode must be fp32 for parity against the CPU oracle (cuDNN defaults to TF32)
+torch.backends.cudnn.allow_tf32 = False
+torch.backends.cuda.matmul.allow_tf32 = False
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
 

@@ -50,9 +50,10 @@ def test_golden_rollout(name, impl):
             assert abs(a[1] - b[1]) <= 1e-4 * abs(b[1]), (a, b)
 
 
+@pytest.mark.parametrize("nonlinear", ["tanh", "relu"])
 @pytest.mark.parametrize("method", ["euler", "rk4"])
-def test_fixed_grid_gradients_vs_oracle(method):
-    f = make_ode_func(odex, C=64, n_units=64).to(DEV)
+def test_fixed_grid_gradients_vs_oracle(method, nonlinear):
+    f = make_ode_func(odex, C=64, n_units=64, nonlinear=nonlinear).to(DEV)
     solver = odex.DiffEqSolver(f, method)
     _, tp = timesteps(6, 4)
     torch.manual_seed(11)
@@ -63,17 +64,24 @@ def test_fixed_grid_gradients_vs_oracle(method):
     (sol * w.to(DEV)).sum().backward()
     ps = {k: v.requires_grad_(True) for k, v in _sd_cpu(solver).items()}
     z1 = z0c.clone().requires_grad_(True)
-    ref = refmodel.diffeq_solver(ps, z1, tp, method)
+    ref = refmodel.diffeq_solver(ps, z1, tp, method, act=nonlinear)
     (ref * w).sum().backward()
     assert rel_err(sol, ref) < 1e-5
-    assert rel_l2(z0.grad, z1.grad) < 1e-4
-    for n, p in solver.named_parameters():
-        assert rel_l2(p.grad, ps[n].grad) < 1e-4, n
+    tol = 1e-4 if nonlinear == "tanh" else 5e-3
+    errs = {n: rel_l2(p.grad, ps[n].grad) for n, p in solver.named_parameters()}
+    errs["z0"] = rel_l2(z0.grad, z1.grad)
+    print(method, nonlinear, errs)
+    assert max(errs.values()) < tol, errs
 
 
-def test_encoder_recurrence_gradients_vs_oracle():
+@pytest.mark.parametrize("nonlinear", ["tanh", "relu"])
+def test_encoder_recurrence_gradients_vs_oracle(nonlinear):
+    """tanh: smooth, so the hand-written backward must match autograd through the oracle to fp32 rounding.
+    relu: a pre-activation within rounding noise of 0 may take the other (equally valid) sub-gradient branch and
+    the difference spreads over the sample, so the bound is looser (the mask arithmetic itself is checked exactly
+    in test_gpu_kernels.py::test_conv2d_epilogues_strides_dgrad_skip)."""
     torch.manual_seed(0)
-    f = make_ode_func(odex, C=64, n_units=64)
+    f = make_ode_func(odex, C=64, n_units=64, nonlinear=nonlinear)
     cell = odex.ODEConvGRUCell(f, None, (16, 16), 64).to(DEV)
     obs, _ = timesteps(5, 5)
     torch.manual_seed(4)
@@ -84,12 +92,14 @@ def test_encoder_recurrence_gradients_vs_oracle():
     ((mean * w1.to(DEV)).sum() + (std * w2.to(DEV)).sum()).backward()
     ps = {k: v.requires_grad_(True) for k, v in _sd_cpu(cell).items()}
     x1 = xc.clone().requires_grad_(True)
-    rm, rs = refmodel.encoder_z0(ps, x1, obs)
+    rm, rs = refmodel.encoder_z0(ps, x1, obs, act=nonlinear)
     ((rm * w1).sum() + (rs * w2).sum()).backward()
     assert rel_err(mean, rm) < 1e-5 and rel_err(std, rs) < 1e-5
-    assert rel_l2(x.grad, x1.grad) < 1e-4
-    for n, p in cell.named_parameters():
-        assert rel_l2(p.grad, ps[n].grad) < 2e-4, n
+    tol = 1e-4 if nonlinear == "tanh" else 5e-3
+    errs = {n: rel_l2(p.grad, ps[n].grad) for n, p in cell.named_parameters()}
+    errs["x"] = rel_l2(x.grad, x1.grad)
+    print(nonlinear, errs)
+    assert max(errs.values()) < tol, errs
 
 
 def test_dopri5_step_sequence_and_gradients():
