@@ -10,7 +10,7 @@ from ode_rl_b200 import _lib
 from oracle import refmodel, torchdiffeq_021 as tde
 from tests.dropin import build_product_model
 from tests.test_golden import CASES, load_case
-from tests.util import make_ode_func, rel_err, rel_l2, timesteps
+from tests.util import latent_rel, make_ode_func, rel_err, rel_l2, timesteps
 
 pytestmark = pytest.mark.gpu
 DEV = torch.device("cuda:0")
@@ -35,13 +35,18 @@ def test_golden_rollout(name, impl):
         assert _lib.launch_count() > n0, "no libodex kernel launched"
     finally:
         odex.set_conv_impl(prev)
+    # north_star: <= 1e-5 relative per predicted latent (||.||2 per latent) for fixed-step methods; dopri5: final state
+    # within rtol.  The max-abs figure is also bounded: 1e-5 for the exact-fp32 FFMA path, 3e-5 for 3xTF32.
     tol = 1e-5 if rec["method"] != "dopri5" else rec["rtol"]
-    errs = {k: rel_err(out[k], rec[k]) for k in ("mean_z0", "std_z0", "pred")}
-    errs["sol_last"] = rel_err(out["sol"][-1], rec["sol_last"])
-    errs["sol_mid"] = rel_err(out["sol"][rec["T"] // 2], rec["sol_mid"])
-    print(name, impl, errs, model.diffeq_solver.last_stats)
-    assert errs["mean_z0"] < 1e-5 and errs["std_z0"] < 1e-5, errs
-    assert errs["sol_last"] < tol and errs["sol_mid"] < tol and errs["pred"] < tol, errs
+    tol_max = (1e-5 if impl == "simt" else 3e-5) if rec["method"] != "dopri5" else rec["rtol"]
+    pairs = {"mean_z0": (out["mean_z0"], rec["mean_z0"]), "std_z0": (out["std_z0"], rec["std_z0"]),
+             "sol_last": (out["sol"][-1], rec["sol_last"]), "sol_mid": (out["sol"][rec["T"] // 2], rec["sol_mid"]),
+             "pred": (out["pred"], rec["pred"])}
+    errs = {k: (latent_rel(a, b), rel_err(a, b)) for k, (a, b) in pairs.items()}
+    print(name, impl, {k: "l2 %.2e max %.2e" % v for k, v in errs.items()}, model.diffeq_solver.last_stats)
+    assert errs["mean_z0"][0] < 1e-5 and errs["std_z0"][0] < 1e-5, errs
+    for k, (l2, mx) in errs.items():
+        assert l2 < tol and mx < tol_max, (k, errs)
     if rec["method"] == "dopri5":
         st = model.diffeq_solver.last_stats
         assert [bool(a[3]) for a in st.attempts] == [a[3] for a in rec["attempts"]]

@@ -28,3 +28,11 @@ def make_ode_func(ode_rl, C=64, n_layers=3, n_units=64, seed=0, scale=1.0, final
             for p in f.parameters():
                 p.mul_(scale)
     return f
+
+
+def latent_rel(a: torch.Tensor, b: torch.Tensor) -> float:
+    """north_star's bar, 'relative per predicted latent': worst over latents (leading dims = time/batch, last 3 =
+    C,H,W) of ||a_i - b_i||_2 / ||b_i||_2."""
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    a, b = a.reshape(-1, *a.shape[-3:]).flatten(1), b.reshape(-1, *b.shape[-3:]).flatten(1)
+    return float(((a - b).norm(dim=1) / b.norm(dim=1).clamp_min(1e-30)).max())
