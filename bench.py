@@ -182,19 +182,13 @@ def main():
     model = ODEConvGRUHarness(args.method, rtol=1e-3, atol=1e-4, device=dev).to(dev)
     params = [p for p in model.parameters()]
     opt = torch.optim.Adam(params, lr=1e-3)
-    if world > 1 and args.method == "dopri5":
-        model.diffeq_solver.reduce_fn = lambda red: dist.all_reduce(red)      # batch-shared step size (SUM mode)
+    from ode_rl_b200 import parallel
+    if world > 1:
+        parallel.shard_solver(model.diffeq_solver, mode="sum")                # dopri5: batch-shared step size (SUM = parity mode)
+    bucket = parallel.GradBucket(params)
     xh, yh = synth(B, 1234 + rank, "cpu", pin=True)
     x, y = xh.to(dev), yh.to(dev)
     obs, tp = times(dev)
-
-    def allreduce_grads():
-        gs = [p.grad for p in params if p.grad is not None]
-        flat = torch._utils._flatten_dense_tensors(gs)
-        dist.all_reduce(flat)
-        flat.div_(world)
-        for g_, f_ in zip(gs, torch._utils._unflatten_dense_tensors(flat, gs)):
-            g_.copy_(f_)
 
     def step(xd, yd):
         opt.zero_grad(set_to_none=True)
@@ -202,7 +196,7 @@ def main():
         loss = torch.nn.functional.mse_loss(pred, yd)
         loss.backward()
         if world > 1:
-            allreduce_grads()
+            bucket.allreduce()
         opt.step()
         return loss
 
