@@ -158,3 +158,26 @@ def test_product_has_no_cpu_path():
     _, tp = timesteps(2, 3)
     with pytest.raises(odex.OdexError):
         odex.DiffEqSolver(f, "euler")(torch.randn(1, 32, 8, 16), tp)
+
+
+def test_c_abi_library_exports_every_header_symbol():
+    """libodex.so loads on a CPU-only box (static cudart) and exports exactly what include/odex.h declares; the
+    ctypes prototype table covers every one of them.  No compute call is made."""
+    import ctypes
+    import os
+    import re
+
+    from ode_rl_b200 import _lib
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hdr = open(os.path.join(root, "include", "odex.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(odex_[a-z0-9_]+)\s*\(", hdr))
+    assert len(declared) >= 20
+    assert declared == set(_lib.SIGNATURES), declared ^ set(_lib.SIGNATURES)
+    l = _lib.lib()
+    for name in declared:
+        assert hasattr(l, name), name
+    assert l.odex_version() == _lib.ODEX_VERSION
+    assert ctypes.sizeof(_lib.DopriState) <= _lib.STATE_HEAD_BYTES
+    assert l.odex_dopri_state_bytes() > _lib.STATE_HEAD_BYTES
