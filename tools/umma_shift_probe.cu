@@ -79,7 +79,7 @@ __global__ void __launch_bounds__(128) probe(const __grid_constant__ CUtensorMap
 // A: 4 planes (32 M-values each) x kRowsT rows x 128 B; B: 2 planes.  D[m][n] = sum_k A[k + shift][m] * B[k][n].
 constexpr int kRowsT = 64;
 __global__ void __launch_bounds__(128) probe_mn(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                                                int shift, int bo_mode, float* out) {
+                                                int shift, int bo_mode, int layout_type, int sbo, float* out) {
     extern __shared__ uint8_t raw[];
     const uint32_t base = (smem_u32(raw) + 1023u) & ~1023u;
     const uint32_t plane = kRowsT * 128;
@@ -107,9 +107,12 @@ __global__ void __launch_bounds__(128) probe_mn(const __grid_constant__ CUtensor
             const uint32_t sa = a_sm + (shift + 8 * k8) * 128;
             const uint32_t sb = b_sm + (8 * k8) * 128;
             const uint32_t bo = bo_mode == 0 ? 0u : ((sa >> 7) & 7u);
-            uint64_t ad = umma_desc_sw128(sa, plane, 1024);
+            uint64_t ad = umma_desc_sw128(sa, plane, sbo);
             ad |= static_cast<uint64_t>(bo) << 49;
-            const uint64_t bd = umma_desc_sw128(sb, plane, 1024);
+            uint64_t bd = umma_desc_sw128(sb, plane, sbo);
+            // layout type lives in bits [61,64): 2 = SWIZZLE_128B (16-byte atoms), 1 = SWIZZLE_128B_BASE32B
+            ad = (ad & ~(7ull << 61)) | (static_cast<uint64_t>(layout_type) << 61);
+            bd = (bd & ~(7ull << 61)) | (static_cast<uint64_t>(layout_type) << 61);
             umma_tf32_ss(tmem, ad, bd, idesc, k8 != 0);
         }
         umma_commit(bar_mma);
@@ -188,6 +191,8 @@ int main() {
         cudaMalloc(&dtA, tA.size() * 4); cudaMalloc(&dtB, tB.size() * 4);
         cudaMemcpy(dtA, tA.data(), tA.size() * 4, cudaMemcpyHostToDevice);
         cudaMemcpy(dtB, tB.data(), tB.size() * 4, cudaMemcpyHostToDevice);
+        for (int lt = 1; lt <= 2; ++lt)
+        for (int sbo = 512; sbo <= 1024; sbo *= 2) {
         CUtensorMap mA, mB;
         auto mk2 = [&](CUtensorMap* tm, float* ptr, int rows) {
             const cuuint64_t dims[2] = {32, static_cast<cuuint64_t>(rows)};
@@ -195,7 +200,8 @@ int main() {
             const cuuint32_t box[2] = {32, static_cast<cuuint32_t>(kRowsT)};
             const cuuint32_t es[2] = {1, 1};
             return enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, ptr, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                       CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                       lt == 1 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                       CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         };
         if (mk2(&mA, dtA, 4 * kRowsT) != CUDA_SUCCESS || mk2(&mB, dtB, 2 * kRowsT) != CUDA_SUCCESS) { printf("encode failed\n"); return 2; }
         const int smem2 = 1024 + 6 * kRowsT * 128 + 64;
@@ -203,7 +209,7 @@ int main() {
         for (int shift = 0; shift < 12; ++shift)
             for (int bo = 0; bo < 2; ++bo) {
                 cudaMemset(dO, 0, 128 * kN * 4);
-                probe_mn<<<1, 128, smem2>>>(mA, mB, shift, bo, dO);
+                probe_mn<<<1, 128, smem2>>>(mA, mB, shift, bo, lt, sbo, dO);
                 cudaError_t e = cudaDeviceSynchronize();
                 if (e != cudaSuccess) { printf("MN shift %d bo %d: CUDA error %s\n", shift, bo, cudaGetErrorString(e)); return 3; }
                 cudaMemcpy(hO.data(), dO, hO.size() * 4, cudaMemcpyDeviceToHost);
@@ -215,8 +221,9 @@ int main() {
                             ref += tA[((m / 32) * kRowsT + k + shift) * 32 + (m % 32)] * tB[((n / 32) * kRowsT + k) * 32 + (n % 32)];
                         if (ref != hO[m * kN + n]) ++bad;
                     }
-                printf("MN-major shift %2d base_offset_mode %d : %s (%d mismatches)\n", shift, bo, bad ? "WRONG" : "ok", bad);
+                printf("MN-major layout_type %d sbo %4d shift %2d base_offset_mode %d : %s (%d mismatches)\n", lt, sbo, shift, bo, bad ? "WRONG" : "ok", bad);
             }
+        }
     }
     return 0;
 }
