@@ -93,6 +93,17 @@ int odex_conv2d(const odex_conv_desc* d, odex_stream_t s);
 int odex_conv2d_wgrad(const float* x0, int ld0, int c0, const float* x1, int ld1, int c1, const float* dy, int ldy,
                       int B, int H, int W, int R, int N, float* dw, float* db, odex_stream_t s);
 
+/* Same gradient, accumulated into the kernels' own layout dwp[tap][c][n] ([R*R][c0+c1][N], n contiguous) so that the
+ * tensor-core kernel can add its TMEM accumulators with 16-byte vector reductions and a backward pass that visits a
+ * layer many times (one visit per f-eval) converts to OIHW only once, with odex_wgrad_unpack (dw[n][c][r][s] +=
+ * dwp[r*R+s][c][n]).  impl: ODEX_CONV_AUTO / _SIMT / _TC.  The TC kernel (tcgen05 kind::tf32, 3xTF32, MN-major
+ * operands straight from NHWC, tap shift = operand start address) needs c0, c1, N % 64 == 0, W % 16 == 0,
+ * H % 4 == 0, R in {1,3,5}.  Replaces the same autograd ops as odex_conv2d_wgrad. */
+int odex_conv2d_wgrad_packed(const float* x0, int ld0, int c0, const float* x1, int ld1, int c1, const float* dy,
+                             int ldy, int B, int H, int W, int R, int N, float* dwp, float* db, int impl,
+                             odex_stream_t s);
+int odex_wgrad_unpack(const float* dwp, int N, int C, int R, float* dw, odex_stream_t s);
+
 /* ------------------------------------------------------------------------------------------------ ConvGRU gates
  * GroupNorm (groups of 32 channels, biased variance, eps, affine) fused with the gate non-linearities.
  * g: conv_gates output [B,H,W,2C] (bias included).  z = sigmoid(GN(g)[:, :C]); r = sigmoid(GN(g)[:, C:]);

@@ -76,6 +76,8 @@ SIGNATURES = {
     "odex_pack_weights": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _vp]),
     "odex_conv2d": (_i, [C.POINTER(ConvDesc), _vp]),
     "odex_conv2d_wgrad": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
+    "odex_conv2d_wgrad_packed": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
+    "odex_wgrad_unpack": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "odex_gru_gates_fwd": (_i, [_vp, _vp, _i, _vp, _vp, _f, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "odex_gru_out_fwd": (_i, [_vp, _vp, _vp, _i, _vp, _vp, _f, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "odex_gru_out_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -213,6 +213,7 @@ struct WgradArgs {
     int B, H, W, R, N;
     float* dw;
     int nsplit;
+    int packed;      // 0: dw is torch OIHW; 1: dw is [tap][Ctot][N] (the accumulation layout of the tensor-core kernel)
 };
 
 __global__ void __launch_bounds__(256) conv_wgrad_kernel(const WgradArgs a) {
@@ -281,7 +282,11 @@ __global__ void __launch_bounds__(256) conv_wgrad_kernel(const WgradArgs a) {
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const int n = nb * 64 + tn * 4 + j;
-            if (n < a.N) atomicAdd(a.dw + ((static_cast<long>(n) * Ctot + c) * a.R + r) * a.R + s, acc[i][j]);
+            if (n < a.N) {
+                float* dst = a.packed ? a.dw + (static_cast<long>(tap) * Ctot + c) * a.N + n
+                                      : a.dw + ((static_cast<long>(n) * Ctot + c) * a.R + r) * a.R + s;
+                atomicAdd(dst, acc[i][j]);
+            }
         }
     }
 }
@@ -347,18 +352,18 @@ extern "C" int odex_pack_weights(const float* w, int N, int C, int R, int dgrad,
     return launched("pack_simt_kernel");
 }
 
-extern "C" int odex_conv2d_wgrad(const float* x0, int ld0, int c0, const float* x1, int ld1, int c1, const float* dy,
-                                 int ldy, int B, int H, int W, int R, int N, float* dw, float* db, odex_stream_t s_) {
-    cudaStream_t s = static_cast<cudaStream_t>(s_);
-    if (!x0 || !dy || !dw) return fail(ODEX_E_ARG, "wgrad: null pointer");
-    if (!x1) c1 = 0;
+namespace odex {
+bool wgrad_tc_supported(int c0, int c1, int N, int H, int W, int R);
+int launch_wgrad_tc(const float* x0, int ld0, int c0, const float* x1, int ld1, int c1, const float* dy, int ldy, int B,
+                    int H, int W, int R, int N, float* dwp, float* db, cudaStream_t s);
+
+static int wgrad_simt(const float* x0, int ld0, int c0, const float* x1, int ld1, int c1, const float* dy, int ldy,
+                      int B, int H, int W, int R, int N, float* dw, float* db, int packed, cudaStream_t s) {
     if (c0 % 64 != 0 || c1 % 64 != 0 || N % 4 != 0)
         return fail(ODEX_E_SHAPE, "wgrad: need c0, c1 %% 64 == 0 and N %% 4 == 0 (c0=%d c1=%d N=%d)", c0, c1, N);
-    if (!aligned16(x0) || !aligned16(dy) || (x1 && !aligned16(x1)) || ld0 % 4 || ldy % 4 || (x1 && ld1 % 4))
-        return fail(ODEX_E_ALIGN, "wgrad: pointers / strides must be 16-byte aligned");
     WgradArgs a;
     a.x0 = x0; a.ld0 = ld0; a.c0 = c0; a.x1 = x1; a.ld1 = ld1; a.c1 = c1;
-    a.dy = dy; a.ldy = ldy; a.B = B; a.H = H; a.W = W; a.R = R; a.N = N; a.dw = dw;
+    a.dy = dy; a.ldy = ldy; a.B = B; a.H = H; a.W = W; a.R = R; a.N = N; a.dw = dw; a.packed = packed;
     const int base = R * R * ((c0 + c1) / 64) * ((N + 63) / 64);
     const long P = static_cast<long>(B) * H * W;
     int nsplit = std::max(1, (4 * kSMs + base - 1) / base);
@@ -375,4 +380,32 @@ extern "C" int odex_conv2d_wgrad(const float* x0, int ld0, int c0, const float* 
         rc = launched("colsum_kernel");
     }
     return rc;
+}
+
+static int wgrad_check(const float* x0, int ld0, const float* x1, int ld1, const float* dy, int ldy, const float* dw) {
+    if (!x0 || !dy || !dw) return fail(ODEX_E_ARG, "wgrad: null pointer");
+    if (!aligned16(x0) || !aligned16(dy) || (x1 && !aligned16(x1)) || ld0 % 4 || ldy % 4 || (x1 && ld1 % 4))
+        return fail(ODEX_E_ALIGN, "wgrad: pointers / strides must be 16-byte aligned");
+    return 0;
+}
+}  // namespace odex
+
+extern "C" int odex_conv2d_wgrad(const float* x0, int ld0, int c0, const float* x1, int ld1, int c1, const float* dy,
+                                 int ldy, int B, int H, int W, int R, int N, float* dw, float* db, odex_stream_t s_) {
+    if (int rc = wgrad_check(x0, ld0, x1, ld1, dy, ldy, dw)) return rc;
+    if (!x1) c1 = 0;
+    return wgrad_simt(x0, ld0, c0, x1, ld1, c1, dy, ldy, B, H, W, R, N, dw, db, 0, static_cast<cudaStream_t>(s_));
+}
+
+extern "C" int odex_conv2d_wgrad_packed(const float* x0, int ld0, int c0, const float* x1, int ld1, int c1,
+                                        const float* dy, int ldy, int B, int H, int W, int R, int N, float* dwp,
+                                        float* db, int impl, odex_stream_t s_) {
+    cudaStream_t s = static_cast<cudaStream_t>(s_);
+    if (int rc = wgrad_check(x0, ld0, x1, ld1, dy, ldy, dwp)) return rc;
+    if (!x1) c1 = 0;
+    const bool tc_ok = wgrad_tc_supported(c0, c1, N, H, W, R);
+    if (impl == ODEX_CONV_TC && !tc_ok)
+        return fail(ODEX_E_UNSUPPORTED, "wgrad(tc): shape not supported (c0=%d c1=%d N=%d HxW=%dx%d R=%d)", c0, c1, N, H, W, R);
+    if (impl != ODEX_CONV_SIMT && tc_ok) return launch_wgrad_tc(x0, ld0, c0, x1, ld1, c1, dy, ldy, B, H, W, R, N, dwp, db, s);
+    return wgrad_simt(x0, ld0, c0, x1, ld1, c1, dy, ldy, B, H, W, R, N, dwp, db, 1, s);
 }

@@ -68,6 +68,18 @@ class GradSink:
 
     def __init__(self):
         self._g: Dict[int, torch.Tensor] = {}
+        self._packed: Dict[int, torch.Tensor] = {}      # conv weights: [R*R, C, N] accumulators (kernel layout)
+
+    def get_packed(self, w: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+        """Accumulator of a Conv2d weight gradient in the wgrad kernels' layout; converted to OIHW in result()."""
+        if w is None or not w.requires_grad:
+            return None
+        g = self._packed.get(id(w))
+        if g is None:
+            N, Cc, R, _ = w.shape
+            g = torch.zeros((R * R, Cc, N), dtype=torch.float32, device=w.device)
+            self._packed[id(w)] = g
+        return g
 
     def get(self, p: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
         if p is None or not p.requires_grad:
@@ -79,7 +91,17 @@ class GradSink:
         return g
 
     def result(self, params: Sequence[torch.Tensor]) -> Tuple[Optional[torch.Tensor], ...]:
+        be = K.backend()
+        for p in params:
+            gp = self._packed.pop(id(p), None)
+            if gp is not None:
+                be.wgrad_unpack(gp, self.get(p))
         return tuple(self._g.get(id(p)) if p.requires_grad else None for p in params)
+
+
+def _scratch_packed(w: torch.Tensor) -> torch.Tensor:
+    N, Cc, R, _ = w.shape
+    return torch.zeros((R * R, Cc, N), dtype=torch.float32, device=w.device)
 
 
 class _PackCache:
@@ -231,11 +253,11 @@ class ConvNetOp:
         for l in range(L - 1, -1, -1):
             conv, _ = self.layers[l]
             a_l = saved[l]
-            gw, gb = sink.get(conv.weight), sink.get(conv.bias)
+            gw, gb = sink.get_packed(conv.weight), sink.get(conv.bias)
             if gw is not None or gb is not None:
                 if gw is None:   # bias-only gradient: still needs a dw target for the kernel
-                    gw = torch.zeros_like(conv.weight)
-                be.conv2d_wgrad(a_l, None, d, conv.kernel_size[0], gw, gb)
+                    gw = _scratch_packed(conv.weight)
+                be.conv2d_wgrad_packed(a_l, None, d, conv.kernel_size[0], gw, gb)
             if l == 0 and not need_dx:
                 return None
             pk = self.caches[l].get(H, W, a_l.shape[3], 0, True)
@@ -318,9 +340,9 @@ class GruOp:
         dh_a = torch.empty((B, H, W, C), dtype=f32, device=dev)
         be.gru_out_bwd(dhnew, cpre, cand, z, h, self.gn_c.weight, st_c, dcpre, dz, dh_a,
                        grad_or_scratch(self.gn_c.weight), grad_or_scratch(self.gn_c.bias))
-        gw, gb = sink.get(self.cc.weight), sink.get(self.cc.bias)
+        gw, gb = sink.get_packed(self.cc.weight), sink.get(self.cc.bias)
         if gw is not None or gb is not None:
-            be.conv2d_wgrad(x, rh, dcpre, R, gw if gw is not None else torch.zeros_like(self.cc.weight), gb)
+            be.conv2d_wgrad_packed(x, rh, dcpre, R, gw if gw is not None else _scratch_packed(self.cc.weight), gb)
         pc = self.pc_c.get(H, W, Cx, C, True)
         D1 = torch.empty((B, H, W, Cx + C), dtype=f32, device=dev)            # [dx_can | drh]
         be.conv2d(dcpre, None, pc.dgrad_simt, pc.dgrad_tc, Cx + C, R, None, ACT_NONE, D1)
@@ -328,9 +350,9 @@ class GruOp:
         drh = D1[..., Cx:]
         be.gru_gates_bwd(dz, drh, dh_a, g, h, self.gn_g.weight, self.gn_g.bias, st_g, dg, drh,
                          grad_or_scratch(self.gn_g.weight), grad_or_scratch(self.gn_g.bias))   # D1[..., Cx:] <- dh_a + drh*r
-        gw, gb = sink.get(self.cg.weight), sink.get(self.cg.bias)
+        gw, gb = sink.get_packed(self.cg.weight), sink.get(self.cg.bias)
         if gw is not None or gb is not None:
-            be.conv2d_wgrad(x, h, dg, R, gw if gw is not None else torch.zeros_like(self.cg.weight), gb)
+            be.conv2d_wgrad_packed(x, h, dg, R, gw if gw is not None else _scratch_packed(self.cg.weight), gb)
         pg = self.pc_g.get(H, W, Cx, C, True)
         D2 = out if out is not None else torch.empty((B, H, W, Cx + C), dtype=f32, device=dev)
         be.conv2d(dg, None, pg.dgrad_simt, pg.dgrad_tc, Cx + C, R, None, ACT_NONE, D2, res=D1, alpha=1.0)

@@ -137,6 +137,35 @@ def test_conv2d_wgrad(be, fb, case):
     assert rel_err(gw, rw) < 5e-6 and rel_err(gb, rb) < 5e-6
 
 
+@pytest.mark.parametrize("impl", ["tc", "simt"])
+@pytest.mark.parametrize("case", [(2, 16, 16, 64, 0, 64, 3), (3, 16, 16, 64, 64, 128, 5), (2, 16, 16, 64, 64, 64, 5),
+                                  (2, 16, 16, 64, 0, 128, 1), (1, 32, 32, 128, 0, 64, 3), (5, 8, 32, 64, 0, 64, 3)],
+                         ids=lambda c: "B%d_%dx%d_c%d+%d_N%d_R%d" % c if isinstance(c, tuple) else c)
+def test_conv2d_wgrad_packed(be, fb, case, impl):
+    """Tensor-core weight gradient (3xTF32, MN-major operands, tap shift = descriptor start address) and the FFMA
+    kernel in the packed accumulation layout, against torch's conv2d_weight on the CPU; then the OIHW unpack."""
+    B, H, W, c0, c1, N, R = case
+    torch.manual_seed(4)
+    x0 = torch.randn(B, H, W, c0)
+    x1 = torch.randn(B, H, W, c1) if c1 else None
+    dy = torch.randn(B, H, W, N)
+    dwp0 = torch.randn(R * R, c0 + c1, N)
+    db0 = torch.randn(N)
+    rw, rb = dwp0.clone(), db0.clone()
+    fb.conv2d_wgrad_packed(x0, x1, dy, R, rw, rb)
+    gw, gb = g(dwp0), g(db0)
+    be.conv2d_wgrad_packed(g(x0), g(x1), g(dy), R, gw, gb, impl=CONV_TC if impl == "tc" else CONV_SIMT)
+    torch.cuda.synchronize()
+    assert rel_err(gw, rw) < 5e-6 and rel_err(gb, rb) < 5e-6
+    dw0 = torch.randn(N, c0 + c1, R, R)
+    ro = dw0.clone()
+    fb.wgrad_unpack(rw, ro)
+    go = g(dw0)
+    be.wgrad_unpack(gw, go)
+    torch.cuda.synchronize()
+    assert rel_err(go, ro) < 5e-6
+
+
 def test_gru_gate_kernels(be, fb):
     B, H, W, Cn = 3, 16, 16, 64
     torch.manual_seed(7)
