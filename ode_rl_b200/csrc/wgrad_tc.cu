@@ -100,7 +100,6 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant_
     const uint32_t bar_stage_empty = bars + 32;    // [2]
     const uint32_t bar_acc = bars + 48;
     const uint32_t tmem_slot = bars + 56;
-    const uint32_t db_scratch = bars + 64;         // 128 x 8 floats
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -233,10 +232,13 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant_
             mbar_arrive(bar_split_full + 8 * st);
         }
 
+        // ---- epilogue: dwp[tap][c][n] += D[c][n] + D[64 + c][n]
+        mbar_wait(bar_acc, 0u);             // every MMA has completed: the stage buffers are free as well
+        tc_fence_after_sync();
         if (do_db) {
             // thread tid always touched physical 16-byte chunk (tid & 7) of rows with (row & 3) == ((tid >> 3) & 3):
             // logical 32-byte group = physical group ^ (row & 3)  (SWIZZLE_128B_BASE32B)
-            float* sc = reinterpret_cast<float*>(smem_raw + (db_scratch - smem_u32(smem_raw)));
+            float* sc = reinterpret_cast<float*>(smem_raw + (base - smem_u32(smem_raw)));   // stage 0 is idle now
             sc[tid * 8 + 0] = db0.x; sc[tid * 8 + 1] = db0.y; sc[tid * 8 + 2] = db0.z; sc[tid * 8 + 3] = db0.w;
             sc[tid * 8 + 4] = db1.x; sc[tid * 8 + 5] = db1.y; sc[tid * 8 + 6] = db1.z; sc[tid * 8 + 7] = db1.w;
             named_bar_sync(1, 128);
@@ -253,9 +255,6 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant_
             }
         }
 
-        // ---- epilogue: dwp[tap][c][n] += D[c][n] + D[64 + c][n]
-        mbar_wait(bar_acc, 0u);
-        tc_fence_after_sync();
         const int q = warp & 3;
         const int row = q * 32 + lane;
         const int c = cg * 64 + (row & 63);
@@ -353,7 +352,7 @@ int launch_wgrad_tc(const float* x0, int ld0, int c0, const float* x1, int ld1, 
     const int units = g.TG * g.CG * g.NB;
     g.PS = std::max(1, std::min(g.ntiles, kSMs / units));
     g.dwp = dwp; g.db = db;
-    const int smem = 1024 + 2 * (4 * g.xplane + 4 * kWgDyPlane) + 64 + 128 * 8 * 4;
+    const int smem = 1024 + 2 * (4 * g.xplane + 4 * kWgDyPlane) + 64;
     if (smem > 232448) return fail(ODEX_E_UNSUPPORTED, "wgrad(tc): needs %d bytes of shared memory", smem);
 
     CUtensorMap tmX0, tmX1, tmDY;
