@@ -1,6 +1,7 @@
 // Host side of the tcgen05 implicit-GEMM convolution (kernel in conv_tc.cuh): geometry, TMA tensor maps, launch.
 #include "conv_tc.cuh"
 
+#include <cstdlib>
 #include <mutex>
 
 #include "common.cuh"
@@ -114,7 +115,13 @@ static int launch_tc(const odex_conv_desc* d, cudaStream_t s) {
     return launched("conv_tc_kernel");
 }
 
+bool conv_tc2_supported(const odex_conv_desc* d);
+int launch_conv_tc2(const odex_conv_desc* d, cudaStream_t s);
+
 int launch_conv_tc(const odex_conv_desc* d, cudaStream_t s) {
+    // v2 (tap shift = descriptor start address, halo split once) wherever all input channels fit in shared memory
+    static const bool no_v2 = getenv("ODEX_CONV_TC_V1") != nullptr;
+    if (!no_v2 && conv_tc2_supported(d)) return launch_conv_tc2(d, s);
     if (!conv_tc_supported(d)) return fail(ODEX_E_UNSUPPORTED, "conv(tc): shape not supported (N=%d R=%d c0=%d c1=%d HxW=%dx%d)", d->N, d->R, d->c0, d->c1, d->H, d->W);
     if (d->N == 64) return launch_tc<64>(d, s);
     return launch_tc<128>(d, s);

@@ -22,6 +22,7 @@
 #include <cuda.h>
 
 #include <algorithm>
+#include <cstdlib>
 #include <mutex>
 
 #include "common.cuh"
@@ -44,6 +45,8 @@ struct WgradTcGeom {
     int ntiles;         // B * (H / 4) * (W / 16)
     float* dwp;         // [R*R][Ctot][N], accumulated
     float* db;          // [N] or nullptr, accumulated
+    int trunc_hi;       // 1: hi operand = raw word (hardware truncation), see split4
+    long long* dbg;     // diagnostic: per-role cycle counters of CTA 0 (ODEX_WGRAD_DEBUG=1), else nullptr
 };
 
 // MN-major SWIZZLE_128B_BASE32B descriptor: LBO = stride between 32-element groups along M/N, SBO = stride between
@@ -66,7 +69,9 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
-__device__ __forceinline__ void split4(uint32_t src, uint32_t dst_hi, uint32_t dst_lo, float4& raw) {
+// trunc != 0: leave the raw fp32 word as the "hi" operand -- the tensor core reads only the top 19 bits of a tf32
+// operand, i.e. hi = trunc(x) -- and store lo = tf32(x - trunc(x)); saves one shared-memory store per element.
+__device__ __forceinline__ void split4(uint32_t src, uint32_t dst_hi, uint32_t dst_lo, float4& raw, int trunc = 0) {
     uint32_t a, b, c, d;
     asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "r"(src));
     raw = make_float4(__uint_as_float(a), __uint_as_float(b), __uint_as_float(c), __uint_as_float(d));
@@ -74,11 +79,44 @@ __device__ __forceinline__ void split4(uint32_t src, uint32_t dst_hi, uint32_t d
     uint32_t hi[4], lo[4];
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
-        hi[e] = tf32_rna_bits(x[e]);
+        hi[e] = trunc ? (x[e] & 0xFFFFE000u) : tf32_rna_bits(x[e]);
         lo[e] = tf32_rna_bits(__float_as_uint(__uint_as_float(x[e]) - __uint_as_float(hi[e])));
     }
-    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(dst_hi), "r"(hi[0]), "r"(hi[1]), "r"(hi[2]), "r"(hi[3]) : "memory");
+    if (!trunc)
+        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(dst_hi), "r"(hi[0]), "r"(hi[1]), "r"(hi[2]), "r"(hi[3]) : "memory");
     asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(dst_lo), "r"(lo[0]), "r"(lo[1]), "r"(lo[2]), "r"(lo[3]) : "memory");
+}
+
+// Software-pipelined form: NB independent 16-byte loads are issued before the first one is consumed (the inline-asm
+// loads / stores are volatile, so the compiler keeps them in program order: without this the loop is one
+// load-use latency per 16 bytes and the split, not the tensor core, bounds the kernel).
+template <int NB>
+__device__ __forceinline__ void split_batch(const uint32_t (&src)[NB], const bool (&ok)[NB], uint32_t lo_delta, int trunc,
+                                            float4& sum) {
+    uint32_t x[NB][4];
+#pragma unroll
+    for (int b = 0; b < NB; ++b) {
+        x[b][0] = x[b][1] = x[b][2] = x[b][3] = 0u;
+        if (ok[b])
+            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(x[b][0]), "=r"(x[b][1]), "=r"(x[b][2]), "=r"(x[b][3]) : "r"(src[b]));
+    }
+#pragma unroll
+    for (int b = 0; b < NB; ++b) {
+        uint32_t hi[4], lo[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            hi[e] = trunc ? (x[b][e] & 0xFFFFE000u) : tf32_rna_bits(x[b][e]);
+            lo[e] = tf32_rna_bits(__float_as_uint(__uint_as_float(x[b][e]) - __uint_as_float(hi[e])));
+        }
+        sum.x += __uint_as_float(x[b][0]); sum.y += __uint_as_float(x[b][1]);
+        sum.z += __uint_as_float(x[b][2]); sum.w += __uint_as_float(x[b][3]);
+        if (ok[b]) {
+            if (!trunc)
+                asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(src[b]), "r"(hi[0]), "r"(hi[1]), "r"(hi[2]), "r"(hi[3]) : "memory");
+            asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(src[b] + lo_delta), "r"(lo[0]), "r"(lo[1]), "r"(lo[2]), "r"(lo[3]) : "memory");
+        }
+    }
 }
 
 __device__ __forceinline__ void tile_coords(const WgradTcGeom& g, int t, int& img, int& y0, int& x0) {
@@ -88,6 +126,7 @@ __device__ __forceinline__ void tile_coords(const WgradTcGeom& g, int t, int& im
     img = t / (tx * ty);
 }
 
+template <int R>
 __global__ void __launch_bounds__(192, 1)
 wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant__ CUtensorMap tmX1,
                 const __grid_constant__ CUtensorMap tmDY, const WgradTcGeom g) {
@@ -110,13 +149,17 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant_
     const int nb = j % g.NB; j /= g.NB;
     const int cg = j % g.CG; j /= g.CG;
     const int tg = j;
-    const int taps = g.R * g.R;
+    constexpr int taps = R * R;
     const int tap0 = tg * g.taps_per_group;
     const int ntap = min(g.taps_per_group, taps - tap0);
-    const int pad = g.R >> 1;
+    constexpr int pad = R >> 1;
     const int hrows = (kWgTH + 2 * pad) * g.P;     // pixel slots of one halo plane
+    // R <= 3: one N = 128 MMA per K atom with B = [dy_hi | dy_lo] (8 KB of operand reads instead of 2 x 6 KB -- the
+    // kernel is bound by shared-memory bandwidth), 128 accumulator columns per tap; R = 5: two N = 64 MMAs into 64 columns
+    constexpr bool kWide = R <= 3;
+    constexpr int DC = kWide ? 128 : 64;
     uint32_t tmem_cols = 32;
-    while (tmem_cols < static_cast<uint32_t>(ntap * 64)) tmem_cols <<= 1;
+    while (tmem_cols < static_cast<uint32_t>(ntap * DC)) tmem_cols <<= 1;
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < 2; ++i) {
@@ -151,10 +194,13 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant_
             const int cx = second ? cabs - g.c0 : cabs;
             const uint32_t tx_bytes = 2u * static_cast<uint32_t>(hrows) * 128u + 2u * kWgDyPlane;
             int it = 0;
+            long long w_empty = 0, t_begin = clock64();
             for (int t = ps; t < g.ntiles; t += g.PS, ++it) {
                 const int st = it & 1;
                 const uint32_t use = static_cast<uint32_t>(it >> 1);
+                const long long c0_ = clock64();
                 mbar_wait(bar_stage_empty + 8 * st, (use & 1u) ^ 1u);
+                w_empty += clock64() - c0_;
                 int img, y0, x0;
                 tile_coords(g, t, img, y0, x0);
                 const uint32_t xs = base + st * stage_bytes;
@@ -166,40 +212,49 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant_
                 tma_load_4d(ds, &tmDY, bar, nb * 64, x0, y0, img);
                 tma_load_4d(ds + kWgDyPlane, &tmDY, bar, nb * 64 + 32, x0, y0, img);
             }
+            if (g.dbg && blockIdx.x == 0) { g.dbg[0] = w_empty; g.dbg[1] = clock64() - t_begin; g.dbg[2] = it; }
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
         if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_tf32(128, 64, 1, 1);
+            constexpr uint32_t idesc = umma_idesc_tf32(128, DC, 1, 1);
+            constexpr int P = kWgTW + 2 * (R / 2);
+            // descriptor words: hi = SBO 512 | version 1 | layout SWIZZLE_128B_BASE32B; lo = LBO << 16 | start >> 4
+            const uint32_t d_hi = static_cast<uint32_t>(umma_desc_mn32(0, 0) >> 32);
+            const uint32_t a_lbo = ((static_cast<uint32_t>(g.xplane) >> 4) & 0x3FFFu) << 16;
+            constexpr uint32_t b_lbo = ((static_cast<uint32_t>(kWgDyPlane) >> 4) & 0x3FFFu) << 16;
             int it = 0;
+            long long w_split = 0, t_begin = clock64();
             for (int t = ps; t < g.ntiles; t += g.PS, ++it) {
                 const int st = it & 1;
                 const uint32_t use = static_cast<uint32_t>(it >> 1);
+                const long long c0_ = clock64();
                 mbar_wait(bar_split_full + 8 * st, use & 1u);
+                w_split += clock64() - c0_;
                 tc_fence_after_sync();
                 const uint32_t xs = base + st * stage_bytes;
                 const uint32_t ds = xs + 4u * g.xplane;
+                const uint32_t b_lo0 = b_lbo | (ds >> 4);
+                int r = tap0 / R, s = tap0 - r * R;
                 for (int tl = 0; tl < ntap; ++tl) {
-                    const int tap = tap0 + tl;
-                    const int r = tap / g.R, s = tap - r * g.R;
-                    const uint32_t d_tmem = tmem_base + tl * 64;
+                    const uint32_t d_tmem = tmem_base + tl * DC;
+                    const uint32_t a_lo0 = a_lbo | ((xs >> 4) + static_cast<uint32_t>(r * P + s) * 8u);
 #pragma unroll
                     for (int ty = 0; ty < kWgTH; ++ty) {
 #pragma unroll
                         for (int h = 0; h < 2; ++h) {
-                            const uint32_t a_addr = xs + static_cast<uint32_t>((ty + r) * g.P + s + 8 * h) * 128u;
-                            const uint32_t b_addr = ds + static_cast<uint32_t>(ty * kWgTW + 8 * h) * 128u;
-                            const uint64_t ad = umma_desc_mn32(a_addr, g.xplane);
-                            const uint64_t bh = umma_desc_mn32(b_addr, kWgDyPlane);
-                            const uint64_t bl = umma_desc_mn32(b_addr + 2u * kWgDyPlane, kWgDyPlane);
-                            umma_tf32_ss(d_tmem, ad, bh, idesc, (it | ty | h) != 0);
-                            umma_tf32_ss(d_tmem, ad, bl, idesc, 1u);
+                            const uint32_t a_lo = a_lo0 + static_cast<uint32_t>(ty * P + 8 * h) * 8u;
+                            const uint32_t b_lo = b_lo0 + static_cast<uint32_t>(ty * kWgTW + 8 * h) * 8u;
+                            umma_tf32_ss_w(d_tmem, a_lo, d_hi, b_lo, d_hi, idesc, (it | ty | h) != 0);
+                            if (!kWide) umma_tf32_ss_w(d_tmem, a_lo, d_hi, b_lo + (2u * kWgDyPlane >> 4), d_hi, idesc, 1u);
                         }
                     }
+                    if (++s == R) { s = 0; ++r; }
                 }
                 umma_commit(bar_stage_empty + 8 * st);
             }
             umma_commit(bar_acc);
+            if (g.dbg && blockIdx.x == 0) { g.dbg[3] = w_split; g.dbg[4] = clock64() - t_begin; }
         }
     } else {
         // ===================== hi/lo split (+ bias-gradient sums), then epilogue =====================
@@ -208,33 +263,52 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant_
         float4 db0 = make_float4(0.f, 0.f, 0.f, 0.f), db1 = db0;
         const int nf4x = hrows * 8;
         int it = 0;
+        long long w_raw = 0, t_begin = clock64();
         for (int t = ps; t < g.ntiles; t += g.PS, ++it) {
             const int st = it & 1;
             const uint32_t use = static_cast<uint32_t>(it >> 1);
+            const long long c0_ = clock64();
             mbar_wait(bar_raw_full + 8 * st, use & 1u);
+            w_raw += clock64() - c0_;
             const uint32_t xs = base + st * stage_bytes;
             const uint32_t ds = xs + 4u * g.xplane;
-            float4 raw;
-            for (int i = tid; i < nf4x; i += 128) {
-                const uint32_t a = xs + static_cast<uint32_t>(i) * 16u;
-                split4(a, a, a + 2u * g.xplane, raw);
-                split4(a + g.xplane, a + g.xplane, a + 3u * g.xplane, raw);
-            }
+            {
+                // X halo planes: items (plane, i) with i = tid + 128 * k, in batches of 4 loads in flight
+                constexpr int kPer = (((kWgTH + 2 * pad) * (kWgTW + 2 * pad) * 8) + 127) / 128;   // per plane, per thread
+                float4 dummy = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-            for (int k = 0; k < (kWgDyPlane / 16) / 128; ++k) {
-                const uint32_t a = ds + static_cast<uint32_t>(tid + 128 * k) * 16u;
-                split4(a, a, a + 2u * kWgDyPlane, raw);
-                db0.x += raw.x; db0.y += raw.y; db0.z += raw.z; db0.w += raw.w;
-                split4(a + kWgDyPlane, a + kWgDyPlane, a + 3u * kWgDyPlane, raw);
-                db1.x += raw.x; db1.y += raw.y; db1.z += raw.z; db1.w += raw.w;
+                for (int k0 = 0; k0 < 2 * kPer; k0 += 4) {
+                    uint32_t src[4]; bool ok[4];
+#pragma unroll
+                    for (int b = 0; b < 4; ++b) {
+                        const int item = k0 + b;
+                        const int i = tid + 128 * (item >> 1);
+                        ok[b] = item < 2 * kPer && i < nf4x;
+                        src[b] = xs + static_cast<uint32_t>(item & 1) * g.xplane + static_cast<uint32_t>(i) * 16u;
+                    }
+                    split_batch<4>(src, ok, 2u * g.xplane, g.trunc_hi, dummy);
+                }
+                // dy planes (sums of the raw values feed the bias gradient)
+#pragma unroll
+                for (int pl = 0; pl < 2; ++pl) {
+                    uint32_t src[4]; bool ok[4];
+#pragma unroll
+                    for (int b = 0; b < 4; ++b) {
+                        ok[b] = true;
+                        src[b] = ds + static_cast<uint32_t>(pl) * kWgDyPlane + static_cast<uint32_t>(tid + 128 * b) * 16u;
+                    }
+                    split_batch<4>(src, ok, 2u * kWgDyPlane, g.trunc_hi, pl == 0 ? db0 : db1);
+                }
             }
             fence_proxy_async_smem();
             mbar_arrive(bar_split_full + 8 * st);
         }
 
         // ---- epilogue: dwp[tap][c][n] += D[c][n] + D[64 + c][n]
+        const long long t_loop = clock64() - t_begin;
         mbar_wait(bar_acc, 0u);             // every MMA has completed: the stage buffers are free as well
         tc_fence_after_sync();
+        const long long t_acc = clock64() - t_begin;
         if (do_db) {
             // thread tid always touched physical 16-byte chunk (tid & 7) of rows with (row & 3) == ((tid >> 3) & 3):
             // logical 32-byte group = physical group ^ (row & 3)  (SWIZZLE_128B_BASE32B)
@@ -255,24 +329,50 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant_
             }
         }
 
+        // D rows 0-63 = Xhi * [dyhi | dylo], rows 64-127 = Xlo * [...]: dw[c][n] is the sum over both row halves (and, in
+        // wide mode, both column halves).  The lo-row warps hand their sums over through shared memory (the stage
+        // buffers are idle), so each CTA issues 64 x 16 vector reductions per tap.
         const int q = warp & 3;
         const int row = q * 32 + lane;
-        const int c = cg * 64 + (row & 63);
+        const int cl = row & 63;
         const uint32_t lane_addr = static_cast<uint32_t>(q * 32) << 16;
         for (int tl = 0; tl < ntap; ++tl) {
-            float* dst = g.dwp + (static_cast<long>(tap0 + tl) * g.Ctot + c) * g.N + nb * 64;
-#pragma unroll 1
+            float acc[64];
+#pragma unroll
             for (int c0 = 0; c0 < 64; c0 += 32) {
                 uint32_t v[32];
-                tmem_ld32(tmem_base + lane_addr + tl * 64 + c0, v);
+                tmem_ld32(tmem_base + lane_addr + tl * DC + c0, v);
                 tmem_ld_wait();
 #pragma unroll
-                for (int k = 0; k < 8; ++k)
-                    red_add_v4(dst + c0 + 4 * k, __uint_as_float(v[4 * k]), __uint_as_float(v[4 * k + 1]),
-                               __uint_as_float(v[4 * k + 2]), __uint_as_float(v[4 * k + 3]));
+                for (int k = 0; k < 32; ++k) acc[c0 + k] = __uint_as_float(v[k]);
+                if (kWide) {
+                    tmem_ld32(tmem_base + lane_addr + tl * DC + 64 + c0, v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int k = 0; k < 32; ++k) acc[c0 + k] += __uint_as_float(v[k]);
+                }
+            }
+            const uint32_t sc = base + 16384u + static_cast<uint32_t>(tl & 1) * 16384u + static_cast<uint32_t>(cl) * 256u;
+            if (row >= 64) {
+#pragma unroll
+                for (int k = 0; k < 16; ++k)
+                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(sc + ((static_cast<uint32_t>(k) ^ (cl & 15)) << 4)),
+                                 "f"(acc[4 * k]), "f"(acc[4 * k + 1]), "f"(acc[4 * k + 2]), "f"(acc[4 * k + 3]) : "memory");
+            }
+            named_bar_sync(1, 128);
+            if (row < 64) {
+                float* dst = g.dwp + (static_cast<long>(tap0 + tl) * g.Ctot + cg * 64 + cl) * g.N + nb * 64;
+#pragma unroll
+                for (int k = 0; k < 16; ++k) {
+                    float4 o;
+                    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(o.x), "=f"(o.y), "=f"(o.z), "=f"(o.w)
+                                 : "r"(sc + ((static_cast<uint32_t>(k) ^ (cl & 15)) << 4)));
+                    red_add_v4(dst + 4 * k, acc[4 * k] + o.x, acc[4 * k + 1] + o.y, acc[4 * k + 2] + o.z, acc[4 * k + 3] + o.w);
+                }
             }
         }
         tc_fence_before_sync();
+        if (g.dbg && blockIdx.x == 0 && tid == 0) { g.dbg[5] = w_raw; g.dbg[6] = t_loop; g.dbg[7] = t_acc; g.dbg[8] = clock64() - t_begin; }
     }
     __syncthreads();
     if (warp == 1) {
@@ -352,6 +452,16 @@ int launch_wgrad_tc(const float* x0, int ld0, int c0, const float* x1, int ld1, 
     const int units = g.TG * g.CG * g.NB;
     g.PS = std::max(1, std::min(g.ntiles, kSMs / units));
     g.dwp = dwp; g.db = db;
+    static const int trunc_hi = getenv("ODEX_WGRAD_TRUNC") ? atoi(getenv("ODEX_WGRAD_TRUNC")) : 1;
+    g.trunc_hi = trunc_hi;
+    g.dbg = nullptr;
+    static const bool debug = getenv("ODEX_WGRAD_DEBUG") != nullptr;
+    if (debug) {
+        static long long* dbuf = nullptr;
+        if (!dbuf) cudaMalloc(&dbuf, 16 * sizeof(long long));
+        cudaMemsetAsync(dbuf, 0, 16 * sizeof(long long), s);
+        g.dbg = dbuf;
+    }
     const int smem = 1024 + 2 * (4 * g.xplane + 4 * kWgDyPlane) + 64;
     if (smem > 232448) return fail(ODEX_E_UNSUPPORTED, "wgrad(tc): needs %d bytes of shared memory", smem);
 
@@ -364,13 +474,24 @@ int launch_wgrad_tc(const float* x0, int ld0, int c0, const float* x1, int ld1, 
     }
     if (int rc = make_map32(&tmDY, dy, ldy, N, B, H, W, kWgTW, kWgTH)) return rc;
 
+    auto kern = R == 1 ? wgrad_tc_kernel<1> : (R == 3 ? wgrad_tc_kernel<3> : wgrad_tc_kernel<5>);
     static std::once_flag once;
     static cudaError_t attr_err = cudaSuccess;
     std::call_once(once, [&] {
-        attr_err = cudaFuncSetAttribute(wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+        attr_err = cudaFuncSetAttribute(wgrad_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+        if (attr_err == cudaSuccess) attr_err = cudaFuncSetAttribute(wgrad_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+        if (attr_err == cudaSuccess) attr_err = cudaFuncSetAttribute(wgrad_tc_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
     });
     if (attr_err != cudaSuccess) return fail(-static_cast<int>(attr_err), "wgrad(tc): cudaFuncSetAttribute: %s", cudaGetErrorString(attr_err));
-    wgrad_tc_kernel<<<units * g.PS, 192, smem, s>>>(tmX0, tmX1, tmDY, g);
+    kern<<<units * g.PS, 192, smem, s>>>(tmX0, tmX1, tmDY, g);
+    if (debug) {
+        long long h[16];
+        cudaStreamSynchronize(s);
+        cudaMemcpy(h, g.dbg, sizeof(h), cudaMemcpyDeviceToHost);
+        fprintf(stderr, "[wgrad_tc R=%d C=%d N=%d B=%d grid=%d tiles/cta=%lld] producer: wait_empty=%lld total=%lld | mma: wait_split=%lld "
+                "total=%lld | split: wait_raw=%lld loop=%lld until_acc=%lld end=%lld (cycles)\n", R, g.Ctot, N, B, units * g.PS, h[2],
+                h[0], h[1], h[3], h[4], h[5], h[6], h[7], h[8]);
+    }
     return launched("wgrad_tc_kernel");
 }
 

@@ -1,0 +1,15 @@
+"""Role-level cycle counters of wgrad_tc_kernel (CTA 0) at the bench shapes.  ODEX_WGRAD_DEBUG=1 python tools/wgrad_debug.py"""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from ode_rl_b200 import kernels as K
+be = K.Backend()
+for (B, c0, c1, N, R) in [(128, 64, 0, 64, 3), (128, 64, 64, 128, 5), (128, 64, 64, 64, 5), (512, 64, 0, 64, 3)]:
+    x0 = torch.randn(B, 16, 16, c0, device="cuda")
+    x1 = torch.randn(B, 16, 16, c1, device="cuda") if c1 else None
+    dy = torch.randn(B, 16, 16, N, device="cuda")
+    dwp = torch.zeros(R * R, c0 + c1, N, device="cuda")
+    db = torch.zeros(N, device="cuda")
+    for _ in range(3):
+        be.conv2d_wgrad_packed(x0, x1, dy, R, dwp, db)
+    torch.cuda.synchronize()
