@@ -241,45 +241,81 @@ def main():
     e2e_value = world * B * T_OUT * args.steps / sec_e
     clk = clocks.summary(w0, w1) if clocks else None
 
-    # ---- roofline of the dominant kernel (tcgen05 3x3 conv 64->64): per-launch CUDA events over one extra step
+    # ---- roofline of the dominant kernel family (tcgen05 3x3 conv 64->64: forward and dgrad of every f-eval).
+    # The launch is repeated from C between two CUDA events on the launching stream (a Python loop over ctypes is slower
+    # than the kernel); inputs are one state plane (B x 64 KiB), resident in L2 as they are inside the step, where every
+    # layer reads what the previous kernel just wrote.
     be = K.backend()
-    recs = []
-    orig = be.conv2d
-
-    def conv2d_timed(x0, x1, w_simt, w_tc, N, R, *a, **kw):
-        hot = (R == 3 and N == 64 and x1 is None and x0.shape[3] == 64 and w_tc is not None)
-        if not hot:
-            return orig(x0, x1, w_simt, w_tc, N, R, *a, **kw)
-        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        s.record()
-        r = orig(x0, x1, w_simt, w_tc, N, R, *a, **kw)
-        e.record()
-        recs.append((s, e))
-        return r
-
-    be.conv2d = conv2d_timed
-    try:
-        step(x, y)
-        torch.cuda.synchronize()
-    finally:
-        be.conv2d = orig
-    roof = None
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except Exception:
         pass
-    if recs:
-        ms = [s.elapsed_time(e) for s, e in recs]
-        avg = float(np.mean(ms)) / 1e3
+    roof = None
+    rk = None
+    if rank == 0:
+        xs = torch.randn(B, 16, 16, 64, device=dev)
+        ws = torch.randn(64, 64, 3, 3, device=dev) * 0.05
+        bs = torch.randn(64, device=dev)
+        os_ = torch.empty(B, 16, 16, 64, device=dev)
+        wt = be.pack_weights(ws, False, True)
+        reps = 200
+        be.conv2d(xs, None, None, wt, 64, 3, bs, K.ACT_RELU, os_, impl=K.CONV_TC, repeat=20)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        be.conv2d(xs, None, None, wt, 64, 3, bs, K.ACT_RELU, os_, impl=K.CONV_TC, repeat=reps)
+        e1.record()
+        torch.cuda.synchronize()
+        avg = e0.elapsed_time(e1) / 1e3 / reps
         ach = CONV3_FLOPS * B / avg / 1e12
         peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
-        roof = {"bound": "tensor", "kernel": "conv_tc_kernel<64> (3x3, 64->64, 3xTF32)", "achieved": ach, "peak": peak,
-                "unit": "TFLOP/s", "frac": ach / peak, "traffic": None,
+        roof = {"bound": "tensor", "kernel": "conv_tc2_kernel<64,3> (3x3, 64->64, 3xTF32, tcgen05 kind::tf32)", "achieved": ach,
+                "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": None,
                 "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (of measured)" if peaks else "fallback 1.4 PF (of fallback)",
-                "note": "achieved counts algorithmic FLOPs once; the kernel issues 3 TF32 MMAs per useful one and the TF32 "
-                        "rate is half the bf16 rate, so frac*6 is the share of tensor issue slots used",
-                "launches_timed": len(ms), "avg_launch_us": avg * 1e6}
+                "note": "achieved counts algorithmic FLOPs once (2*M*N*K); the kernel issues 3 TF32 MMAs per useful one and TF32 runs "
+                        "at half the bf16 rate, so frac*6 is the share of tensor issue slots used; %d launches back to back, "
+                        "batch %d" % (reps, B),
+                "launches_timed": reps, "avg_launch_us": avg * 1e6}
+
+        # ---- RK-stage GB/s (the second half of BASELINE's metric): the fused stage-combination / error-norm / dense-output
+        # kernels at the dopri5 configuration's size (B=512: 33.5 MB planes, 10 planes = 335 MB > the 126 MB L2).
+        nB = 512
+        planes = [torch.randn(nB, 16, 16, 64, device=dev) for _ in range(9)]
+        outp = torch.empty_like(planes[0])
+        n_el = planes[0].numel()
+        dt_dev = torch.tensor([0.05], dtype=torch.float64, device=dev)
+        from ode_rl_b200.solver import DP_BETA
+
+        def rk_pass():
+            # the six stage combinations of one dopri5 attempt (26 reads + 6 writes of a plane) ...
+            for s_ in range(6):
+                coefs = [c for c in DP_BETA[s_] if c != 0.0]
+                ins = [planes[0]] + [planes[1 + j] for j, c in enumerate(DP_BETA[s_]) if c != 0.0]
+                be.lincomb(outp, ins, [1.0] + coefs, dtmask=(1 << len(ins)) - 2, dt_dev=dt_dev)
+            # ... and the rk4 (3/8 rule) combinations of one step (14 reads + 4 writes)
+            be.lincomb(outp, planes[:2], [1.0, 1.0 / 3.0], dtmask=2, dt_dev=dt_dev)
+            be.lincomb(outp, planes[:3], [1.0, -1.0 / 3.0, 1.0], dtmask=6, dt_dev=dt_dev)
+            be.lincomb(outp, planes[:4], [1.0, 1.0, -1.0, 1.0], dtmask=14, dt_dev=dt_dev)
+            be.lincomb(outp, planes[:5], [1.0, 0.125, 0.375, 0.375, 0.125], dtmask=30, dt_dev=dt_dev)
+
+        rk_bytes = (26 + 6 + 14 + 4) * n_el * 4
+        for _ in range(3):
+            rk_pass()
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(10):
+            rk_pass()
+        e1.record()
+        torch.cuda.synchronize()
+        rk_s = e0.elapsed_time(e1) / 1e3 / 10
+        hbm = float(peaks.get("hbm_gbs", 6650.0))
+        rk = {"bound": "hbm", "kernel": "lincomb_kernel<NIN> (dopri5 stage combines of one attempt + rk4 3/8-rule combines of one step)",
+              "achieved": rk_bytes / rk_s / 1e9, "peak": hbm, "unit": "GB/s", "frac": rk_bytes / rk_s / 1e9 / hbm,
+              "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
+              "bytes_per_pass": rk_bytes, "planes_mb": n_el * 4 / 1e6, "batch": nB,
+              "note": "algorithmic bytes: every distinct operand plane read once, every result written once (SURVEY.md 8d)"}
+        del planes, outp
 
     if rank == 0:
         cpu = None
@@ -292,13 +328,15 @@ def main():
                 "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": sec / args.steps * 1e3,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32 (3xTF32 tensor-core convs, fp32 accumulate)",
                 "data": "synthetic",
-                "config": {"workload": "BASELINE configs[1]: ODEConvGRU forward+backward+Adam, %s fixed-step, batch %d per GPU, "
-                                       "10 in / 10 out 64x64x1" % (args.method, B),
+                "config": {"workload": "BASELINE configs[%s]: ODEConvGRU forward+backward+Adam, %s, batch %d per GPU, "
+                                       "10 in / 10 out 64x64x1" % ("1" if args.method != "dopri5" else "2 (as a training step)",
+                                                                   args.method + (" fixed-step" if args.method != "dopri5" else
+                                                                                  " adaptive rtol=1e-3 atol=1e-4, device-resident controller"), B),
                            "global_batch": B * world, "parallelism": "batch-sharded dp%d, NCCL flat-bucket gradient allreduce" % world,
                            "l2": "no explicit flush: the per-step working set (saved activations ~2 GB) is >> the 126 MB L2"},
                 "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": int(xh.numel() * 4 + yh.numel() * 4),
                         "d2h_bytes_per_step": 4, "ms_per_step": sec_e / args.steps * 1e3},
-                "gpu_launches": int(launches), "clocks": clk, "roofline": roof, "cpu_baseline": cpu}
+                "gpu_launches": int(launches), "clocks": clk, "roofline": roof, "rk_stage": rk, "cpu_baseline": cpu}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

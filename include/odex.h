@@ -86,6 +86,8 @@ typedef struct odex_conv_desc {
     int impl;                               /* ODEX_CONV_* */
 } odex_conv_desc;
 int odex_conv2d(const odex_conv_desc* d, odex_stream_t s);
+/* Measurement helper (bench.py): the same launch enqueued `reps` times back to back from C. */
+int odex_conv2d_repeat(const odex_conv_desc* d, int reps, odex_stream_t s);
 
 /* Weight / bias gradient of the same convolution: dw[n,c,r,s] += sum_p dy[p,n] * X[p + (r,s) - pad, c]
  * (OIHW, torch layout, ACCUMULATED into dw) and db[n] += sum_p dy[p,n] (db nullable).

@@ -75,6 +75,7 @@ SIGNATURES = {
     "odex_packed_weight_floats": (_sz, [_i, _i, _i, _i]),
     "odex_pack_weights": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _vp]),
     "odex_conv2d": (_i, [C.POINTER(ConvDesc), _vp]),
+    "odex_conv2d_repeat": (_i, [C.POINTER(ConvDesc), _i, _vp]),
     "odex_conv2d_wgrad": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
     "odex_conv2d_wgrad_packed": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
     "odex_wgrad_unpack": (_i, [_vp, _i, _i, _i, _vp, _vp]),

@@ -37,3 +37,11 @@ extern "C" int odex_conv2d(const odex_conv_desc* d, odex_stream_t s_) {
         default: return fail(ODEX_E_ARG, "conv2d: unknown impl %d", d->impl);
     }
 }
+
+// Measurement helper: enqueue the same convolution `reps` times from C (a Python loop over ctypes is slower than the
+// kernel, so events around it would time the host).  bench.py brackets this with CUDA events on the same stream.
+extern "C" int odex_conv2d_repeat(const odex_conv_desc* d, int reps, odex_stream_t s) {
+    for (int i = 0; i < reps; ++i)
+        if (int rc = odex_conv2d(d, s)) return rc;
+    return 0;
+}

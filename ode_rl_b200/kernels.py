@@ -101,7 +101,7 @@ class Backend:
                w_tc: Optional[torch.Tensor], N: int, R: int, bias: Optional[torch.Tensor], act: int,
                out: torch.Tensor, dact: Optional[torch.Tensor] = None, dact_kind: int = 0,
                res: Optional[torch.Tensor] = None, alpha: float = 1.0, alpha_dev: Optional[torch.Tensor] = None,
-               skip: Optional[torch.Tensor] = None, impl: int = CONV_AUTO) -> torch.Tensor:
+               skip: Optional[torch.Tensor] = None, impl: int = CONV_AUTO, repeat: int = 1) -> torch.Tensor:
         """odex_conv2d: out = res + alpha * (act(conv(cat(x0,x1)) + bias) * act'(dact))."""
         self.require(x0)
         d = _lib.ConvDesc()
@@ -127,7 +127,10 @@ class Backend:
         d.out, d.ldo = _rows(out)
         d.skip = _ptr(skip)
         d.impl = impl
-        _lib.check(self.lib.odex_conv2d(C.byref(d), _stream()), "odex_conv2d")
+        if repeat > 1:
+            _lib.check(self.lib.odex_conv2d_repeat(C.byref(d), int(repeat), _stream()), "odex_conv2d_repeat")
+        else:
+            _lib.check(self.lib.odex_conv2d(C.byref(d), _stream()), "odex_conv2d")
         return out
 
     def conv2d_wgrad(self, x0: torch.Tensor, x1: Optional[torch.Tensor], dy: torch.Tensor, R: int,
