@@ -239,6 +239,7 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
         }
         tc_fence_before_sync();
         asm volatile("bar.sync 1, 128;" ::: "memory");
+        const long long t_ph1 = clock64() - t0_;
 
         // Phase 2: coalesced epilogue.  Consecutive threads take consecutive 16-byte chunks of a pixel row, so the
         // residual / saved-activation loads and the output stores are full 128-byte lines.
@@ -281,7 +282,7 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
             *reinterpret_cast<float4*>(ep.out + pix * ep.ldo + 4 * jch) = make_float4(v[0], v[1], v[2], v[3]);
         }
         tc_fence_before_sync();
-        if (g.dbg && blockIdx.x == 0 && tid == 0) { g.dbg[5] = w_raw; g.dbg[6] = t_split; g.dbg[7] = t_acc; g.dbg[8] = clock64() - t0_; }
+        if (g.dbg && blockIdx.x == 0 && tid == 0) { g.dbg[5] = w_raw; g.dbg[6] = t_split; g.dbg[7] = t_acc; g.dbg[8] = clock64() - t0_; g.dbg[9] = t_ph1; }
     }
     __syncthreads();
     if (warp == 1) {
@@ -403,8 +404,8 @@ static int launch_tc2(const odex_conv_desc* d, cudaStream_t s) {
         cudaStreamSynchronize(s);
         cudaMemcpy(h, g.dbg, sizeof(h), cudaMemcpyDeviceToHost);
         fprintf(stderr, "[conv_tc2 R=%d C=%d N=%d B=%d grid=%d SB=%d smem=%d] producer: wait_b_empty=%lld total=%lld | mma: wait_split=%lld "
-                "wait_b_full=%lld total=%lld | split: wait_raw=%lld split_done=%lld acc_done=%lld end=%lld (cycles)\n", R, g.nsrc * g.csrc,
-                N, d->B, grid, g.b_stages, smem, h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7], h[8]);
+                "wait_b_full=%lld total=%lld | split: wait_raw=%lld split_done=%lld acc_done=%lld staged=%lld end=%lld (cycles)\n", R, g.nsrc * g.csrc,
+                N, d->B, grid, g.b_stages, smem, h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7], h[9], h[8]);
     }
     return launched("conv_tc2_kernel");
 }

@@ -16,6 +16,7 @@ def main():
     method = sys.argv[1] if len(sys.argv) > 1 else "rk4"
     B = int(sys.argv[2]) if len(sys.argv) > 2 else 128
     torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cudnn.benchmark = os.environ.get('CUDNN_BENCHMARK', '0') == '1'
     torch.backends.cuda.matmul.allow_tf32 = False
     dev = torch.device("cuda", 0)
     torch.manual_seed(0)
