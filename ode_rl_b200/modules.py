@@ -330,6 +330,23 @@ class ODEConvGRUCell(nn.Module):
         std_z0 = std_z0.abs()
         return mean_z0, std_z0
 
+    def _deltas(self, timesteps, device, order):
+        """Step sizes exactly as the reference forms them (fp64): prev_t, t_i = t[-1]+0.01, t[-1]; then prev_t, t_i =
+        t[i], t[i-1] after visiting frame i (modules/ODEConvGRUCell.py:48,73).  Cached per timesteps tensor: the index
+        tensor below is a pageable host->device copy, which must not happen while a CUDA graph is being captured."""
+        key = (timesteps.data_ptr(), timesteps._version, tuple(timesteps.shape), str(device), order)
+        if getattr(self, "_delta_key", None) == key:
+            return self._delta_val
+        t = len(order)
+        ts = timesteps.detach().to(device=device, dtype=torch.float64)
+        deltas = torch.empty(t, dtype=torch.float64, device=device)
+        deltas[0] = ts[-1] - (ts[-1] + 0.01)
+        if t > 1:
+            idx = torch.tensor(list(order[:-1]), device=device)
+            deltas[1:] = ts[idx - 1] - ts[idx]
+        self._delta_key, self._delta_val = key, deltas
+        return deltas
+
     def run_ode_conv_gru(self, inputs, timesteps, run_backwards=True, mask=None):
         t, b, c, h, w = inputs.size()
         assert (t == len(timesteps)), "Sequence length should be same as time_steps"
@@ -338,14 +355,7 @@ class ODEConvGRUCell(nn.Module):
         order = list(range(t))
         if run_backwards:
             order = order[::-1]
-        # step sizes exactly as the reference forms them (fp64): prev_t, t_i = t[-1]+0.01, t[-1]; then
-        # prev_t, t_i = t[i], t[i-1] after visiting frame i (modules/ODEConvGRUCell.py:48,73)
-        ts = timesteps.detach().to(device=inputs.device, dtype=torch.float64)
-        deltas = torch.empty(t, dtype=torch.float64, device=inputs.device)
-        deltas[0] = ts[-1] - (ts[-1] + 0.01)
-        if t > 1:
-            idx = torch.tensor(order[:-1], device=inputs.device)
-            deltas[1:] = ts[idx - 1] - ts[idx]
+        deltas = self._deltas(timesteps, inputs.device, tuple(order))
         f_op, g_op = self.ode_func.op(), self.cgru_cell.op()
         params = f_op.params() + g_op.params()
         hs = _EncoderFn.apply(f_op, g_op, len(f_op.params()), order, inputs, deltas, *params)   # [T,B,C,H,W]
