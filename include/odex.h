@@ -95,11 +95,11 @@ int odex_conv2d_repeat(const odex_conv_desc* d, int reps, odex_stream_t s);
 int odex_conv2d_wgrad(const float* x0, int ld0, int c0, const float* x1, int ld1, int c1, const float* dy, int ldy,
                       int B, int H, int W, int R, int N, float* dw, float* db, odex_stream_t s);
 
-/* Same gradient, accumulated into the kernels' own layout dwp[tap][c][n] ([R*R][c0+c1][N], n contiguous) so that the
+/* Same gradient, accumulated into the kernels' own layout dwp[tap][n][c] ([R*R][N][c0+c1], c contiguous) so that the
  * tensor-core kernel can add its TMEM accumulators with 16-byte vector reductions and a backward pass that visits a
  * layer many times (one visit per f-eval) converts to OIHW only once, with odex_wgrad_unpack (dw[n][c][r][s] +=
- * dwp[r*R+s][c][n]).  impl: ODEX_CONV_AUTO / _SIMT / _TC.  The TC kernel (tcgen05 kind::tf32, 3xTF32, MN-major
- * operands straight from NHWC, tap shift = operand start address) needs c0, c1, N % 64 == 0, W % 16 == 0,
+ * dwp[r*R+s][n][c]).  impl: ODEX_CONV_AUTO / _SIMT / _TC.  The TC kernel (tcgen05 kind::tf32, 3xTF32; dy as the K-major A operand in
+ * TMEM, the tap-shifted X atoms as MN-major B operands straight from the NHWC halo tile) needs c0, c1, N % 64 == 0, W % 16 == 0,
  * H % 4 == 0, R in {1,3,5}.  Replaces the same autograd ops as odex_conv2d_wgrad. */
 int odex_conv2d_wgrad_packed(const float* x0, int ld0, int c0, const float* x1, int ld1, int c1, const float* dy,
                              int ldy, int B, int H, int W, int R, int N, float* dwp, float* db, int impl,

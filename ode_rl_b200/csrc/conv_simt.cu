@@ -213,7 +213,7 @@ struct WgradArgs {
     int B, H, W, R, N;
     float* dw;
     int nsplit;
-    int packed;      // 0: dw is torch OIHW; 1: dw is [tap][Ctot][N] (the accumulation layout of the tensor-core kernel)
+    int packed;      // 0: dw is torch OIHW; 1: dw is [tap][N][Ctot] (the accumulation layout of the tensor-core kernel)
 };
 
 __global__ void __launch_bounds__(256) conv_wgrad_kernel(const WgradArgs a) {
@@ -283,7 +283,7 @@ __global__ void __launch_bounds__(256) conv_wgrad_kernel(const WgradArgs a) {
         for (int j = 0; j < 4; ++j) {
             const int n = nb * 64 + tn * 4 + j;
             if (n < a.N) {
-                float* dst = a.packed ? a.dw + (static_cast<long>(tap) * Ctot + c) * a.N + n
+                float* dst = a.packed ? a.dw + (static_cast<long>(tap) * a.N + n) * Ctot + c
                                       : a.dw + ((static_cast<long>(n) * Ctot + c) * a.R + r) * a.R + s;
                 atomicAdd(dst, acc[i][j]);
             }

@@ -122,7 +122,8 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
+        // whole warp runs the loop (warp-uniform operands stay in uniform registers); one elected lane issues
+        {
             constexpr uint32_t idesc_wide = umma_idesc_tf32(128, 2 * N);
             constexpr uint32_t idesc_narrow = umma_idesc_tf32(128, N);
             // descriptor words (K-major SWIZZLE_128B): hi = SBO | version | layout, lo = LBO(16 B) << 16 | start >> 4;
@@ -143,23 +144,27 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
                     tc_fence_after_sync();
                     const uint32_t b_lo0 = lbo16 | ((bst0 + sb * kBStageBytes) >> 4);
                     const uint32_t a_lo0 = lbo16 | ((hi >> 4) + static_cast<uint32_t>(r * P + s) * 8u);
+                    if (elect_one()) {
 #pragma unroll
-                    for (int k8 = 0; k8 < 4; ++k8) {
+                        for (int k8 = 0; k8 < 4; ++k8) {
 #pragma unroll
-                        for (int mt = 0; mt < 2; ++mt) {
-                            const uint32_t a_lo = a_lo0 + mt * 64u + k8 * 2u;
-                            const uint32_t d = tmem_base + mt * 2 * N;
-                            umma_tf32_ss_w(d, a_lo, a_hi32, b_lo0 + k8 * 2u, b_hi32, idesc_wide, (c | tap | k8) != 0);
-                            umma_tf32_ss_w(d + N, a_lo + lo_delta, a_hi32, b_lo0 + k8 * 2u, b_hi32, idesc_narrow, 1u);
+                            for (int mt = 0; mt < 2; ++mt) {
+                                const uint32_t a_lo = a_lo0 + mt * 64u + k8 * 2u;
+                                const uint32_t d = tmem_base + mt * 2 * N;
+                                umma_tf32_ss_w(d, a_lo, a_hi32, b_lo0 + k8 * 2u, b_hi32, idesc_wide, (c | tap | k8) != 0);
+                                umma_tf32_ss_w(d + N, a_lo + lo_delta, a_hi32, b_lo0 + k8 * 2u, b_hi32, idesc_narrow, 1u);
+                            }
                         }
+                        umma_commit(bar_b_empty + 8 * sb);
                     }
-                    umma_commit(bar_b_empty + 8 * sb);
+                    __syncwarp();
                     if (++sb == SB) { sb = 0; pb ^= 1u; }
                     if (++s == R) { s = 0; ++r; }
                 }
             }
-            umma_commit(bar_acc);
-            if (g.dbg && blockIdx.x == 0) { g.dbg[2] = w_sp; g.dbg[3] = w_bf; g.dbg[4] = clock64() - t0_; }
+            if (elect_one()) umma_commit(bar_acc);
+            __syncwarp();
+            if (g.dbg && blockIdx.x == 0 && lane == 0) { g.dbg[2] = w_sp; g.dbg[3] = w_bf; g.dbg[4] = clock64() - t0_; }
         }
     } else {
         // ===================== hi/lo split, then epilogue =====================

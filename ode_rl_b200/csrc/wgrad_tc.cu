@@ -43,7 +43,7 @@ struct WgradTcGeom {
     int TG, CG, NB, PS; // grid factors: tap groups, 64-channel groups of X, 64-channel blocks of dy, pixel splits
     int taps_per_group;
     int ntiles;         // B * (H / 4) * (W / 16)
-    float* dwp;         // [R*R][Ctot][N], accumulated
+    float* dwp;         // [R*R][N][Ctot], accumulated
     float* db;          // [N] or nullptr, accumulated
     int trunc_hi;       // 1: hi operand = raw word (hardware truncation), see split4
     long long* dbg;     // diagnostic: per-role cycle counters of CTA 0 (ODEX_WGRAD_DEBUG=1), else nullptr
@@ -126,19 +126,32 @@ __device__ __forceinline__ void tile_coords(const WgradTcGeom& g, int t, int& im
     img = t / (tx * ty);
 }
 
+// TS-mode MMA: A (dy, K-major) from TMEM, B (X atom, MN-major) from shared memory.
+__device__ __forceinline__ void umma_tf32_ts_w(uint32_t d_tmem, uint32_t a_tmem, uint32_t b_lo, uint32_t b_hi, uint32_t idesc,
+                                               uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 db;\n\t"
+        "mov.b64 db, {%2, %3};\n\t"
+        "setp.ne.b32 p, %5, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], db, %4, p;\n\t}"
+        ::"r"(d_tmem), "r"(a_tmem), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
 template <int R>
 __global__ void __launch_bounds__(192, 1)
 wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant__ CUtensorMap tmX1,
                 const __grid_constant__ CUtensorMap tmDY, const WgradTcGeom g) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-    const uint32_t stage_bytes = 4u * g.xplane + 4u * kWgDyPlane;
-    const uint32_t bars = base + 2u * stage_bytes;
-    const uint32_t bar_raw_full = bars;            // [2]
-    const uint32_t bar_split_full = bars + 16;     // [2]
-    const uint32_t bar_stage_empty = bars + 32;    // [2]
-    const uint32_t bar_acc = bars + 48;
-    const uint32_t tmem_slot = bars + 56;
+    const uint32_t stage_bytes = 4u * g.xplane + 2u * kWgDyPlane;   // [Xhi c0-31][Xhi c32-63][Xlo ..][Xlo ..][dy n0-31][dy n32-63]
+    constexpr int S = (R <= 3) ? 3 : 2;            // pipeline stages (shared-memory tiles and TMEM A slots)
+    const uint32_t bars = base + static_cast<uint32_t>(S) * stage_bytes;
+    const uint32_t bar_raw_full = bars;            // [S]
+    const uint32_t bar_split_full = bars + 24;     // [S]
+    const uint32_t bar_stage_empty = bars + 48;    // [S]
+    const uint32_t bar_acc = bars + 72;
+    const uint32_t tmem_slot = bars + 80;
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -153,16 +166,19 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant_
     const int tap0 = tg * g.taps_per_group;
     const int ntap = min(g.taps_per_group, taps - tap0);
     constexpr int pad = R >> 1;
-    const int hrows = (kWgTH + 2 * pad) * g.P;     // pixel slots of one halo plane
-    // R <= 3: one N = 128 MMA per K atom with B = [dy_hi | dy_lo] (8 KB of operand reads instead of 2 x 6 KB -- the
-    // kernel is bound by shared-memory bandwidth), 128 accumulator columns per tap; R = 5: two N = 64 MMAs into 64 columns
-    constexpr bool kWide = R <= 3;
+    constexpr int P = kWgTW + 2 * pad;
+    constexpr int hrows = (kWgTH + 2 * pad) * P;   // pixel slots of one halo plane
+    // The A operand [dy_hi ; dy_lo] (M = 128 rows = 64 channels x {hi, lo}, K = the tile's 64 pixels) lives in TMEM, so the
+    // tensor core reads only the X atoms from shared memory: per 8-pixel atom two N = 64 MMAs (B = Xhi atom, then Xlo atom)
+    // accumulate all four partial products into the tap's 64 columns (rows 0-63: dy_hi x ., rows 64-127: dy_lo x .).
+    constexpr bool kWide = false;
     constexpr int DC = kWide ? 128 : 64;
+    const uint32_t a_col0 = static_cast<uint32_t>(ntap * DC);       // S slots x 64 columns of A behind the accumulators
     uint32_t tmem_cols = 32;
-    while (tmem_cols < static_cast<uint32_t>(ntap * DC)) tmem_cols <<= 1;
+    while (tmem_cols < a_col0 + 64u * S) tmem_cols <<= 1;
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < 2; ++i) {
+        for (int i = 0; i < S; ++i) {
             mbar_init(bar_raw_full + 8 * i, 1);
             mbar_init(bar_split_full + 8 * i, 128);
             mbar_init(bar_stage_empty + 8 * i, 1);
@@ -192,12 +208,12 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant_
             const bool second = cabs >= g.c0;
             const CUtensorMap* tmX = second ? &tmX1 : &tmX0;
             const int cx = second ? cabs - g.c0 : cabs;
-            const uint32_t tx_bytes = 2u * static_cast<uint32_t>(hrows) * 128u + 2u * kWgDyPlane;
+            constexpr uint32_t tx_bytes = 2u * hrows * 128u + 2u * kWgDyPlane;
             int it = 0;
             long long w_empty = 0, t_begin = clock64();
             for (int t = ps; t < g.ntiles; t += g.PS, ++it) {
-                const int st = it & 1;
-                const uint32_t use = static_cast<uint32_t>(it >> 1);
+                const int st = it % S;
+                const uint32_t use = static_cast<uint32_t>(it / S);
                 const long long c0_ = clock64();
                 mbar_wait(bar_stage_empty + 8 * st, (use & 1u) ^ 1u);
                 w_empty += clock64() - c0_;
@@ -216,65 +232,81 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant_
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_tf32(128, DC, 1, 1);
-            constexpr int P = kWgTW + 2 * (R / 2);
-            // descriptor words: hi = SBO 512 | version 1 | layout SWIZZLE_128B_BASE32B; lo = LBO << 16 | start >> 4
+        // The whole warp runs this loop so that every operand (descriptor words, TMEM addresses) is warp-uniform and stays
+        // in uniform registers; one elected lane issues.  (Wrapped in `if (lane == 0)` the operands are per-thread
+        // values and every UTCHMMA is preceded by an ELECT / R2UR.BROADCAST sequence: ~60 cycles per MMA, measured.)
+        {
+            constexpr uint32_t idesc = umma_idesc_tf32(128, DC, 0, 1);        // A K-major (TMEM), B MN-major (smem)
+            // B descriptor words: hi = SBO 512 | version 1 | layout SWIZZLE_128B_BASE32B; lo = LBO << 16 | start >> 4
             const uint32_t d_hi = static_cast<uint32_t>(umma_desc_mn32(0, 0) >> 32);
-            const uint32_t a_lbo = ((static_cast<uint32_t>(g.xplane) >> 4) & 0x3FFFu) << 16;
-            constexpr uint32_t b_lbo = ((static_cast<uint32_t>(kWgDyPlane) >> 4) & 0x3FFFu) << 16;
+            const uint32_t b_lbo = ((static_cast<uint32_t>(g.xplane) >> 4) & 0x3FFFu) << 16;
+            const uint32_t lo_delta = (2u * static_cast<uint32_t>(g.xplane)) >> 4;   // Xhi planes -> Xlo planes
             int it = 0;
             long long w_split = 0, t_begin = clock64();
             for (int t = ps; t < g.ntiles; t += g.PS, ++it) {
-                const int st = it & 1;
-                const uint32_t use = static_cast<uint32_t>(it >> 1);
+                const int st = it % S;
+                const uint32_t use = static_cast<uint32_t>(it / S);
                 const long long c0_ = clock64();
                 mbar_wait(bar_split_full + 8 * st, use & 1u);
                 w_split += clock64() - c0_;
                 tc_fence_after_sync();
                 const uint32_t xs = base + st * stage_bytes;
-                const uint32_t ds = xs + 4u * g.xplane;
-                const uint32_t b_lo0 = b_lbo | (ds >> 4);
+                const uint32_t a_tmem = tmem_base + a_col0 + static_cast<uint32_t>(st) * 64u;
                 int r = tap0 / R, s = tap0 - r * R;
                 for (int tl = 0; tl < ntap; ++tl) {
                     const uint32_t d_tmem = tmem_base + tl * DC;
-                    const uint32_t a_lo0 = a_lbo | ((xs >> 4) + static_cast<uint32_t>(r * P + s) * 8u);
+                    const uint32_t b_lo0 = b_lbo | ((xs >> 4) + static_cast<uint32_t>(r * P + s) * 8u);
+                    if (elect_one()) {
 #pragma unroll
-                    for (int ty = 0; ty < kWgTH; ++ty) {
+                        for (int ty = 0; ty < kWgTH; ++ty) {
 #pragma unroll
-                        for (int h = 0; h < 2; ++h) {
-                            const uint32_t a_lo = a_lo0 + static_cast<uint32_t>(ty * P + 8 * h) * 8u;
-                            const uint32_t b_lo = b_lo0 + static_cast<uint32_t>(ty * kWgTW + 8 * h) * 8u;
-                            umma_tf32_ss_w(d_tmem, a_lo, d_hi, b_lo, d_hi, idesc, (it | ty | h) != 0);
-                            if (!kWide) umma_tf32_ss_w(d_tmem, a_lo, d_hi, b_lo + (2u * kWgDyPlane >> 4), d_hi, idesc, 1u);
+                            for (int h = 0; h < 2; ++h) {
+                                const uint32_t b_lo = b_lo0 + static_cast<uint32_t>(ty * P + 8 * h) * 8u;
+                                const uint32_t a_at = a_tmem + static_cast<uint32_t>(ty * kWgTW + 8 * h);
+                                umma_tf32_ts_w(d_tmem, a_at, b_lo, d_hi, idesc, (it | ty | h) != 0);
+                                if (!kWide) umma_tf32_ts_w(d_tmem, a_at, b_lo + lo_delta, d_hi, idesc, 1u);
+                            }
                         }
                     }
+                    __syncwarp();
                     if (++s == R) { s = 0; ++r; }
                 }
-                umma_commit(bar_stage_empty + 8 * st);
+                if (elect_one()) umma_commit(bar_stage_empty + 8 * st);
+                __syncwarp();
             }
-            umma_commit(bar_acc);
-            if (g.dbg && blockIdx.x == 0) { g.dbg[3] = w_split; g.dbg[4] = clock64() - t_begin; }
+            if (elect_one()) umma_commit(bar_acc);
+            __syncwarp();
+            if (g.dbg && blockIdx.x == 0 && lane == 0) { g.dbg[3] = w_split; g.dbg[4] = clock64() - t_begin; }
         }
     } else {
-        // ===================== hi/lo split (+ bias-gradient sums), then epilogue =====================
-        const int tid = threadIdx.x - 64;                 // 0..127
-        const bool do_db = g.db != nullptr && tg == 0 && cg == 0;
-        float4 db0 = make_float4(0.f, 0.f, 0.f, 0.f), db1 = db0;
-        const int nf4x = hrows * 8;
+        // ===================== operand preparation, then epilogue =====================
+        // thread <-> TMEM lane L = 32 * (warp % 4) + lane: dy channel n = L % 64, part = L / 64 (0: hi rows, 1: lo rows)
+        const int tid = threadIdx.x - 64;                 // 0..127 (X split work distribution)
+        const int q = warp & 3;
+        const int L = q * 32 + lane;
+        const int n = L & 63;
+        const int part = L >> 6;
+        const uint32_t lane_addr = static_cast<uint32_t>(q * 32) << 16;
+        const bool do_db = g.db != nullptr && tg == 0 && cg == 0 && part == 0;
+        float dbsum = 0.f;
+        constexpr int nf4x = hrows * 8;
+        // dy element (pixel k, channel n) inside the SWIZZLE_128B_ATOM_32B tile: 32-byte group ((n % 32) / 8) ^ (k % 4)
+        const uint32_t dy_off = static_cast<uint32_t>(n >> 5) * kWgDyPlane + static_cast<uint32_t>(n & 7) * 4u;
+        const uint32_t dy_grp = static_cast<uint32_t>((n & 31) >> 3);
         int it = 0;
         long long w_raw = 0, t_begin = clock64();
         for (int t = ps; t < g.ntiles; t += g.PS, ++it) {
-            const int st = it & 1;
-            const uint32_t use = static_cast<uint32_t>(it >> 1);
+            const int st = it % S;
+            const uint32_t use = static_cast<uint32_t>(it / S);
             const long long c0_ = clock64();
             mbar_wait(bar_raw_full + 8 * st, use & 1u);
             w_raw += clock64() - c0_;
             const uint32_t xs = base + st * stage_bytes;
-            const uint32_t ds = xs + 4u * g.xplane;
+            const uint32_t ds = xs + 4u * g.xplane + dy_off;
             {
-                // X halo planes: items (plane, i) with i = tid + 128 * k, in batches of 4 loads in flight
-                constexpr int kPer = (((kWgTH + 2 * pad) * (kWgTW + 2 * pad) * 8) + 127) / 128;   // per plane, per thread
+                // X halo planes: hi = the raw word (the tensor core reads the top 19 bits), lo = tf32(x - trunc(x)) into
+                // the lo planes; items (plane, i) with i = tid + 128 * k, 4 loads in flight
+                constexpr int kPer = (nf4x + 127) / 128;   // per plane, per thread
                 float4 dummy = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
                 for (int k0 = 0; k0 < 2 * kPer; k0 += 4) {
@@ -286,56 +318,45 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant_
                         ok[b] = item < 2 * kPer && i < nf4x;
                         src[b] = xs + static_cast<uint32_t>(item & 1) * g.xplane + static_cast<uint32_t>(i) * 16u;
                     }
-                    split_batch<4>(src, ok, 2u * g.xplane, g.trunc_hi, dummy);
-                }
-                // dy planes (sums of the raw values feed the bias gradient)
-#pragma unroll
-                for (int pl = 0; pl < 2; ++pl) {
-                    uint32_t src[4]; bool ok[4];
-#pragma unroll
-                    for (int b = 0; b < 4; ++b) {
-                        ok[b] = true;
-                        src[b] = ds + static_cast<uint32_t>(pl) * kWgDyPlane + static_cast<uint32_t>(tid + 128 * b) * 16u;
-                    }
-                    split_batch<4>(src, ok, 2u * kWgDyPlane, g.trunc_hi, pl == 0 ? db0 : db1);
+                    split_batch<4>(src, ok, 2u * g.xplane, 1, dummy);
                 }
             }
+            // dy: this lane's channel at the tile's 64 pixels -> A operand row in TMEM (K-major: column = pixel)
+            tc_fence_after_sync();
+#pragma unroll
+            for (int c0 = 0; c0 < 64; c0 += 32) {
+                uint32_t a[32];
+#pragma unroll
+                for (int k0 = 0; k0 < 32; k0 += 16) {
+                    uint32_t v[16];
+#pragma unroll
+                    for (int b = 0; b < 16; ++b) {
+                        const uint32_t k = static_cast<uint32_t>(c0 + k0 + b);
+                        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v[b]) : "r"(ds + k * 128u + ((dy_grp ^ (k & 3u)) << 5)));
+                    }
+#pragma unroll
+                    for (int b = 0; b < 16; ++b) {
+                        const float x = __uint_as_float(v[b]);
+                        dbsum += x;
+                        const float hi = __uint_as_float(v[b] & 0xFFFFE000u);
+                        a[k0 + b] = part == 0 ? v[b] : tf32_rna_bits(__float_as_uint(x - hi));
+                    }
+                }
+                tmem_st32(tmem_base + lane_addr + a_col0 + static_cast<uint32_t>(st) * 64u + c0, a);
+            }
+            tmem_st_wait();
+            tc_fence_before_sync();
             fence_proxy_async_smem();
             mbar_arrive(bar_split_full + 8 * st);
         }
-
-        // ---- epilogue: dwp[tap][c][n] += D[c][n] + D[64 + c][n]
         const long long t_loop = clock64() - t_begin;
         mbar_wait(bar_acc, 0u);             // every MMA has completed: the stage buffers are free as well
         tc_fence_after_sync();
         const long long t_acc = clock64() - t_begin;
-        if (do_db) {
-            // thread tid always touched physical 16-byte chunk (tid & 7) of rows with (row & 3) == ((tid >> 3) & 3):
-            // logical 32-byte group = physical group ^ (row & 3)  (SWIZZLE_128B_BASE32B)
-            float* sc = reinterpret_cast<float*>(smem_raw + (base - smem_u32(smem_raw)));   // stage 0 is idle now
-            sc[tid * 8 + 0] = db0.x; sc[tid * 8 + 1] = db0.y; sc[tid * 8 + 2] = db0.z; sc[tid * 8 + 3] = db0.w;
-            sc[tid * 8 + 4] = db1.x; sc[tid * 8 + 5] = db1.y; sc[tid * 8 + 6] = db1.z; sc[tid * 8 + 7] = db1.w;
-            named_bar_sync(1, 128);
-            if (tid < 64) {
-                const int plane = tid >> 5, l32 = (tid & 31) >> 3, b4 = (tid & 7) >> 2, e = tid & 3;
-                float sum = 0.f;
-#pragma unroll
-                for (int rr = 0; rr < 4; ++rr) {
-                    const int c16 = ((l32 ^ rr) << 1) | b4;
-#pragma unroll
-                    for (int rb = 0; rb < 4; ++rb) sum += sc[((rr + 4 * rb) * 8 + c16) * 8 + plane * 4 + e];
-                }
-                atomicAdd(g.db + nb * 64 + tid, sum);
-            }
-        }
+        if (do_db) atomicAdd(g.db + nb * 64 + n, dbsum);
 
-        // D rows 0-63 = Xhi * [dyhi | dylo], rows 64-127 = Xlo * [...]: dw[c][n] is the sum over both row halves (and, in
-        // wide mode, both column halves).  The lo-row warps hand their sums over through shared memory (the stage
-        // buffers are idle), so each CTA issues 64 x 16 vector reductions per tap.
-        const int q = warp & 3;
-        const int row = q * 32 + lane;
-        const int cl = row & 63;
-        const uint32_t lane_addr = static_cast<uint32_t>(q * 32) << 16;
+        // ---- epilogue: dwp[tap][n][c] += D[n][c] (+ D[n][64 + c]) + the same from the lo rows D[64 + n][.]; the lo-row
+        // warps hand their sums over through shared memory, so a CTA issues 64 x 16 vector reductions per tap
         for (int tl = 0; tl < ntap; ++tl) {
             float acc[64];
 #pragma unroll
@@ -352,21 +373,21 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant_
                     for (int k = 0; k < 32; ++k) acc[c0 + k] += __uint_as_float(v[k]);
                 }
             }
-            const uint32_t sc = base + 16384u + static_cast<uint32_t>(tl & 1) * 16384u + static_cast<uint32_t>(cl) * 256u;
-            if (row >= 64) {
+            const uint32_t sc = base + 16384u + static_cast<uint32_t>(tl & 1) * 16384u + static_cast<uint32_t>(n) * 256u;
+            if (part == 1) {
 #pragma unroll
                 for (int k = 0; k < 16; ++k)
-                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(sc + ((static_cast<uint32_t>(k) ^ (cl & 15)) << 4)),
+                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(sc + ((static_cast<uint32_t>(k) ^ (n & 15)) << 4)),
                                  "f"(acc[4 * k]), "f"(acc[4 * k + 1]), "f"(acc[4 * k + 2]), "f"(acc[4 * k + 3]) : "memory");
             }
             named_bar_sync(1, 128);
-            if (row < 64) {
-                float* dst = g.dwp + (static_cast<long>(tap0 + tl) * g.Ctot + cg * 64 + cl) * g.N + nb * 64;
+            if (part == 0) {
+                float* dst = g.dwp + (static_cast<long>(tap0 + tl) * g.N + nb * 64 + n) * g.Ctot + cg * 64;
 #pragma unroll
                 for (int k = 0; k < 16; ++k) {
                     float4 o;
                     asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(o.x), "=f"(o.y), "=f"(o.z), "=f"(o.w)
-                                 : "r"(sc + ((static_cast<uint32_t>(k) ^ (cl & 15)) << 4)));
+                                 : "r"(sc + ((static_cast<uint32_t>(k) ^ (n & 15)) << 4)));
                     red_add_v4(dst + 4 * k, acc[4 * k] + o.x, acc[4 * k + 1] + o.y, acc[4 * k + 2] + o.z, acc[4 * k + 3] + o.w);
                 }
             }
@@ -381,7 +402,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant_
     }
 }
 
-// dw[n][c][r][s] += dwp[tap][c][n]   (torch OIHW <- the kernels' accumulation layout)
+// dw[n][c][r][s] += dwp[tap][n][c]   (torch OIHW <- the kernels' accumulation layout)
 __global__ void __launch_bounds__(256) wgrad_unpack_kernel(const float* __restrict__ dwp, int N, int C, int taps,
                                                            float* __restrict__ dw) {
     const long total = static_cast<long>(N) * C * taps;
@@ -390,7 +411,7 @@ __global__ void __launch_bounds__(256) wgrad_unpack_kernel(const float* __restri
         const int tap = static_cast<int>(i % taps);
         const int c = static_cast<int>((i / taps) % C);
         const int n = static_cast<int>(i / (static_cast<long>(taps) * C));
-        dw[i] += dwp[(static_cast<long>(tap) * C + c) * N + n];
+        dw[i] += dwp[(static_cast<long>(tap) * N + n) * C + c];
     }
 }
 
@@ -462,7 +483,8 @@ int launch_wgrad_tc(const float* x0, int ld0, int c0, const float* x1, int ld1, 
         cudaMemsetAsync(dbuf, 0, 16 * sizeof(long long), s);
         g.dbg = dbuf;
     }
-    const int smem = 1024 + 2 * (4 * g.xplane + 4 * kWgDyPlane) + 64;
+    const int stages = R <= 3 ? 3 : 2;
+    const int smem = 1024 + stages * (4 * g.xplane + 2 * kWgDyPlane) + 128;
     if (smem > 232448) return fail(ODEX_E_UNSUPPORTED, "wgrad(tc): needs %d bytes of shared memory", smem);
 
     CUtensorMap tmX0, tmX1, tmDY;

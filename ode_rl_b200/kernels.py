@@ -150,7 +150,7 @@ class Backend:
 
     def conv2d_wgrad_packed(self, x0: torch.Tensor, x1: Optional[torch.Tensor], dy: torch.Tensor, R: int,
                             dwp: torch.Tensor, db: Optional[torch.Tensor], impl: int = CONV_AUTO) -> None:
-        """odex_conv2d_wgrad_packed: dwp [R*R, c0+c1, N] += X^T dy (tensor-core kernel where the shape allows),
+        """odex_conv2d_wgrad_packed: dwp [R*R, N, c0+c1] += dy^T X (tensor-core kernel where the shape allows),
         db += colsum(dy)."""
         B, H, W, c0 = x0.shape
         p0, ld0 = _rows(x0)
@@ -160,14 +160,14 @@ class Backend:
             c1 = x1.shape[3]
         pdy, ldy = _rows(dy)
         N = dy.shape[3]
-        assert dwp.is_contiguous() and tuple(dwp.shape) == (R * R, c0 + c1, N), (tuple(dwp.shape), (R * R, c0 + c1, N))
+        assert dwp.is_contiguous() and tuple(dwp.shape) == (R * R, N, c0 + c1), (tuple(dwp.shape), (R * R, N, c0 + c1))
         _lib.check(self.lib.odex_conv2d_wgrad_packed(p0, ld0, c0, p1, ld1, c1, pdy, ldy, B, H, W, R, N, dwp.data_ptr(),
                                                      _ptr(db), impl, _stream()), "odex_conv2d_wgrad_packed")
 
     def wgrad_unpack(self, dwp: torch.Tensor, dw: torch.Tensor) -> None:
-        """odex_wgrad_unpack: dw (OIHW) += dwp ([R*R, C, N])."""
+        """odex_wgrad_unpack: dw (OIHW) += dwp ([R*R, N, C])."""
         N, Cc, R, _ = dw.shape
-        assert dw.is_contiguous() and dwp.is_contiguous() and tuple(dwp.shape) == (R * R, Cc, N)
+        assert dw.is_contiguous() and dwp.is_contiguous() and tuple(dwp.shape) == (R * R, N, Cc)
         _lib.check(self.lib.odex_wgrad_unpack(dwp.data_ptr(), N, Cc, R, dw.data_ptr(), _stream()), "odex_wgrad_unpack")
 
     # ------------------------------------------------------------------ ConvGRU gates (+GroupNorm)

@@ -68,7 +68,7 @@ class GradSink:
 
     def __init__(self):
         self._g: Dict[int, torch.Tensor] = {}
-        self._packed: Dict[int, torch.Tensor] = {}      # conv weights: [R*R, C, N] accumulators (kernel layout)
+        self._packed: Dict[int, torch.Tensor] = {}      # conv weights: [R*R, N, C] accumulators (kernel layout)
 
     def get_packed(self, w: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
         """Accumulator of a Conv2d weight gradient in the wgrad kernels' layout; converted to OIHW in result()."""
@@ -77,7 +77,7 @@ class GradSink:
         g = self._packed.get(id(w))
         if g is None:
             N, Cc, R, _ = w.shape
-            g = torch.zeros((R * R, Cc, N), dtype=torch.float32, device=w.device)
+            g = torch.zeros((R * R, N, Cc), dtype=torch.float32, device=w.device)
             self._packed[id(w)] = g
         return g
 
@@ -101,7 +101,7 @@ class GradSink:
 
 def _scratch_packed(w: torch.Tensor) -> torch.Tensor:
     N, Cc, R, _ = w.shape
-    return torch.zeros((R * R, Cc, N), dtype=torch.float32, device=w.device)
+    return torch.zeros((R * R, N, Cc), dtype=torch.float32, device=w.device)
 
 
 class _PackCache:

@@ -107,14 +107,14 @@ class FakeBackend:
         N, Cc = dy.shape[3], x.shape[3]
         g = torch.nn.grad.conv2d_weight(x.permute(0, 3, 1, 2).contiguous(), (N, Cc, R, R),
                                         dy.permute(0, 3, 1, 2).contiguous(), padding=(R - 1) // 2)
-        dwp += g.permute(2, 3, 1, 0).reshape(R * R, Cc, N)
+        dwp += g.permute(2, 3, 0, 1).reshape(R * R, N, Cc)
         if db is not None:
             db += dy.sum((0, 1, 2))
 
     def wgrad_unpack(self, dwp, dw):
         self.launches += 1
         N, Cc, R, _ = dw.shape
-        dw += dwp.reshape(R, R, Cc, N).permute(3, 2, 0, 1)
+        dw += dwp.reshape(R, R, N, Cc).permute(2, 3, 0, 1)
 
     # ------------------------------------------------------------------ ConvGRU gates
     @staticmethod

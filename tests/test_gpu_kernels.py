@@ -149,7 +149,7 @@ def test_conv2d_wgrad_packed(be, fb, case, impl):
     x0 = torch.randn(B, H, W, c0)
     x1 = torch.randn(B, H, W, c1) if c1 else None
     dy = torch.randn(B, H, W, N)
-    dwp0 = torch.randn(R * R, c0 + c1, N)
+    dwp0 = torch.randn(R * R, N, c0 + c1)
     db0 = torch.randn(N)
     rw, rb = dwp0.clone(), db0.clone()
     fb.conv2d_wgrad_packed(x0, x1, dy, R, rw, rb)

@@ -8,7 +8,7 @@ for (B, c0, c1, N, R) in [(128, 64, 0, 64, 3), (128, 64, 64, 128, 5), (128, 64, 
     x0 = torch.randn(B, 16, 16, c0, device="cuda")
     x1 = torch.randn(B, 16, 16, c1, device="cuda") if c1 else None
     dy = torch.randn(B, 16, 16, N, device="cuda")
-    dwp = torch.zeros(R * R, c0 + c1, N, device="cuda")
+    dwp = torch.zeros(R * R, N, c0 + c1, device="cuda")
     db = torch.zeros(N, device="cuda")
     for _ in range(3):
         be.conv2d_wgrad_packed(x0, x1, dy, R, dwp, db)
