@@ -161,7 +161,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         }
     } else if (warp == 5) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
+        // whole warp runs the loop (warp-uniform operands stay in uniform registers); one elected lane issues
+        {
             constexpr uint32_t idesc_wide = umma_idesc_tf32(128, 2 * N);
             constexpr uint32_t idesc_narrow = umma_idesc_tf32(128, N);
             int sb = 0, sa = 0; uint32_t pb = 0, pa = 0;
@@ -170,6 +171,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                 mbar_wait(bar_a_full + 8 * sa, pa);
                 tc_fence_after_sync();
                 const uint32_t bsm = bst0 + sb * Cfg::kBStageBytes;
+                if (elect_one()) {
 #pragma unroll
                 for (int k8 = 0; k8 < 4; ++k8) {
                     const uint64_t bd = umma_desc_sw128(bsm + k8 * 32, 16, 1024);
@@ -187,10 +189,13 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                 }
                 umma_commit(bar_a_empty + 8 * sa);
                 umma_commit(bar_b_empty + 8 * sb);
+                }
+                __syncwarp();
                 if (++sb == SB) { sb = 0; pb ^= 1u; }
                 if (++sa == SA) { sa = 0; pa ^= 1u; }
             }
-            umma_commit(bar_acc);
+            if (elect_one()) umma_commit(bar_acc);
+            __syncwarp();
         }
     } else {
         // ===================== transform (A operand) + epilogue: thread <-> output pixel =====================

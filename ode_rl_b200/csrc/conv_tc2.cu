@@ -38,7 +38,8 @@ struct Conv2Geom {
 template <int N, int R>
 __global__ void __launch_bounds__(192, 1)
 conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
-                const __grid_constant__ CUtensorMap tmB, const Conv2Geom g, const ConvEpilogue ep) {
+                const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmOut, const Conv2Geom g,
+                const ConvEpilogue ep) {
     if (ep.skip != nullptr && *ep.skip != 0) return;
     constexpr int kBStageBytes = 2 * N * 128;
     constexpr uint32_t kTmemCols = 4 * N;          // 2 M-tiles x (main N + corr N)
@@ -71,6 +72,7 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
         tma_prefetch_desc(&tmA0);
         tma_prefetch_desc(&tmA1);
         tma_prefetch_desc(&tmB);
+        tma_prefetch_desc(&tmOut);
     }
     if (warp == 1) {
         tmem_alloc(tmem_slot, kTmemCols);
@@ -212,79 +214,103 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
         mbar_wait(bar_acc, 0u);
         tc_fence_after_sync();
         const long long t_acc = clock64() - t0_;
-        // Phase 1: TMEM -> registers -> shared staging tile [256 pixels][N floats] (the halo planes are idle now).
-        // Thread <-> TMEM lane <-> pixel; 16-byte chunks are XOR-swizzled by the pixel index so that both this
-        // row-per-thread write and the coalesced read-back below are bank-conflict free.
+        // Phase 1: TMEM -> registers -> shared staging tile (the halo planes are idle now), laid out as the TMA store box:
+        // N / 32 planes of [256 pixels][32 channels], 128-byte rows with the SWIZZLE_128B chunk XOR (conflict-free for
+        // this row-per-thread write).  With no residual / act' operand the whole epilogue (bias, activation) happens
+        // here in registers; otherwise the raw sums are staged and Phase 2 finishes them in place with coalesced loads.
         const int q = warp & 3;
         const int m = q * 32 + lane;                  // TMEM lane = pixel of the M-tile: (ty, tx) = (m / 8, m % 8)
         const uint32_t lane_addr = static_cast<uint32_t>(q * 32) << 16;
-        constexpr int kRowBytes = N * 4;
-        constexpr int kChunks = N / 4;                // 16-byte chunks per pixel row (16 or 32)
+        constexpr int kChunks = N / 4;                // 16-byte chunks per pixel (16 or 32)
+        const bool fast = ep.dact == nullptr && ep.res == nullptr;
 #pragma unroll 1
         for (int mt = 0; mt < 2; ++mt) {
             const int p = (m >> 3) * 16 + mt * 8 + (m & 7);
-            const uint32_t row = base + static_cast<uint32_t>(p) * kRowBytes;
 #pragma unroll 1
             for (int c0 = 0; c0 < N; c0 += 32) {
                 uint32_t vm[32], vc[32];
                 tmem_ld32(tmem_base + lane_addr + mt * 2 * N + c0, vm);
                 tmem_ld32(tmem_base + lane_addr + mt * 2 * N + N + c0, vc);
                 tmem_ld_wait();
+                const uint32_t row = base + static_cast<uint32_t>(c0 / 32) * 32768u + static_cast<uint32_t>(p) * 128u;
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
-                    const float a0 = __uint_as_float(vm[4 * j]) + __uint_as_float(vc[4 * j]);
-                    const float a1 = __uint_as_float(vm[4 * j + 1]) + __uint_as_float(vc[4 * j + 1]);
-                    const float a2 = __uint_as_float(vm[4 * j + 2]) + __uint_as_float(vc[4 * j + 2]);
-                    const float a3 = __uint_as_float(vm[4 * j + 3]) + __uint_as_float(vc[4 * j + 3]);
-                    const uint32_t ch = static_cast<uint32_t>(c0 / 4 + j);
-                    const uint32_t dst = row + ((ch ^ (static_cast<uint32_t>(p) & (kChunks - 1))) << 4);
-                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "f"(a0), "f"(a1), "f"(a2), "f"(a3) : "memory");
+                    float a[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) a[e] = __uint_as_float(vm[4 * j + e]) + __uint_as_float(vc[4 * j + e]);
+                    if (fast) {
+                        if (ep.bias) {
+                            const float4 bv = __ldg(reinterpret_cast<const float4*>(ep.bias + c0) + j);
+                            a[0] += bv.x; a[1] += bv.y; a[2] += bv.z; a[3] += bv.w;
+                        }
+                        if (ep.act == 1) {
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) a[e] = fmaxf(a[e], 0.f);
+                        } else if (ep.act == 2) {
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) a[e] = tanhf(a[e]);
+                        }
+                    }
+                    const uint32_t dst = row + ((static_cast<uint32_t>(j) ^ (static_cast<uint32_t>(p) & 7u)) << 4);
+                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "f"(a[0]), "f"(a[1]), "f"(a[2]), "f"(a[3]) : "memory");
                 }
             }
         }
         tc_fence_before_sync();
+        if (fast) fence_proxy_async_smem();
         asm volatile("bar.sync 1, 128;" ::: "memory");
         const long long t_ph1 = clock64() - t0_;
 
-        // Phase 2: coalesced epilogue.  Consecutive threads take consecutive 16-byte chunks of a pixel row, so the
-        // residual / saved-activation loads and the output stores are full 128-byte lines.
-        float alpha = ep.alpha;
-        if (ep.alpha_dev) alpha *= static_cast<float>(*ep.alpha_dev);
-        const int jch = tid & (kChunks - 1);          // this thread's chunk of every row it visits (128 % kChunks == 0)
-        float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (ep.bias) bv = __ldg(reinterpret_cast<const float4*>(ep.bias) + jch);
+        if (!fast) {
+            // Phase 2: finish in place.  Consecutive threads take consecutive 16-byte chunks of a pixel row, so the residual /
+            // saved-activation loads are full 128-byte lines.
+            float alpha = ep.alpha;
+            if (ep.alpha_dev) alpha *= static_cast<float>(*ep.alpha_dev);
+            const int jch = tid & (kChunks - 1);      // this thread's chunk of every row it visits (128 % kChunks == 0)
+            float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (ep.bias) bv = __ldg(reinterpret_cast<const float4*>(ep.bias) + jch);
 #pragma unroll 4
-        for (int i = tid; i < 256 * kChunks; i += 128) {
-            const int p = i / kChunks;
-            const uint32_t src = base + static_cast<uint32_t>(p) * kRowBytes +
-                                 ((static_cast<uint32_t>(jch) ^ (static_cast<uint32_t>(p) & (kChunks - 1))) << 4);
-            float v[4];
-            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]) : "r"(src));
-            const long pix = (static_cast<long>(img) * g.H + y0 + (p >> 4)) * g.W + x0 + (p & 15);
-            v[0] += bv.x; v[1] += bv.y; v[2] += bv.z; v[3] += bv.w;
-            if (ep.act == 1) {
+            for (int i = tid; i < 256 * kChunks; i += 128) {
+                const int p = i / kChunks;
+                const uint32_t src = base + static_cast<uint32_t>(jch >> 3) * 32768u + static_cast<uint32_t>(p) * 128u +
+                                     ((static_cast<uint32_t>(jch & 7) ^ (static_cast<uint32_t>(p) & 7u)) << 4);
+                float v[4];
+                asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]) : "r"(src));
+                const long pix = (static_cast<long>(img) * g.H + y0 + (p >> 4)) * g.W + x0 + (p & 15);
+                v[0] += bv.x; v[1] += bv.y; v[2] += bv.z; v[3] += bv.w;
+                if (ep.act == 1) {
 #pragma unroll
-                for (int e = 0; e < 4; ++e) v[e] = fmaxf(v[e], 0.f);
-            } else if (ep.act == 2) {
+                    for (int e = 0; e < 4; ++e) v[e] = fmaxf(v[e], 0.f);
+                } else if (ep.act == 2) {
 #pragma unroll
-                for (int e = 0; e < 4; ++e) v[e] = tanhf(v[e]);
-            }
-            if (ep.dact) {
-                const float4 mk = *reinterpret_cast<const float4*>(ep.dact + pix * ep.ldd + 4 * jch);
-                if (ep.dact_kind == 1) {
-                    v[0] = mk.x > 0.f ? v[0] : 0.f; v[1] = mk.y > 0.f ? v[1] : 0.f;
-                    v[2] = mk.z > 0.f ? v[2] : 0.f; v[3] = mk.w > 0.f ? v[3] : 0.f;
-                } else {
-                    v[0] *= 1.f - mk.x * mk.x; v[1] *= 1.f - mk.y * mk.y;
-                    v[2] *= 1.f - mk.z * mk.z; v[3] *= 1.f - mk.w * mk.w;
+                    for (int e = 0; e < 4; ++e) v[e] = tanhf(v[e]);
                 }
+                if (ep.dact) {
+                    const float4 mk = *reinterpret_cast<const float4*>(ep.dact + pix * ep.ldd + 4 * jch);
+                    if (ep.dact_kind == 1) {
+                        v[0] = mk.x > 0.f ? v[0] : 0.f; v[1] = mk.y > 0.f ? v[1] : 0.f;
+                        v[2] = mk.z > 0.f ? v[2] : 0.f; v[3] = mk.w > 0.f ? v[3] : 0.f;
+                    } else {
+                        v[0] *= 1.f - mk.x * mk.x; v[1] *= 1.f - mk.y * mk.y;
+                        v[2] *= 1.f - mk.z * mk.z; v[3] *= 1.f - mk.w * mk.w;
+                    }
+                }
+                if (ep.res) {
+                    const float4 rr = *reinterpret_cast<const float4*>(ep.res + pix * ep.ldr + 4 * jch);
+                    v[0] = fmaf(alpha, v[0], rr.x); v[1] = fmaf(alpha, v[1], rr.y);
+                    v[2] = fmaf(alpha, v[2], rr.z); v[3] = fmaf(alpha, v[3], rr.w);
+                }
+                asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(src), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]) : "memory");
             }
-            if (ep.res) {
-                const float4 rr = *reinterpret_cast<const float4*>(ep.res + pix * ep.ldr + 4 * jch);
-                v[0] = fmaf(alpha, v[0], rr.x); v[1] = fmaf(alpha, v[1], rr.y);
-                v[2] = fmaf(alpha, v[2], rr.z); v[3] = fmaf(alpha, v[3], rr.w);
-            }
-            *reinterpret_cast<float4*>(ep.out + pix * ep.ldo + 4 * jch) = make_float4(v[0], v[1], v[2], v[3]);
+            fence_proxy_async_smem();
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+        }
+        // Phase 3: one thread hands the tile to the TMA store engine (full-line asynchronous writes)
+        if (tid == 0) {
+#pragma unroll
+            for (int pl = 0; pl < N / 32; ++pl) tma_store_4d(&tmOut, base + pl * 32768u, pl * 32, x0, y0, img);
+            tma_store_commit();
+            tma_store_wait_read();
         }
         tc_fence_before_sync();
         if (g.dbg && blockIdx.x == 0 && tid == 0) { g.dbg[5] = w_raw; g.dbg[6] = t_split; g.dbg[7] = t_acc; g.dbg[8] = clock64() - t0_; g.dbg[9] = t_ph1; }
@@ -366,7 +392,8 @@ static int launch_tc2(const odex_conv_desc* d, cudaStream_t s) {
     Conv2Geom g; int smem;
     if (conv2_plan(d, &g, &smem)) return fail(ODEX_E_UNSUPPORTED, "conv(tc2): tile does not fit shared memory");
     const int pad = d->R / 2;
-    CUtensorMap tmA0, tmA1, tmB;
+    CUtensorMap tmA0, tmA1, tmB, tmOut;
+    if (int rc = make_act_map2(&tmOut, d->out, d->ldo, d->N, d->B, d->H, d->W, 16, 16)) return rc;
     if (int rc = make_act_map2(&tmA0, d->x0, d->ld0, d->c0, d->B, d->H, d->W, g.P, 16 + 2 * pad)) return rc;
     if (d->x1) {
         if (int rc = make_act_map2(&tmA1, d->x1, d->ld1, d->c1, d->B, d->H, d->W, g.P, 16 + 2 * pad)) return rc;
@@ -403,7 +430,7 @@ static int launch_tc2(const odex_conv_desc* d, cudaStream_t s) {
         cudaMemsetAsync(dbuf, 0, 16 * sizeof(long long), s);
         g.dbg = dbuf;
     }
-    kern<<<grid, 192, smem, s>>>(tmA0, tmA1, tmB, g, ep);
+    kern<<<grid, 192, smem, s>>>(tmA0, tmA1, tmB, tmOut, g, ep);
     if (debug) {
         long long h[16];
         cudaStreamSynchronize(s);
