@@ -30,6 +30,34 @@ inline int launched(const char* what) {
     return 0;
 }
 
+// Programmatic dependent launch: a kernel launched through launch_pdl may become resident while its predecessor on the
+// stream is still draining (the predecessor calls pdl_trigger once its own dependency is satisfied).  Every such kernel
+// sets up shared memory / barriers / TMEM first and executes pdl_wait() before its FIRST global-memory access; the wait
+// returns when the predecessor grid has completed and its writes are visible.  For a kernel launched the ordinary way
+// both instructions are no-ops.  ODEX_PDL=0 turns the launch attribute off.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+inline bool pdl_enabled() {
+    static const bool on = [] { const char* e = getenv("ODEX_PDL"); return !(e && e[0] == '0'); }();
+    return on;
+}
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 // 148 SMs on a B200; elementwise / reduction grids are sized as a multiple of it

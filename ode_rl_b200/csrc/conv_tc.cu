@@ -111,7 +111,7 @@ static int launch_tc(const odex_conv_desc* d, cudaStream_t s) {
     std::call_once(once, [&] { attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemMax); });
     if (attr_err != cudaSuccess) return fail(-static_cast<int>(attr_err), "conv(tc): cudaFuncSetAttribute: %s", cudaGetErrorString(attr_err));
     const int grid = d->B * (d->H / g.TH);
-    kern<<<grid, ConvCfg<N>::kThreads, smem, s>>>(tmA0, tmA1, tmB, g, ep);
+    launch_pdl(kern, grid, ConvCfg<N>::kThreads, smem, s, tmA0, tmA1, tmB, g, ep);
     return launched("conv_tc_kernel");
 }
 

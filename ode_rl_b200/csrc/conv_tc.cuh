@@ -19,6 +19,7 @@
 #pragma once
 #include <cuda.h>
 
+#include "common.cuh"
 #include "ptx_sm100.cuh"
 
 namespace odex {
@@ -70,7 +71,6 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     using Cfg = ConvCfg<N>;
     constexpr int SB = Cfg::kBStages;
     constexpr int SA = kATmem ? Cfg::kAStages : Cfg::kAStagesSS;
-    if (ep.skip != nullptr && *ep.skip != 0) return;
 
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -124,7 +124,13 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     const int y0 = (blockIdx.x % tiles_per_img) * g.TH;
     const int KB = G * taps * 2;
 
-    if (warp == 4) {
+    // shared memory / TMEM set-up above may overlap the previous kernel's tail; global memory is first read below
+    pdl_wait();
+    pdl_trigger();
+    const bool skip = ep.skip != nullptr && *ep.skip != 0;      // CTA-uniform: a skipped attempt only tears down
+
+    if (skip) {
+    } else if (warp == 4) {
         // ===================== TMA producer =====================
         if (lane == 0) {
             int sb = 0; uint32_t pb = 0;

@@ -32,15 +32,17 @@ struct Conv2Geom {
     int P;              // halo pitch in pixel slots = 16 + 2 * pad
     int plane;          // bytes of one 32-channel halo plane (hi or lo), multiple of 1024
     int b_stages;
+    int aux_mode;       // 1: the epilogue's one extra operand tile (act' mask or residual) is TMA-prefetched into shared memory
+    int stage_off;      // byte offset of the output staging tile inside the halo planes
     long long* dbg;     // diagnostic cycle counters of CTA 0 (ODEX_CONV_DEBUG=1), else nullptr
 };
 
 template <int N, int R>
 __global__ void __launch_bounds__(192, 1)
 conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
-                const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmOut, const Conv2Geom g,
+                const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmAux,
+                const Conv2Geom g,
                 const ConvEpilogue ep) {
-    if (ep.skip != nullptr && *ep.skip != 0) return;
     constexpr int kBStageBytes = 2 * N * 128;
     constexpr uint32_t kTmemCols = 4 * N;          // 2 M-tiles x (main N + corr N)
     extern __shared__ uint8_t smem_raw[];
@@ -55,6 +57,9 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
     const uint32_t bar_b_empty = bars + 160;       // [SB <= 4]
     const uint32_t bar_acc = bars + 192;
     const uint32_t tmem_slot = bars + 200;
+    const uint32_t bar_early = bars + 208;         // MMAs of every chunk but the last have completed
+    const uint32_t bar_aux = bars + 216;           // the epilogue operand tile has landed
+    const uint32_t bias_s = bars + 256;            // [N] floats, staged once so the epilogue never waits on global memory
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -66,6 +71,8 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
         for (int i = 0; i < NC; ++i) { mbar_init(bar_raw_full + 8 * i, 1); mbar_init(bar_split_full + 8 * i, 128); }
         for (int i = 0; i < SB; ++i) { mbar_init(bar_b_full + 8 * i, 1); mbar_init(bar_b_empty + 8 * i, 1); }
         mbar_init(bar_acc, 1);
+        mbar_init(bar_early, 1);
+        mbar_init(bar_aux, 1);
         fence_barrier_init();
     }
     if (warp == 0 && lane == 0) {
@@ -73,6 +80,7 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
         tma_prefetch_desc(&tmA1);
         tma_prefetch_desc(&tmB);
         tma_prefetch_desc(&tmOut);
+        tma_prefetch_desc(&tmAux);
     }
     if (warp == 1) {
         tmem_alloc(tmem_slot, kTmemCols);
@@ -90,7 +98,14 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
     const int img = blockIdx.x / (tiles_x * tiles_y);
     const int hrows = (16 + 2 * pad) * g.P;
 
-    if (warp == 0) {
+    // Everything above touched only shared memory / TMEM, so it may overlap the tail of the previous kernel on the
+    // stream; from here on global memory is read.
+    pdl_wait();
+    pdl_trigger();
+    const bool skip = ep.skip != nullptr && *ep.skip != 0;      // CTA-uniform: a skipped attempt only tears down
+
+    if (skip) {
+    } else if (warp == 0) {
         // ===================== TMA producer =====================
         if (lane == 0) {
             for (int c = 0; c < NC; ++c) {
@@ -163,6 +178,10 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
                     if (++sb == SB) { sb = 0; pb ^= 1u; }
                     if (++s == R) { s = 0; ++r; }
                 }
+                if (g.aux_mode && c == NC - 2) {        // chunks 0 .. NC-2 are dead once these MMAs retire
+                    if (elect_one()) umma_commit(bar_early);
+                    __syncwarp();
+                }
             }
             if (elect_one()) umma_commit(bar_acc);
             __syncwarp();
@@ -172,6 +191,12 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
         // ===================== hi/lo split, then epilogue =====================
         const int tid = threadIdx.x - 64;
         const int nf4 = hrows * 8;
+        if (tid < N / 4) {
+            float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (ep.bias) bv = __ldg(reinterpret_cast<const float4*>(ep.bias) + tid);
+            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(bias_s + 16u * tid), "f"(bv.x), "f"(bv.y), "f"(bv.z), "f"(bv.w) : "memory");
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
         long long w_raw = 0; const long long t0_ = clock64();
         for (int c = 0; c < NC; ++c) {
             { const long long c0_ = clock64(); mbar_wait(bar_raw_full + 8 * c, 0u); w_raw += clock64() - c0_; }
@@ -211,8 +236,21 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
 
         // ---------- epilogue: (main + corr) + bias -> act -> act'(saved) -> res + alpha*v -> NHWC store ----------
         const long long t_split = clock64() - t0_;
+        const uint32_t stage = base + static_cast<uint32_t>(g.stage_off);
+        if (g.aux_mode) {
+            // the act' mask / residual tile goes into the planes of the chunks the tensor core is done with, while the
+            // last chunk's MMAs are still running; the output is staged in the last chunk's planes afterwards
+            if (tid == 0) {
+                mbar_wait(bar_early, 0u);
+                mbar_arrive_expect_tx(bar_aux, 256u * N * 4u);
+#pragma unroll
+                for (int pl = 0; pl < N / 32; ++pl) tma_load_4d(base + pl * 32768u, &tmAux, bar_aux, pl * 32, x0, y0, img);
+            }
+            __syncwarp();
+        }
         mbar_wait(bar_acc, 0u);
         tc_fence_after_sync();
+        if (g.aux_mode) mbar_wait(bar_aux, 0u);
         const long long t_acc = clock64() - t0_;
         // Phase 1: TMEM -> registers -> shared staging tile (the halo planes are idle now), laid out as the TMA store box:
         // N / 32 planes of [256 pixels][32 channels], 128-byte rows with the SWIZZLE_128B chunk XOR (conflict-free for
@@ -222,27 +260,37 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
         const int m = q * 32 + lane;                  // TMEM lane = pixel of the M-tile: (ty, tx) = (m / 8, m % 8)
         const uint32_t lane_addr = static_cast<uint32_t>(q * 32) << 16;
         constexpr int kChunks = N / 4;                // 16-byte chunks per pixel (16 or 32)
-        const bool fast = ep.dact == nullptr && ep.res == nullptr;
+        const bool fast = g.aux_mode || (ep.dact == nullptr && ep.res == nullptr);     // whole epilogue in registers
+        const int aux_kind = !g.aux_mode ? 0 : ep.res ? 3 : ep.dact_kind;                // 1 relu', 2 tanh', 3 residual
+        float alpha = ep.alpha;
+        if (ep.alpha_dev) alpha *= static_cast<float>(*ep.alpha_dev);
+        const float4* bias4 = reinterpret_cast<const float4*>(smem_raw + (bias_s - smem_u32(smem_raw)));
+        // 64 accumulator columns (main + correction) per trip: four TMEM loads in flight, one wait
 #pragma unroll 1
-        for (int mt = 0; mt < 2; ++mt) {
+        for (int it = 0; it < N / 32; ++it) {
+            const int mt = it / (N / 64);
+            const int c0 = (it % (N / 64)) * 64;
             const int p = (m >> 3) * 16 + mt * 8 + (m & 7);
-#pragma unroll 1
-            for (int c0 = 0; c0 < N; c0 += 32) {
-                uint32_t vm[32], vc[32];
-                tmem_ld32(tmem_base + lane_addr + mt * 2 * N + c0, vm);
-                tmem_ld32(tmem_base + lane_addr + mt * 2 * N + N + c0, vc);
-                tmem_ld_wait();
-                const uint32_t row = base + static_cast<uint32_t>(c0 / 32) * 32768u + static_cast<uint32_t>(p) * 128u;
+            uint32_t vm[2][32], vc[2][32];
+            tmem_ld32(tmem_base + lane_addr + mt * 2 * N + c0, vm[0]);
+            tmem_ld32(tmem_base + lane_addr + mt * 2 * N + N + c0, vc[0]);
+            tmem_ld32(tmem_base + lane_addr + mt * 2 * N + c0 + 32, vm[1]);
+            tmem_ld32(tmem_base + lane_addr + mt * 2 * N + N + c0 + 32, vc[1]);
+            tmem_ld_wait();
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                float4 bv[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) bv[j] = fast ? bias4[(c0 + 32 * h) / 4 + j] : make_float4(0.f, 0.f, 0.f, 0.f);
+                const uint32_t rel = static_cast<uint32_t>(c0 / 32 + h) * 32768u + static_cast<uint32_t>(p) * 128u;
+                const uint32_t row = stage + rel;
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                     float a[4];
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) a[e] = __uint_as_float(vm[4 * j + e]) + __uint_as_float(vc[4 * j + e]);
+                    for (int e = 0; e < 4; ++e) a[e] = __uint_as_float(vm[h][4 * j + e]) + __uint_as_float(vc[h][4 * j + e]);
+                    a[0] += bv[j].x; a[1] += bv[j].y; a[2] += bv[j].z; a[3] += bv[j].w;
                     if (fast) {
-                        if (ep.bias) {
-                            const float4 bv = __ldg(reinterpret_cast<const float4*>(ep.bias + c0) + j);
-                            a[0] += bv.x; a[1] += bv.y; a[2] += bv.z; a[3] += bv.w;
-                        }
                         if (ep.act == 1) {
 #pragma unroll
                             for (int e = 0; e < 4; ++e) a[e] = fmaxf(a[e], 0.f);
@@ -251,8 +299,23 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
                             for (int e = 0; e < 4; ++e) a[e] = tanhf(a[e]);
                         }
                     }
-                    const uint32_t dst = row + ((static_cast<uint32_t>(j) ^ (static_cast<uint32_t>(p) & 7u)) << 4);
-                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "f"(a[0]), "f"(a[1]), "f"(a[2]), "f"(a[3]) : "memory");
+                    const uint32_t sw = (static_cast<uint32_t>(j) ^ (static_cast<uint32_t>(p) & 7u)) << 4;
+                    if (aux_kind) {
+                        float x[4];
+                        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(x[0]), "=f"(x[1]), "=f"(x[2]), "=f"(x[3]) : "r"(base + rel + sw));
+                        if (aux_kind == 1) {
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) a[e] = x[e] > 0.f ? a[e] : 0.f;
+                        } else if (aux_kind == 2) {
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) a[e] *= 1.f - x[e] * x[e];
+                        } else {
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) a[e] = fmaf(alpha, a[e], x[e]);
+                        }
+                    }
+                    const uint32_t dst = row + sw;
+                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "f"(a[0]), "f"(a[1]), "f"(a[2]), "f"(a[3]));
                 }
             }
         }
@@ -264,15 +327,13 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
         if (!fast) {
             // Phase 2: finish in place.  Consecutive threads take consecutive 16-byte chunks of a pixel row, so the residual /
             // saved-activation loads are full 128-byte lines.
-            float alpha = ep.alpha;
-            if (ep.alpha_dev) alpha *= static_cast<float>(*ep.alpha_dev);
             const int jch = tid & (kChunks - 1);      // this thread's chunk of every row it visits (128 % kChunks == 0)
-            float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (ep.bias) bv = __ldg(reinterpret_cast<const float4*>(ep.bias) + jch);
+            float4 bv;
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(bv.x), "=f"(bv.y), "=f"(bv.z), "=f"(bv.w) : "r"(bias_s + 16u * jch));
 #pragma unroll 4
             for (int i = tid; i < 256 * kChunks; i += 128) {
                 const int p = i / kChunks;
-                const uint32_t src = base + static_cast<uint32_t>(jch >> 3) * 32768u + static_cast<uint32_t>(p) * 128u +
+                const uint32_t src = stage + static_cast<uint32_t>(jch >> 3) * 32768u + static_cast<uint32_t>(p) * 128u +
                                      ((static_cast<uint32_t>(jch & 7) ^ (static_cast<uint32_t>(p) & 7u)) << 4);
                 float v[4];
                 asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]) : "r"(src));
@@ -308,7 +369,7 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
         // Phase 3: one thread hands the tile to the TMA store engine (full-line asynchronous writes)
         if (tid == 0) {
 #pragma unroll
-            for (int pl = 0; pl < N / 32; ++pl) tma_store_4d(&tmOut, base + pl * 32768u, pl * 32, x0, y0, img);
+            for (int pl = 0; pl < N / 32; ++pl) tma_store_4d(&tmOut, stage + pl * 32768u, pl * 32, x0, y0, img);
             tma_store_commit();
             tma_store_wait_read();
         }
@@ -349,13 +410,23 @@ static int conv2_plan(const odex_conv_desc* d, Conv2Geom* g, int* smem) {
     const int hrows = (16 + 2 * pad) * g->P;
     g->plane = (hrows * 128 + 1023) / 1024 * 1024;
     const int NC = g->nsrc * g->csrc / 32;
-    const int fixed = 1024 + NC * 2 * g->plane + 256;
+    const int fixed = 1024 + NC * 2 * g->plane + 256 + 512;     // alignment slack, halo planes, barriers, bias
     const int bstage = 2 * d->N * 128;
     int sb = (kSmemMax2 - fixed) / bstage;
     if (sb > 4) sb = 4;
     g->b_stages = sb;
     *smem = fixed + sb * bstage;
     g->dbg = nullptr;
+    g->aux_mode = 0;
+    g->stage_off = 0;
+    {
+        const int tile = 256 * d->N * 4;
+        const bool one = (d->dact != nullptr) != (d->res != nullptr);
+        if (one && NC >= 2 && tile <= 2 * g->plane && tile <= (NC - 1) * 2 * g->plane) {
+            g->aux_mode = 1;
+            g->stage_off = (NC - 1) * 2 * g->plane;
+        }
+    }
     if (256 * d->N * 4 > NC * 2 * g->plane) return 1;      // the epilogue stages the output tile in the halo planes
     return sb >= 2 ? 0 : 1;
 }
@@ -392,8 +463,13 @@ static int launch_tc2(const odex_conv_desc* d, cudaStream_t s) {
     Conv2Geom g; int smem;
     if (conv2_plan(d, &g, &smem)) return fail(ODEX_E_UNSUPPORTED, "conv(tc2): tile does not fit shared memory");
     const int pad = d->R / 2;
-    CUtensorMap tmA0, tmA1, tmB, tmOut;
+    CUtensorMap tmA0, tmA1, tmB, tmOut, tmAux;
     if (int rc = make_act_map2(&tmOut, d->out, d->ldo, d->N, d->B, d->H, d->W, 16, 16)) return rc;
+    tmAux = tmOut;
+    if (g.aux_mode) {
+        const float* aux = d->res ? d->res : d->dact;
+        if (int rc = make_act_map2(&tmAux, aux, d->res ? d->ldr : d->ldd, d->N, d->B, d->H, d->W, 16, 16)) return rc;
+    }
     if (int rc = make_act_map2(&tmA0, d->x0, d->ld0, d->c0, d->B, d->H, d->W, g.P, 16 + 2 * pad)) return rc;
     if (d->x1) {
         if (int rc = make_act_map2(&tmA1, d->x1, d->ld1, d->c1, d->B, d->H, d->W, g.P, 16 + 2 * pad)) return rc;
@@ -430,7 +506,7 @@ static int launch_tc2(const odex_conv_desc* d, cudaStream_t s) {
         cudaMemsetAsync(dbuf, 0, 16 * sizeof(long long), s);
         g.dbg = dbuf;
     }
-    kern<<<grid, 192, smem, s>>>(tmA0, tmA1, tmB, tmOut, g, ep);
+    launch_pdl(kern, grid, 192, smem, s, tmA0, tmA1, tmB, tmOut, tmAux, g, ep);
     if (debug) {
         long long h[16];
         cudaStreamSynchronize(s);

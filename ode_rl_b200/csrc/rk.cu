@@ -29,6 +29,8 @@ struct LinArgs {
 template <int NIN>
 __global__ void __launch_bounds__(256) lincomb_kernel(float* __restrict__ out, const LinArgs a, const double* dt_dev,
                                                       long n4, const int* skip) {
+    pdl_wait();
+    pdl_trigger();
     if (skip != nullptr && *skip != 0) return;
     float c[NIN];
     const float dt = dt_dev ? static_cast<float>(*dt_dev) : 1.f;
@@ -53,6 +55,8 @@ __global__ void __launch_bounds__(256) lincomb_kernel(float* __restrict__ out, c
 // out = dy * act'(a): gradient through a trailing activation of a conv stack (a = saved activation output)
 __global__ void __launch_bounds__(256) act_bwd_kernel(float* __restrict__ out, const float* __restrict__ dy,
                                                       const float* __restrict__ a, int kind, long n4) {
+    pdl_wait();
+    pdl_trigger();
     for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n4;
          i += static_cast<long>(gridDim.x) * blockDim.x) {
         const float4 d = ld4(dy + 4 * i), v = ld4(a + 4 * i);
@@ -342,14 +346,14 @@ extern "C" int odex_lincomb(float* out, int nin, const float* const* in, const d
     const long n4 = n / 4;
     const int blocks = ew_blocks(n4);
     switch (nin) {
-        case 1: lincomb_kernel<1><<<blocks, 256, 0, s>>>(out, a, dt_dev, n4, skip); break;
-        case 2: lincomb_kernel<2><<<blocks, 256, 0, s>>>(out, a, dt_dev, n4, skip); break;
-        case 3: lincomb_kernel<3><<<blocks, 256, 0, s>>>(out, a, dt_dev, n4, skip); break;
-        case 4: lincomb_kernel<4><<<blocks, 256, 0, s>>>(out, a, dt_dev, n4, skip); break;
-        case 5: lincomb_kernel<5><<<blocks, 256, 0, s>>>(out, a, dt_dev, n4, skip); break;
-        case 6: lincomb_kernel<6><<<blocks, 256, 0, s>>>(out, a, dt_dev, n4, skip); break;
-        case 7: lincomb_kernel<7><<<blocks, 256, 0, s>>>(out, a, dt_dev, n4, skip); break;
-        default: lincomb_kernel<8><<<blocks, 256, 0, s>>>(out, a, dt_dev, n4, skip); break;
+        case 1: launch_pdl(lincomb_kernel<1>, blocks, 256, 0, s, out, a, dt_dev, n4, skip); break;
+        case 2: launch_pdl(lincomb_kernel<2>, blocks, 256, 0, s, out, a, dt_dev, n4, skip); break;
+        case 3: launch_pdl(lincomb_kernel<3>, blocks, 256, 0, s, out, a, dt_dev, n4, skip); break;
+        case 4: launch_pdl(lincomb_kernel<4>, blocks, 256, 0, s, out, a, dt_dev, n4, skip); break;
+        case 5: launch_pdl(lincomb_kernel<5>, blocks, 256, 0, s, out, a, dt_dev, n4, skip); break;
+        case 6: launch_pdl(lincomb_kernel<6>, blocks, 256, 0, s, out, a, dt_dev, n4, skip); break;
+        case 7: launch_pdl(lincomb_kernel<7>, blocks, 256, 0, s, out, a, dt_dev, n4, skip); break;
+        default: launch_pdl(lincomb_kernel<8>, blocks, 256, 0, s, out, a, dt_dev, n4, skip); break;
     }
     return launched("lincomb_kernel");
 }
@@ -358,7 +362,7 @@ extern "C" int odex_lincomb(float* out, int nin, const float* const* in, const d
 extern "C" int odex_act_bwd(float* out, const float* dy, const float* a, int kind, long long n, odex_stream_t s) {
     if (!out || !dy || !a || n <= 0 || n % 4) return fail(ODEX_E_ARG, "act_bwd: bad argument");
     if (!aligned16(out) || !aligned16(dy) || !aligned16(a)) return fail(ODEX_E_ALIGN, "act_bwd: pointers must be 16-byte aligned");
-    act_bwd_kernel<<<ew_blocks(n / 4), 256, 0, static_cast<cudaStream_t>(s)>>>(out, dy, a, kind, n / 4);
+    launch_pdl(act_bwd_kernel, ew_blocks(n / 4), 256, 0, static_cast<cudaStream_t>(s), out, dy, a, kind, n / 4);
     return launched("act_bwd_kernel");
 }
 

@@ -201,6 +201,10 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant_
     uint32_t tmem_base;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
+    // shared memory / TMEM set-up above may overlap the previous kernel's tail; global memory is first touched below
+    pdl_wait();
+    pdl_trigger();
+
     if (warp == 0) {
         // ===================== TMA producer =====================
         if (lane == 0) {
@@ -505,7 +509,7 @@ int launch_wgrad_tc(const float* x0, int ld0, int c0, const float* x1, int ld1, 
         if (attr_err == cudaSuccess) attr_err = cudaFuncSetAttribute(wgrad_tc_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
     });
     if (attr_err != cudaSuccess) return fail(-static_cast<int>(attr_err), "wgrad(tc): cudaFuncSetAttribute: %s", cudaGetErrorString(attr_err));
-    kern<<<units * g.PS, 192, smem, s>>>(tmX0, tmX1, tmDY, g);
+    launch_pdl(kern, units * g.PS, 192, smem, s, tmX0, tmX1, tmDY, g);
     if (debug) {
         long long h[16];
         cudaStreamSynchronize(s);
