@@ -292,7 +292,10 @@ def main():
         ach = CONV3_FLOPS * B / avg / 1e12
         peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
         roof = {"bound": "tensor", "kernel": "conv_tc2_kernel<64,3> (3x3, 64->64, 3xTF32, tcgen05 kind::tf32)", "achieved": ach,
-                "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": None,
+                "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+                # dram__bytes_read.sum + dram__bytes_write.sum of one launch at batch 128 (ncu --set full, profiles/r01_final_ncu.md):
+                # the 8.4 MB input is read once, the output stays in the 126 MB L2; scaled with the batch
+                "traffic": int(8761088 * B / 128), "traffic_source": "profiles/r01_final_ncu.md (ncu --set full, per launch)",
                 "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (of measured)" if peaks else "fallback 1.4 PF (of fallback)",
                 "note": "achieved counts algorithmic FLOPs once (2*M*N*K); the kernel issues 3 TF32 MMAs per useful one and TF32 runs "
                         "at half the bf16 rate, so frac*6 is the share of tensor issue slots used; %d launches back to back, "

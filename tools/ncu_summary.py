@@ -1,0 +1,90 @@
+"""Turn the outputs of tools/profile_pass.sh (gpurun_out/launches_*.csv, gpurun_out/prof_*_<kernel>.ncu-rep) into the
+markdown summaries committed under profiles/.  Needs `ncu` on PATH (reads reports, no GPU).
+usage: python tools/ncu_summary.py <tag> > profiles/<tag>_ncu.md          (tag e.g. r01b)"""
+import collections
+import csv
+import io
+import re
+import subprocess
+import sys
+
+KERNELS = ["conv_tc2_kernel", "wgrad_tc_kernel", "conv_tc_kernel", "lincomb_kernel"]
+METRICS = [
+    ("launch__grid_size", "grid"),
+    ("launch__registers_per_thread", "registers / thread"),
+    ("launch__shared_mem_per_block_dynamic", "dynamic smem / CTA"),
+    ("gpu__time_duration.sum", "duration (cold cache, serialised)"),
+    ("gpc__cycles_elapsed.max", "elapsed cycles"),
+    ("sm__cycles_active.avg", "SM active cycles (avg over 148)"),
+    ("sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", "tensor pipe active, % of active cycles"),
+    ("sm__mem_tensor_cycles_active.avg.pct_of_peak_sustained_active", "tensor memory pipe active, % of active cycles"),
+    ("sm__throughput.avg.pct_of_peak_sustained_elapsed", "SM throughput, % of peak (elapsed)"),
+    ("smsp__issue_active.avg.pct_of_peak_sustained_active", "issue slots busy, %"),
+    ("l1tex__data_pipe_lsu_wavefronts_mem_shared.sum", "shared-memory wavefronts (LSU)"),
+    ("l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "shared-memory bank conflicts (LSU)"),
+    ("lts__t_sector_hit_rate.pct", "L2 hit rate"),
+    ("dram__bytes_read.sum", "DRAM read"),
+    ("dram__bytes_write.sum", "DRAM written"),
+    ("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "DRAM throughput, % of peak"),
+]
+
+
+def raw(path):
+    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(out)))
+    return rows[0], rows[1], rows[2:]
+
+
+def launches(path):
+    rows = list(csv.reader(l for l in open(path) if l.startswith('"')))
+    hdr = rows[0]
+    ki, vi, ui = hdr.index("Kernel Name"), hdr.index("Metric Value"), hdr.index("Metric Unit")
+    agg, tot = collections.OrderedDict(), 0.0
+    for r in rows[1:]:
+        name = re.sub(r"\(.*", "", r[ki])[:70]
+        v = float(r[vi].replace(",", ""))
+        v = v / 1000 if r[ui] == "ns" else v * 1000 if r[ui] == "ms" else v
+        a = agg.setdefault(name, [0, 0.0])
+        a[0] += 1
+        a[1] += v
+        tot += v
+    return agg, tot, len(rows) - 1
+
+
+def main():
+    tag = sys.argv[1]
+    print("# %s - ncu summary of one eager training step (configs[1]: rk4, B=128, 1 x B200)\n" % tag)
+    print("Produced by `tools/profile_pass.sh` under gpurun (after the same script exited 0 without ncu), summarised by")
+    print("`tools/ncu_summary.py %s`.  Times under ncu are cold-cache and serialised: shares, not absolutes.\n" % tag)
+    agg, tot, n = launches("gpurun_out/launches_%s.csv" % tag)
+    print("## Launch list (`ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none python tools/one_step.py`)\n")
+    print("%d kernel launches in the step, %.2f ms summed.\n" % (n, tot / 1000))
+    print("| share | total us | launches | avg us | kernel |\n|---|---|---|---|---|")
+    ours = 0.0
+    for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+        if "odex::" in k:
+            ours += v[1]
+    for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1])[:24]:
+        print("| %.1f %% | %.1f | %d | %.1f | `%s` |" % (100 * v[1] / tot, v[1], v[0], v[1] / v[0], k))
+    print("\nlibodex kernels: %.1f %% of the summed device time; the rest is the torch/cuDNN ConvEncode/ConvDecode, loss and"
+          " Adam (out of scope, SURVEY.md 8f n1).\n" % (100 * ours / tot))
+    for k in KERNELS:
+        try:
+            hdr, units, rows = raw("gpurun_out/prof_%s_%s.ncu-rep" % (tag, k))
+        except Exception as e:  # noqa: BLE001
+            print("## %s: report missing (%s)\n" % (k, e))
+            continue
+        print("## `%s` (`ncu --set full --clock-control none --import-source on -k regex:%s`)\n" % (k, k))
+        names = [r[hdr.index("Kernel Name")] for r in rows]
+        print("| metric | " + " | ".join("`%s`" % re.sub(r"\(.*", "", nm).replace("void ", "")[:40] for nm in names) + " |")
+        print("|---|" + "---|" * len(rows))
+        for m, label in METRICS:
+            if m not in hdr:
+                continue
+            i = hdr.index(m)
+            print("| %s | " % label + " | ".join("%s %s" % (r[i], units[i]) for r in rows) + " |")
+        print()
+
+
+if __name__ == "__main__":
+    main()
