@@ -106,6 +106,32 @@ int odex_conv2d_wgrad_packed(const float* x0, int ld0, int c0, const float* x1, 
                              odex_stream_t s);
 int odex_wgrad_unpack(const float* dwp, int N, int C, int R, float* dw, odex_stream_t s);
 
+/* ------------------------------------------------------------------------------------------------ fused conv chain
+ * A chain of L 3x3 C->C convolutions (C = 64) over 16x16 images in ONE launch, the image resident in shared memory
+ * between layers:  a_0 = x;  v_l = act_l(conv_l(a_l) + bias_l);  v_l = v_l * act'(aux_l) [aux_kind 1 = ReLU', 2 = Tanh',
+ * aux_l the saved activation]  or  v_l = aux_l + alpha * v_l [aux_kind 3, residual];  a_{l+1} = v_l;  out[l] = v_l when
+ * out[l] != NULL (out[L-1] is required).  alpha = alpha * (alpha_dev ? (float)*alpha_dev : 1).
+ * With forward-packed weights this is ODEFunc.forward (modules/DiffEqSolver.py:71-80 over the Sequential of
+ * helpers/utils.py:158-183) including the saved activations and the fused `y + dt * f` increment of the solvers;
+ * with dgrad-packed weights, aux = saved activations (masks) and out = every layer's input gradient, it is the
+ * autograd backward-data chain of the same network.  Same 3xTF32 tcgen05 arithmetic as odex_conv2d(TC).
+ * odex_convnet_supported returns 1 when the shape is taken (H = W = 16, C = 64, 1 <= L <= ODEX_NET_MAX_LAYERS, every
+ * w_tc present, strides % 4 == 0), else 0; odex_convnet on an unsupported shape returns ODEX_E_UNSUPPORTED. */
+#define ODEX_NET_MAX_LAYERS 6
+typedef struct odex_convnet_desc {
+    const float* x; int ldx;
+    int B, H, W, C, L;
+    const float* w_tc[ODEX_NET_MAX_LAYERS];     /* odex_pack_weights(tc=1) of each layer */
+    const float* bias[ODEX_NET_MAX_LAYERS];     /* [C] or NULL */
+    int act[ODEX_NET_MAX_LAYERS];               /* ODEX_ACT_* */
+    const float* aux[ODEX_NET_MAX_LAYERS]; int ld_aux[ODEX_NET_MAX_LAYERS]; int aux_kind[ODEX_NET_MAX_LAYERS];
+    float* out[ODEX_NET_MAX_LAYERS]; int ld_out[ODEX_NET_MAX_LAYERS];
+    float alpha; const double* alpha_dev;
+    const int* skip;
+} odex_convnet_desc;
+int odex_convnet(const odex_convnet_desc* d, odex_stream_t s);
+int odex_convnet_supported(const odex_convnet_desc* d);
+
 /* ------------------------------------------------------------------------------------------------ ConvGRU gates
  * GroupNorm (groups of 32 channels, biased variance, eps, affine) fused with the gate non-linearities.
  * g: conv_gates output [B,H,W,2C] (bias included).  z = sigmoid(GN(g)[:, :C]); r = sigmoid(GN(g)[:, C:]);

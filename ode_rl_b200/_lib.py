@@ -43,6 +43,25 @@ class ConvDesc(C.Structure):
     ]
 
 
+NET_MAX_LAYERS = 6
+
+
+class ConvNetDesc(C.Structure):
+    """struct odex_convnet_desc (include/odex.h)."""
+
+    _fields_ = [
+        ("x", C.c_void_p), ("ldx", C.c_int),
+        ("B", C.c_int), ("H", C.c_int), ("W", C.c_int), ("C", C.c_int), ("L", C.c_int),
+        ("w_tc", C.c_void_p * NET_MAX_LAYERS),
+        ("bias", C.c_void_p * NET_MAX_LAYERS),
+        ("act", C.c_int * NET_MAX_LAYERS),
+        ("aux", C.c_void_p * NET_MAX_LAYERS), ("ld_aux", C.c_int * NET_MAX_LAYERS), ("aux_kind", C.c_int * NET_MAX_LAYERS),
+        ("out", C.c_void_p * NET_MAX_LAYERS), ("ld_out", C.c_int * NET_MAX_LAYERS),
+        ("alpha", C.c_float), ("alpha_dev", C.c_void_p),
+        ("skip", C.c_void_p),
+    ]
+
+
 class DopriState(C.Structure):
     """struct odex_dopri_state (include/odex.h) -- the host reads a copy of it back once per forward."""
 
@@ -76,6 +95,8 @@ SIGNATURES = {
     "odex_pack_weights": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _vp]),
     "odex_conv2d": (_i, [C.POINTER(ConvDesc), _vp]),
     "odex_conv2d_repeat": (_i, [C.POINTER(ConvDesc), _i, _vp]),
+    "odex_convnet": (_i, [C.POINTER(ConvNetDesc), _vp]),
+    "odex_convnet_supported": (_i, [C.POINTER(ConvNetDesc)]),
     "odex_conv2d_wgrad": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
     "odex_conv2d_wgrad_packed": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
     "odex_wgrad_unpack": (_i, [_vp, _i, _i, _i, _vp, _vp]),

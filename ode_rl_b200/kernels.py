@@ -14,6 +14,7 @@ Layout conventions (include/odex.h):
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List, Optional, Sequence
 
 import torch
@@ -132,6 +133,43 @@ class Backend:
         else:
             _lib.check(self.lib.odex_conv2d(C.byref(d), _stream()), "odex_conv2d")
         return out
+
+    def _convnet_desc(self, x, w_tc, bias, act, aux, aux_kind, out, alpha, alpha_dev, skip):
+        d = _lib.ConvNetDesc()
+        B, H, W, Cc = x.shape
+        d.x, d.ldx = _rows(x)
+        d.B, d.H, d.W, d.C, d.L = B, H, W, Cc, len(w_tc)
+        for l in range(len(w_tc)):
+            d.w_tc[l] = _ptr(w_tc[l])
+            d.bias[l] = _ptr(bias[l].detach()) if bias[l] is not None else None
+            d.act[l] = int(act[l])
+            d.aux_kind[l] = int(aux_kind[l]) if aux[l] is not None else 0
+            if aux[l] is not None:
+                assert tuple(aux[l].shape) == (B, H, W, Cc)
+                d.aux[l], d.ld_aux[l] = _rows(aux[l])
+            if out[l] is not None:
+                assert tuple(out[l].shape) == (B, H, W, Cc)
+                d.out[l], d.ld_out[l] = _rows(out[l])
+        d.alpha = float(alpha)
+        d.alpha_dev = _ptr(alpha_dev)
+        d.skip = _ptr(skip)
+        return d
+
+    def convnet_supported(self, x: torch.Tensor, n_layers: int) -> bool:
+        """Shape test of odex_convnet (16x16 images, 64 -> 64 3x3 layers, at most NET_MAX_LAYERS of them)."""
+        B, H, W, Cc = x.shape
+        return (H == 16 and W == 16 and Cc == 64 and 1 <= n_layers <= _lib.NET_MAX_LAYERS and B > 0
+                and x.stride(3) == 1 and x.stride(2) % 4 == 0 and os.environ.get("ODEX_NO_FUSED_NET") is None)
+
+    def convnet(self, x: torch.Tensor, w_tc: Sequence[torch.Tensor], bias: Sequence[Optional[torch.Tensor]],
+                act: Sequence[int], aux: Sequence[Optional[torch.Tensor]], aux_kind: Sequence[int],
+                out: Sequence[Optional[torch.Tensor]], alpha: float = 1.0, alpha_dev: Optional[torch.Tensor] = None,
+                skip: Optional[torch.Tensor] = None) -> None:
+        """odex_convnet: the whole conv chain in one launch; layer l: v = act(conv(a_l) + bias), v *= act'(aux) (kind 1/2)
+        or v = aux + alpha * v (kind 3), stored to out[l] when given (out[-1] required)."""
+        self.require(x)
+        d = self._convnet_desc(x, w_tc, bias, act, aux, aux_kind, out, alpha, alpha_dev, skip)
+        _lib.check(self.lib.odex_convnet(C.byref(d), _stream()), "odex_convnet")
 
     def conv2d_wgrad(self, x0: torch.Tensor, x1: Optional[torch.Tensor], dy: torch.Tensor, R: int,
                      dw: torch.Tensor, db: Optional[torch.Tensor]) -> None:

@@ -205,6 +205,12 @@ class ConvNetOp:
         for c in self.caches:
             c.invalidate()
 
+    def _fused(self, be, x: torch.Tensor) -> bool:
+        """True when the whole chain runs as one odex_convnet launch (16x16 images, every layer 64 -> 64 3x3, tcgen05)."""
+        if CONV_IMPL == "simt" or not hasattr(be, "convnet") or not be.convnet_supported(x, len(self.layers)):
+            return False
+        return all(c.in_channels == 64 and c.out_channels == 64 and c.kernel_size == (3, 3) for c, _ in self.layers)
+
     # out = res + alpha * f(x)   (res None: out = f(x))
     def fwd(self, x: torch.Tensor, save: bool = False, out: Optional[torch.Tensor] = None,
             res: Optional[torch.Tensor] = None, alpha: float = 1.0, alpha_dev: Optional[torch.Tensor] = None,
@@ -214,6 +220,37 @@ class ConvNetOp:
         L = len(self.layers)
         saved = [x] if save else None
         a = x
+        if self._fused(be, x):
+            pks = [self.caches[l].get(H, W, 64, 0, need_dgrad or save) for l in range(L)]
+            last_act = self.layers[-1][1]
+            fuse = res is not None and last_act == ACT_NONE
+            outs: List[Optional[torch.Tensor]] = [None] * L
+            for l in range(L - 1):
+                if save:
+                    outs[l] = torch.empty((B, H, W, 64), dtype=torch.float32, device=x.device)
+            if out is not None and (res is None or fuse):
+                outs[L - 1] = out
+            else:
+                outs[L - 1] = torch.empty((B, H, W, 64), dtype=torch.float32, device=x.device)
+            aux: List[Optional[torch.Tensor]] = [None] * L
+            kinds = [0] * L
+            if fuse:
+                aux[L - 1], kinds[L - 1] = res, 3
+            be.convnet(x, [pk.fwd_tc for pk in pks], [c.bias for c, _ in self.layers], [act for _, act in self.layers],
+                       aux, kinds, outs, alpha=alpha if fuse else 1.0, alpha_dev=alpha_dev if fuse else None, skip=skip)
+            if save:
+                saved.extend(outs[:L - 1])
+                if last_act != ACT_NONE:
+                    saved.append(outs[L - 1])
+            a = outs[L - 1]
+            if res is not None and not fuse:
+                o = out if out is not None else torch.empty_like(a)
+                if alpha_dev is not None:
+                    be.lincomb(o, [res, a], [1.0, alpha], dtmask=2, dt_dev=alpha_dev, skip=skip)
+                else:
+                    be.lincomb(o, [res, a], [1.0, alpha], skip=skip)
+                a = o
+            return (a, saved) if save else a
         for l, (conv, act) in enumerate(self.layers):
             last = l == L - 1
             pk = self.caches[l].get(H, W, a.shape[3], 0, need_dgrad or save)
@@ -250,6 +287,33 @@ class ConvNetOp:
         if last_act != ACT_NONE:
             assert d.is_contiguous() and saved[L].is_contiguous()
             d = be.act_bwd(torch.empty_like(saved[L]), d, saved[L], last_act)
+        if self._fused(be, x) and d.shape[3] == 64 and (need_dx or L > 1):
+            # the data-gradient chain d_{l-1} = conv_l^T(d_l) * act'(a_l) in one launch, then the weight gradients
+            lo = 0 if need_dx else 1                 # lowest layer whose input gradient is needed
+            ls = list(range(L - 1, lo - 1, -1))      # chain position k handles layer ls[k]
+            pks = [self.caches[l].get(H, W, 64, 0, True) for l in ls]
+            aux: List[Optional[torch.Tensor]] = []
+            kinds = []
+            outs: List[Optional[torch.Tensor]] = []
+            for l in ls:
+                if l > 0:
+                    aux.append(saved[l]); kinds.append(self.layers[l - 1][1])
+                    outs.append(torch.empty((B, H, W, 64), dtype=torch.float32, device=x.device))
+                else:
+                    aux.append(res); kinds.append(3 if res is not None else 0)
+                    outs.append(out if out is not None else torch.empty((B, H, W, 64), dtype=torch.float32, device=x.device))
+            be.convnet(d, [pk.dgrad_tc for pk in pks], [None] * len(ls), [ACT_NONE] * len(ls), aux, kinds, outs, alpha=1.0)
+            grads = {L - 1: d}
+            for k, l in enumerate(ls):
+                grads[l - 1] = outs[k]               # outs[k] = gradient w.r.t. the input of layer l = d_{l-1}
+            for l in range(L - 1, -1, -1):
+                conv, _ = self.layers[l]
+                gw, gb = sink.get_packed(conv.weight), sink.get(conv.bias)
+                if gw is not None or gb is not None:
+                    if gw is None:
+                        gw = _scratch_packed(conv.weight)
+                    be.conv2d_wgrad_packed(saved[l], None, grads[l], conv.kernel_size[0], gw, gb)
+            return grads[-1] if need_dx else None
         for l in range(L - 1, -1, -1):
             conv, _ = self.layers[l]
             a_l = saved[l]

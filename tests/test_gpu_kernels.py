@@ -239,3 +239,57 @@ def test_lincomb_actbwd_layout(be, fb):
     assert torch.equal(o.cpu(), x.movedim(-3, -1).contiguous())
     back = be.nhwc_to_nchw(o, torch.empty(5, 3, 64, 16, 16, device="cuda"))
     assert torch.equal(back.cpu(), x)
+
+
+@pytest.mark.parametrize("act", [ACT_RELU, ACT_TANH])
+@pytest.mark.parametrize("L,B", [(5, 3), (1, 2), (6, 150)])
+def test_convnet_fused_chain_matches_layerwise(be, L, B, act):
+    """odex_convnet (the whole 64->64 3x3 chain on a shared-memory-resident image) against the exact-fp32 FFMA convolution
+    called layer by layer: forward mode (bias, act, saved activations, fused residual with a device-side alpha) and
+    data-gradient mode (dgrad-packed weights, act' masks from saved activations, residual on the last link)."""
+    torch.manual_seed(7)
+    x = torch.randn(B, 16, 16, 64, device="cuda")
+    ws = [torch.randn(64, 64, 3, 3, device="cuda") / 24.0 for _ in range(L)]
+    bs = [torch.randn(64, device="cuda") * 0.1 if l % 2 == 0 else None for l in range(L)]
+    acts = [act] * (L - 1) + [ACT_NONE]
+    res = torch.randn(B, 16, 16, 64, device="cuda")
+    alpha_dev = torch.tensor(-0.05, dtype=torch.float64, device="cuda")
+    # ---- forward: reference layer by layer (SIMT)
+    ref, a = [], x
+    for l in range(L):
+        o = torch.empty(B, 16, 16, 64, device="cuda")
+        last = l == L - 1
+        be.conv2d(a, None, be.pack_weights(ws[l], False, False), None, 64, 3, bs[l], acts[l], o,
+                  res=res if last else None, alpha=2.0 if last else 1.0, alpha_dev=alpha_dev if last else None, impl=CONV_SIMT)
+        ref.append(o)
+        a = o
+    outs = [torch.empty(B, 16, 16, 64, device="cuda") if (l % 2 == 1 or l == L - 1) else None for l in range(L)]
+    be.convnet(x, [be.pack_weights(w, False, True) for w in ws], bs, acts, [None] * (L - 1) + [res], [0] * (L - 1) + [3], outs,
+               alpha=2.0, alpha_dev=alpha_dev)
+    torch.cuda.synchronize()
+    for l in range(L):
+        if outs[l] is not None:
+            assert rel_err(outs[l], ref[l]) < 1e-5, "forward layer %d" % l
+    # ---- data-gradient chain: d_{k+1} = conv^T(d_k) * act'(mask_k), last link adds a residual
+    dy = torch.randn(B, 16, 16, 64, device="cuda")
+    masks = [torch.randn(B, 16, 16, 64, device="cuda").tanh() for _ in range(L)]
+    ref, d = [], dy
+    for k in range(L):
+        o = torch.empty(B, 16, 16, 64, device="cuda")
+        last = k == L - 1
+        be.conv2d(d, None, be.pack_weights(ws[k], True, False), None, 64, 3, None, ACT_NONE, o,
+                  dact=None if last else masks[k], dact_kind=0 if last else act, res=res if last else None, impl=CONV_SIMT)
+        ref.append(o)
+        d = o
+    outs = [torch.empty(B, 16, 16, 64, device="cuda") for _ in range(L)]
+    be.convnet(dy, [be.pack_weights(w, True, True) for w in ws], [None] * L, [ACT_NONE] * L,
+               masks[:L - 1] + [res], [act] * (L - 1) + [3], outs)
+    torch.cuda.synchronize()
+    for k in range(L):
+        assert rel_err(outs[k], ref[k]) < 1e-5, "dgrad link %d" % k
+    # ---- skip flag: nothing is written
+    skip = torch.ones(1, dtype=torch.int32, device="cuda")
+    o2 = [None] * (L - 1) + [torch.full((B, 16, 16, 64), 7.0, device="cuda")]
+    be.convnet(x, [be.pack_weights(w, False, True) for w in ws], bs, acts, [None] * L, [0] * L, o2, skip=skip)
+    torch.cuda.synchronize()
+    assert float((o2[-1] - 7.0).abs().max()) == 0.0
