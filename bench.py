@@ -30,6 +30,9 @@ FEVAL_FLOPS = 94371840            # per sample, 5 x conv3x3 64->64 at 16x16 (SUR
 CONV3_FLOPS = 2 * 256 * 64 * 576  # one 3x3 64->64 conv, per sample
 
 
+NET_TRAFFIC_B128 = None      # bytes; filled from the ncu capture of convnet_tc_kernel
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -275,31 +278,43 @@ def main():
     roof = None
     rk = None
     if rank == 0:
+        # the dominant kernel of the step: the fused ODE-function chain (5 x conv3x3 64->64, ReLU between, saved activations
+        # stored, `y + dt*f` residual on the last layer) = one f-eval of the training forward, 92 launches per step
+        # (forward + data-gradient chains).  Launched back to back from Python: at ~66 us per launch the enqueue keeps ahead.
+        L_net = 5
         xs = torch.randn(B, 16, 16, 64, device=dev)
-        ws = torch.randn(64, 64, 3, 3, device=dev) * 0.05
-        bs = torch.randn(64, device=dev)
-        os_ = torch.empty(B, 16, 16, 64, device=dev)
-        wt = be.pack_weights(ws, False, True)
-        reps = 200
-        be.conv2d(xs, None, None, wt, 64, 3, bs, K.ACT_RELU, os_, impl=K.CONV_TC, repeat=20)
+        wts = [be.pack_weights(torch.randn(64, 64, 3, 3, device=dev) * 0.05, False, True) for _ in range(L_net)]
+        bss = [torch.randn(64, device=dev) for _ in range(L_net)]
+        outs_ = [torch.empty(B, 16, 16, 64, device=dev) for _ in range(L_net)]
+        acts_ = [K.ACT_RELU] * (L_net - 1) + [K.ACT_NONE]
+        aux_ = [None] * (L_net - 1) + [xs]
+        kinds_ = [0] * (L_net - 1) + [3]
+        reps = 100
+
+        def net_pass(n):
+            for _ in range(n):
+                be.convnet(xs, wts, bss, acts_, aux_, kinds_, outs_, alpha=0.05)
+
+        net_pass(10)
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        be.conv2d(xs, None, None, wt, 64, 3, bs, K.ACT_RELU, os_, impl=K.CONV_TC, repeat=reps)
+        net_pass(reps)
         e1.record()
         torch.cuda.synchronize()
         avg = e0.elapsed_time(e1) / 1e3 / reps
-        ach = CONV3_FLOPS * B / avg / 1e12
+        ach = L_net * CONV3_FLOPS * B / avg / 1e12
         peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
-        roof = {"bound": "tensor", "kernel": "conv_tc2_kernel<64,3> (3x3, 64->64, 3xTF32, tcgen05 kind::tf32)", "achieved": ach,
+        roof = {"bound": "tensor", "kernel": "convnet_tc_kernel (5 x conv3x3 64->64 fused, 3xTF32, tcgen05 kind::tf32)", "achieved": ach,
                 "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
-                # dram__bytes_read.sum + dram__bytes_write.sum of one launch at batch 128 (ncu --set full, profiles/r01_final_ncu.md):
-                # the 8.4 MB input is read once, the output stays in the 126 MB L2; scaled with the batch
-                "traffic": int(8761088 * B / 128), "traffic_source": "profiles/r01_final_ncu.md (ncu --set full, per launch)",
+                # dram__bytes_read.sum + dram__bytes_write.sum of one launch at batch 128 (ncu --set full,
+                # profiles/r01_convnet_ncu.md), scaled with the batch; None until that capture exists
+                "traffic": NET_TRAFFIC_B128 and int(NET_TRAFFIC_B128 * B / 128),
+                "traffic_source": "profiles/r01_convnet_ncu.md (ncu --set full, per launch)",
                 "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (of measured)" if peaks else "fallback 1.4 PF (of fallback)",
-                "note": "achieved counts algorithmic FLOPs once (2*M*N*K); the kernel issues 3 TF32 MMAs per useful one and TF32 runs "
-                        "at half the bf16 rate, so frac*6 is the share of tensor issue slots used; %d launches back to back, "
-                        "batch %d" % (reps, B),
+                "note": "achieved counts algorithmic FLOPs once (2*M*N*K per layer, 5 layers per launch); the kernel issues 3 TF32 "
+                        "MMAs per useful one and TF32 runs at half the bf16 rate, so frac*6 is the share of tensor issue slots "
+                        "used; %d launches back to back, batch %d" % (reps, B),
                 "launches_timed": reps, "avg_launch_us": avg * 1e6}
 
         # ---- RK-stage GB/s (the second half of BASELINE's metric): the fused stage-combination / error-norm / dense-output

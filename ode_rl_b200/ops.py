@@ -69,6 +69,31 @@ class GradSink:
     def __init__(self):
         self._g: Dict[int, torch.Tensor] = {}
         self._packed: Dict[int, torch.Tensor] = {}      # conv weights: [R*R, N, C] accumulators (kernel layout)
+        self._pending: Dict[int, Tuple[nn.Conv2d, list]] = {}
+        self.deferred = False                           # True: add_wgrad only records; flush() launches, batched
+
+    def add_wgrad(self, conv: nn.Conv2d, x: torch.Tensor, dy: torch.Tensor) -> None:
+        """dW(conv) += x^T dy, db += colsum(dy).  While `deferred`, the request is only recorded: weight gradients are off
+        the critical path of a backward pass, and requests whose operands are consecutive slices of one buffer (the RK
+        stages of a step, allocated as [s, B, ...] arenas) run as ONE launch over s*B images."""
+        if (conv.weight is None or not conv.weight.requires_grad) and (conv.bias is None or not conv.bias.requires_grad):
+            return
+        if not self.deferred:
+            self._launch(conv, x, dy)
+        else:
+            self._pending.setdefault(id(conv.weight), (conv, []))[1].append((x, dy))
+
+    def _launch(self, conv: nn.Conv2d, x: torch.Tensor, dy: torch.Tensor) -> None:
+        gw, gb = self.get_packed(conv.weight), self.get(conv.bias)
+        if gw is None:          # bias-only gradient: the kernel still needs a dw target
+            gw = _scratch_packed(conv.weight)
+        K.backend().conv2d_wgrad_packed(x, None, dy, conv.kernel_size[0], gw, gb)
+
+    def flush(self) -> None:
+        for conv, items in self._pending.values():
+            for x, dy in _slice_runs(items):
+                self._launch(conv, x, dy)
+        self._pending.clear()
 
     def get_packed(self, w: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
         """Accumulator of a Conv2d weight gradient in the wgrad kernels' layout; converted to OIHW in result()."""
@@ -92,11 +117,41 @@ class GradSink:
 
     def result(self, params: Sequence[torch.Tensor]) -> Tuple[Optional[torch.Tensor], ...]:
         be = K.backend()
+        self.flush()
         for p in params:
             gp = self._packed.pop(id(p), None)
             if gp is not None:
                 be.wgrad_unpack(gp, self.get(p))
         return tuple(self._g.get(id(p)) if p.requires_grad else None for p in params)
+
+
+def _slice_runs(items):
+    """[(x, dy)] -> the same requests with every run of consecutive dense slices of one storage merged into one
+    (x [n*B, ...], dy [n*B, ...]) pair."""
+    items = sorted(items, key=lambda it: it[0].data_ptr())
+    out, i = [], 0
+    while i < len(items):
+        x0, d0 = items[i]
+        n = 1
+        if x0.dim() == 4 and x0.is_contiguous() and d0.is_contiguous():
+            sx, sd = x0.numel() * x0.element_size(), d0.numel() * d0.element_size()
+            while i + n < len(items):
+                x1, d1 = items[i + n]
+                if (x1.shape == x0.shape and d1.shape == d0.shape and x1.is_contiguous() and d1.is_contiguous()
+                        and x1.data_ptr() == x0.data_ptr() + n * sx and d1.data_ptr() == d0.data_ptr() + n * sd
+                        and x1.untyped_storage().data_ptr() == x0.untyped_storage().data_ptr()
+                        and d1.untyped_storage().data_ptr() == d0.untyped_storage().data_ptr()):
+                    n += 1
+                else:
+                    break
+        if n > 1:
+            B = x0.shape[0]
+            out.append((torch.as_strided(x0, (n * B,) + tuple(x0.shape[1:]), x0.stride()),
+                        torch.as_strided(d0, (n * B,) + tuple(d0.shape[1:]), d0.stride())))
+        else:
+            out.append((x0, d0))
+        i += n
+    return out
 
 
 def _scratch_packed(w: torch.Tensor) -> torch.Tensor:
@@ -214,7 +269,9 @@ class ConvNetOp:
     # out = res + alpha * f(x)   (res None: out = f(x))
     def fwd(self, x: torch.Tensor, save: bool = False, out: Optional[torch.Tensor] = None,
             res: Optional[torch.Tensor] = None, alpha: float = 1.0, alpha_dev: Optional[torch.Tensor] = None,
-            skip: Optional[torch.Tensor] = None, need_dgrad: bool = False):
+            skip: Optional[torch.Tensor] = None, need_dgrad: bool = False,
+            bufs: Optional[List[torch.Tensor]] = None):
+        """bufs: optional caller-owned buffers for the outputs of layers 0 .. L-2 (the saved activations)."""
         be = K.backend()
         B, H, W, _ = x.shape
         L = len(self.layers)
@@ -227,7 +284,7 @@ class ConvNetOp:
             outs: List[Optional[torch.Tensor]] = [None] * L
             for l in range(L - 1):
                 if save:
-                    outs[l] = torch.empty((B, H, W, 64), dtype=torch.float32, device=x.device)
+                    outs[l] = bufs[l] if bufs is not None else torch.empty((B, H, W, 64), dtype=torch.float32, device=x.device)
             if out is not None and (res is None or fuse):
                 outs[L - 1] = out
             else:
@@ -257,6 +314,8 @@ class ConvNetOp:
             fuse = last and (res is not None) and act == ACT_NONE
             if last and out is not None and (res is None or fuse):
                 o = out
+            elif not last and bufs is not None:
+                o = bufs[l]
             else:
                 o = torch.empty((B, H, W, pk.N), dtype=torch.float32, device=x.device)
             be.conv2d(a, None, pk.fwd_simt, pk.fwd_tc, pk.N, pk.R, conv.bias, act, o,
@@ -277,7 +336,9 @@ class ConvNetOp:
 
     # dx = res + J_f(x)^T dy ; parameter gradients accumulated into `sink`
     def bwd(self, saved: List[torch.Tensor], dy: torch.Tensor, sink: GradSink, out: Optional[torch.Tensor] = None,
-            res: Optional[torch.Tensor] = None, need_dx: bool = True) -> Optional[torch.Tensor]:
+            res: Optional[torch.Tensor] = None, need_dx: bool = True,
+            gbufs: Optional[List[torch.Tensor]] = None) -> Optional[torch.Tensor]:
+        """gbufs: optional caller-owned buffers for the gradients w.r.t. the inputs of layers 1 .. L-1 (index l-1)."""
         be = K.backend()
         x = saved[0]
         B, H, W, _ = x.shape
@@ -298,7 +359,8 @@ class ConvNetOp:
             for l in ls:
                 if l > 0:
                     aux.append(saved[l]); kinds.append(self.layers[l - 1][1])
-                    outs.append(torch.empty((B, H, W, 64), dtype=torch.float32, device=x.device))
+                    outs.append(gbufs[l - 1] if gbufs is not None else
+                                torch.empty((B, H, W, 64), dtype=torch.float32, device=x.device))
                 else:
                     aux.append(res); kinds.append(3 if res is not None else 0)
                     outs.append(out if out is not None else torch.empty((B, H, W, 64), dtype=torch.float32, device=x.device))
@@ -307,26 +369,17 @@ class ConvNetOp:
             for k, l in enumerate(ls):
                 grads[l - 1] = outs[k]               # outs[k] = gradient w.r.t. the input of layer l = d_{l-1}
             for l in range(L - 1, -1, -1):
-                conv, _ = self.layers[l]
-                gw, gb = sink.get_packed(conv.weight), sink.get(conv.bias)
-                if gw is not None or gb is not None:
-                    if gw is None:
-                        gw = _scratch_packed(conv.weight)
-                    be.conv2d_wgrad_packed(saved[l], None, grads[l], conv.kernel_size[0], gw, gb)
+                sink.add_wgrad(self.layers[l][0], saved[l], grads[l])
             return grads[-1] if need_dx else None
         for l in range(L - 1, -1, -1):
             conv, _ = self.layers[l]
             a_l = saved[l]
-            gw, gb = sink.get_packed(conv.weight), sink.get(conv.bias)
-            if gw is not None or gb is not None:
-                if gw is None:   # bias-only gradient: still needs a dw target for the kernel
-                    gw = _scratch_packed(conv.weight)
-                be.conv2d_wgrad_packed(a_l, None, d, conv.kernel_size[0], gw, gb)
+            sink.add_wgrad(conv, a_l, d)
             if l == 0 and not need_dx:
                 return None
             pk = self.caches[l].get(H, W, a_l.shape[3], 0, True)
             if l > 0:
-                nd = torch.empty((B, H, W, pk.C), dtype=torch.float32, device=x.device)
+                nd = gbufs[l - 1] if gbufs is not None else torch.empty((B, H, W, pk.C), dtype=torch.float32, device=x.device)
                 be.conv2d(d, None, pk.dgrad_simt, pk.dgrad_tc, pk.C, pk.R, None, ACT_NONE, nd,
                           dact=a_l, dact_kind=self.layers[l - 1][1])
                 d = nd

@@ -73,18 +73,28 @@ def rk_step_fwd(be, op: ConvNetOp, tab: Tableau, y: torch.Tensor, y_next: torch.
         r = op.fwd(y, save=save, out=y_next, res=y, alpha=1.0, alpha_dev=dt_dev, skip=skip)
         return [r[1]] if save else None
     ks: List[torch.Tensor] = []
+    # training: stage inputs and saved activations of the s stages live in [s, B, ...] arenas, so that the deferred weight
+    # gradients of a layer run as one launch over all stages (GradSink.add_wgrad)
+    arenas = yi_arena = None
+    if save and len(op.layers) > 1:
+        yi_arena = torch.empty((s,) + tuple(y.shape), dtype=y.dtype, device=y.device)
+        if all(c.out_channels == y.shape[3] for c, _ in op.layers[:-1]):
+            arenas = [torch.empty((s,) + tuple(y.shape), dtype=y.dtype, device=y.device) for _ in range(len(op.layers) - 1)]
     for i in range(s):
         if i == 0:
             yi = y
         else:
-            yi = torch.empty_like(y) if (save or k_bufs is None) else k_bufs[s + (i & 1)]
+            if yi_arena is not None:
+                yi = yi_arena[i]
+            else:
+                yi = torch.empty_like(y) if (save or k_bufs is None) else k_bufs[s + (i & 1)]
             _lin(be, yi, [y] + ks, [1.0] + tab.beta[i - 1], dt_dev=dt_dev, dt_from=1, skip=skip)
         if i == 0 and k0 is not None:
             ks.append(k0)
             saved.append(None)
             continue
         kout = k_bufs[i] if k_bufs is not None else None
-        r = op.fwd(yi, save=save, out=kout, skip=skip)
+        r = op.fwd(yi, save=save, out=kout, skip=skip, bufs=[a[i] for a in arenas] if arenas is not None else None)
         if save:
             ks.append(r[0])
             saved.append(r[1])
@@ -102,6 +112,13 @@ def rk_step_bwd(be, op: ConvNetOp, tab: Tableau, saved, a_next: torch.Tensor, dt
     dk_extra: optional {stage: (tensor, coef)} added into dk_stage (dopri5 dense-output terms)."""
     s = tab.s
     dys: List[Optional[torch.Tensor]] = [None] * s
+    L = len(op.layers)
+    shape = (s,) + tuple(a_next.shape)
+    dk_arena = torch.empty(shape, dtype=a_next.dtype, device=a_next.device)
+    g_arenas = None
+    if L > 1 and all(c.in_channels == a_next.shape[3] for c, _ in op.layers[1:]):
+        g_arenas = [torch.empty(shape, dtype=a_next.dtype, device=a_next.device) for _ in range(L - 1)]
+    was_deferred, sink.deferred = sink.deferred, True
     for i in range(s - 1, -1, -1):
         ins, coefs = [a_next], [tab.c_sol[i]]
         for m in range(i + 1, s):
@@ -111,9 +128,12 @@ def rk_step_bwd(be, op: ConvNetOp, tab: Tableau, saved, a_next: torch.Tensor, dt
                 coefs.append(b)
         if all(c == 0.0 for c in coefs):
             continue                                   # stage does not influence y_next
-        dk = torch.empty_like(a_next)
+        dk = dk_arena[i]
         _lin(be, dk, ins, coefs, dt_dev=dt_dev, dt_from=0)
-        dys[i] = op.bwd(saved[i], dk, sink)
+        dys[i] = op.bwd(saved[i], dk, sink, gbufs=[g[i] for g in g_arenas] if g_arenas is not None else None)
+    sink.deferred = was_deferred
+    if not was_deferred:
+        sink.flush()
     terms = [a_next] + [d for d in dys if d is not None] + list(extra)
     res = out if out is not None else torch.empty_like(a_next)
     while len(terms) > 8:                              # odex_lincomb takes <= 8 operands

@@ -124,7 +124,9 @@ def test_two_rank_gloo_shared_steps_and_grad_bucket(mode):
         assert sum(res[0][3]) >= st.n_accept + st.n_reject
         assert (sharded - sol).abs().max() <= 5e-3 * sol.abs().max()
     assert res[0][5] == g.numel() * 4
-    assert torch.allclose(res[0][4], g, rtol=1e-4, atol=1e-6) and torch.allclose(res[1][4], g, rtol=1e-4, atol=1e-6)
+    # fp32 summation order differs between (3 + 2 samples, summed by the bucket) and one pass over 5 samples
+    atol = 1e-5 * float(g.abs().max())
+    assert torch.allclose(res[0][4], g, rtol=1e-4, atol=atol) and torch.allclose(res[1][4], g, rtol=1e-4, atol=atol)
 
 
 def test_shard_range_ragged_and_empty():
