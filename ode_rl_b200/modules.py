@@ -242,9 +242,16 @@ class _EncoderFn(torch.autograd.Function):
         hs = torch.empty((T, B, H, W, C), dtype=torch.float32, device=x.device)
         h = torch.zeros((B, H, W, C), dtype=torch.float32, device=x.device)
         saved = []
+        # saved activations of f over the T iterations in [T, B, ...] arenas: the deferred weight gradients of a layer then
+        # run as one launch over all iterations (GradSink.add_wgrad)
+        arenas = None
+        Lf = len(f_op.layers)
+        if save and Lf > 1 and all(c.out_channels == C for c, _ in f_op.layers[:-1]):
+            arenas = [torch.empty((T, B, H, W, C), dtype=torch.float32, device=x.device) for _ in range(Lf - 1)]
         for n, i in enumerate(order):
             ht = torch.empty_like(h)
-            r = f_op.fwd(h, save=save, out=ht, res=h, alpha=1.0, alpha_dev=deltas[n:n + 1])
+            r = f_op.fwd(h, save=save, out=ht, res=h, alpha=1.0, alpha_dev=deltas[n:n + 1],
+                         bufs=[a_[n] for a_ in arenas] if arenas is not None else None)
             g = g_op.fwd(x[i], ht, save=save, out=hs[n])
             if save:
                 saved.append((r[1], g[1]))
@@ -264,6 +271,12 @@ class _EncoderFn(torch.autograd.Function):
         T, B, H, W, Cx = ctx.x_shape
         C = g_op.C
         sink = GradSink()
+        sink.deferred = True                                  # weight gradients of f: batched over the iterations at the end
+        Lf = len(f_op.layers)
+        dk_arena = torch.empty((T, B, H, W, C), dtype=torch.float32, device=d.device)
+        g_arenas = None
+        if Lf > 1 and all(c.in_channels == C for c, _ in f_op.layers[1:]):
+            g_arenas = [torch.empty((T, B, H, W, C), dtype=torch.float32, device=d.device) for _ in range(Lf - 1)]
         DX = torch.empty((T, B, H, W, Cx + C), dtype=torch.float32, device=d.device)   # [dx_i | dh~] per frame
         a = None                                              # adjoint of h after iteration n
         for n in range(T - 1, -1, -1):
@@ -278,22 +291,23 @@ class _EncoderFn(torch.autograd.Function):
             dht = D[..., Cx:]                                 # adjoint of h~ (row stride Cx+C)
             if n == 0:
                 # h_0 = 0 is a constant: only the parameter gradients of f(0) remain
-                dk = _scaled_copy(be, dht, deltas[n:n + 1])
-                f_op.bwd(sv_f, dk, sink, need_dx=False)
+                dk = _scaled_copy(be, dht, deltas[n:n + 1], out=dk_arena[n])
+                f_op.bwd(sv_f, dk, sink, need_dx=False, gbufs=[g_[n] for g_ in g_arenas] if g_arenas is not None else None)
                 a = None
             else:
-                dk = _scaled_copy(be, dht, deltas[n:n + 1])
-                a = f_op.bwd(sv_f, dk, sink, res=dht)
+                dk = _scaled_copy(be, dht, deltas[n:n + 1], out=dk_arena[n])
+                a = f_op.bwd(sv_f, dk, sink, res=dht, gbufs=[g_[n] for g_ in g_arenas] if g_arenas is not None else None)
             saved[n] = None
         ctx.saved = None
         dx = from_nhwc(DX[..., :Cx]) if ctx.needs_input_grad[4] else None
         return (None, None, None, None, dx, None) + sink.result(ctx.params)
 
 
-def _scaled_copy(be, view: torch.Tensor, dt_dev: torch.Tensor) -> torch.Tensor:
+def _scaled_copy(be, view: torch.Tensor, dt_dev: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """dense copy of an NHWC channel-slice view scaled by *dt_dev: the adjoint of `f(h) * dt` w.r.t. f(h)."""
     dense = view.contiguous() if not view.is_contiguous() else view
-    out = torch.empty_like(dense)
+    if out is None:
+        out = torch.empty_like(dense)
     be.lincomb(out, [dense], [1.0], dtmask=1, dt_dev=dt_dev)
     return out
 
