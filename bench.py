@@ -30,7 +30,7 @@ FEVAL_FLOPS = 94371840            # per sample, 5 x conv3x3 64->64 at 16x16 (SUR
 CONV3_FLOPS = 2 * 256 * 64 * 576  # one 3x3 64->64 conv, per sample
 
 
-NET_TRAFFIC_B128 = None      # bytes; filled from the ncu capture of convnet_tc_kernel
+NET_TRAFFIC_B128 = 10488704  # bytes per launch at batch 128: dram read 9.95 MB + written 0.54 MB (ncu --set full, profiles/r01_final_ncu.md)
 
 
 def parse():
@@ -308,9 +308,9 @@ def main():
         roof = {"bound": "tensor", "kernel": "convnet_tc_kernel (5 x conv3x3 64->64 fused, 3xTF32, tcgen05 kind::tf32)", "achieved": ach,
                 "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
                 # dram__bytes_read.sum + dram__bytes_write.sum of one launch at batch 128 (ncu --set full,
-                # profiles/r01_convnet_ncu.md), scaled with the batch; None until that capture exists
+                # profiles/r01_final_ncu.md), scaled with the batch; None until that capture exists
                 "traffic": NET_TRAFFIC_B128 and int(NET_TRAFFIC_B128 * B / 128),
-                "traffic_source": "profiles/r01_convnet_ncu.md (ncu --set full, per launch)",
+                "traffic_source": "profiles/r01_final_ncu.md (ncu --set full, per launch)",
                 "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (of measured)" if peaks else "fallback 1.4 PF (of fallback)",
                 "note": "achieved counts algorithmic FLOPs once (2*M*N*K per layer, 5 layers per launch); the kernel issues 3 TF32 "
                         "MMAs per useful one and TF32 runs at half the bf16 rate, so frac*6 is the share of tensor issue slots "

@@ -181,3 +181,35 @@ def test_c_abi_library_exports_every_header_symbol():
     assert l.odex_version() == _lib.ODEX_VERSION
     assert ctypes.sizeof(_lib.DopriState) <= _lib.STATE_HEAD_BYTES
     assert l.odex_dopri_state_bytes() > _lib.STATE_HEAD_BYTES
+
+
+def test_grad_sink_merges_consecutive_slices(fake_backend):
+    """GradSink.add_wgrad while deferred: requests whose (x, dy) are consecutive dense slices of one buffer become ONE
+    launch over n*B images; anything else stays a launch of its own; the accumulated gradient equals the eager one."""
+    import torch.nn as nn
+    from ode_rl_b200.ops import GradSink, _slice_runs
+
+    torch.manual_seed(3)
+    conv = nn.Conv2d(8, 8, 3, padding=1)
+    xa, da = torch.randn(4, 2, 6, 6, 8), torch.randn(4, 2, 6, 6, 8)          # [s, B, H, W, C] arenas
+    lone_x, lone_d = torch.randn(2, 6, 6, 8), torch.randn(2, 6, 6, 8)
+    items = [(xa[2], da[2]), (lone_x, lone_d), (xa[0], da[0]), (xa[1], da[1]), (xa[3], da[1])]   # last: dy not consecutive
+    runs = _slice_runs(items)
+    sizes = sorted(r[0].shape[0] for r in runs)
+    assert sizes == [2, 2, 6]                                                # 3 slices merged, two singles
+    merged = [r for r in runs if r[0].shape[0] == 6][0]
+    assert torch.equal(merged[0], xa[:3].reshape(6, 6, 6, 8)) and torch.equal(merged[1], da[:3].reshape(6, 6, 6, 8))
+
+    def total(deferred):
+        sink = GradSink()
+        sink.deferred = deferred
+        n0 = fake_backend.launches
+        for x, d in items:
+            sink.add_wgrad(conv, x, d)
+        gw, gb = sink.result([conv.weight, conv.bias])
+        return gw, gb, fake_backend.launches - n0
+
+    gw0, gb0, l0 = total(False)
+    gw1, gb1, l1 = total(True)
+    assert l1 == l0 - 2                                                      # 5 launches -> 3 (+ the same unpack)
+    assert rel_err(gw1, gw0) < 1e-6 and rel_err(gb1, gb0) < 1e-6
