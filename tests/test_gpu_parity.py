@@ -189,3 +189,32 @@ def test_cuda_graph_training_step_matches_eager():
     assert max(abs(a - b) for a, b in zip(losses1, losses2[2:])) < 1e-5 * abs(losses2[-1]) + 1e-7
     for (n1, p1), (_, p2) in zip(m1.named_parameters(), m2.named_parameters()):
         assert rel_err(p1, p2) < 1e-4, n1
+
+
+def test_vidode_shapes_encoder_and_solver():
+    """BASELINE configs[4] shapes (models/VidODE.py:53-57): 128 latent channels on 32x32, f = conv3x3 128->64, 64->64,
+    64->64, 64->128, ConvGRU 5x5 with 256 -> 256 gates.  Small batch / few frames so the CPU oracle finishes in seconds;
+    the kernels take their tensor-core paths where the shape allows (conv_tc v1 / conv_tc2) and the exact FFMA path for
+    the N = 256 gates convolution.  Same bars as config A: outputs <= 1e-5, gradients <= 1e-4 (tanh: smooth)."""
+    torch.manual_seed(0)
+    f = make_ode_func(odex, C=128, n_layers=2, n_units=64, nonlinear="tanh")
+    cell = odex.ODEConvGRUCell(f, None, (32, 32), 128).to(DEV)
+    obs, tp = timesteps(3, 3)
+    torch.manual_seed(9)
+    xc = torch.randn(3, 1, 128, 32, 32)
+    x = xc.to(DEV).requires_grad_(True)
+    mean, std = cell(x, obs.to(DEV))
+    solver = odex.DiffEqSolver(cell.ode_func, "rk4")
+    sol = solver(mean, tp.to(DEV))
+    w1, w2 = torch.randn(sol.shape), torch.randn(std.shape)
+    ((sol * w1.to(DEV)).sum() + (std * w2.to(DEV)).sum()).backward()
+    ps = {k: v.requires_grad_(True) for k, v in _sd_cpu(cell).items()}
+    x1 = xc.clone().requires_grad_(True)
+    rm, rs = refmodel.encoder_z0(ps, x1, obs, act="tanh")
+    rsol = refmodel.diffeq_solver(ps, rm, tp, "rk4", act="tanh")
+    ((rsol * w1).sum() + (rs * w2).sum()).backward()
+    assert rel_err(mean, rm) < 1e-5 and rel_err(std, rs) < 1e-5 and rel_err(sol, rsol) < 1e-5
+    errs = {n: rel_l2(p.grad, ps[n].grad) for n, p in cell.named_parameters()}
+    errs["x"] = rel_l2(x.grad, x1.grad)
+    print(errs)
+    assert max(errs.values()) < 1e-4, errs
