@@ -293,3 +293,32 @@ def test_convnet_fused_chain_matches_layerwise(be, L, B, act):
     be.convnet(x, [be.pack_weights(w, False, True) for w in ws], bs, acts, [None] * L, [0] * L, o2, skip=skip)
     torch.cuda.synchronize()
     assert float((o2[-1] - 7.0).abs().max()) == 0.0
+
+
+def test_convnet_fused_chain_is_deterministic(be):
+    """The fused chain recycles its shared-memory planes between layers (operands overwritten in place, TMA loads into
+    retired planes, TMA stores reading planes the next layer is already using).  A missing fence or barrier would show up
+    as run-to-run differences: 40 launches on the same input, forward and data-gradient form, must agree bit for bit, with
+    another kernel (different shared-memory contents) in between."""
+    torch.manual_seed(21)
+    B, L = 148 * 2 + 5, 5
+    x = torch.randn(B, 16, 16, 64, device="cuda")
+    ws_f = [be.pack_weights(torch.randn(64, 64, 3, 3, device="cuda") / 24.0, False, True) for _ in range(L)]
+    ws_d = [be.pack_weights(torch.randn(64, 64, 3, 3, device="cuda") / 24.0, True, True) for _ in range(L)]
+    bs = [torch.randn(64, device="cuda") * 0.1 for _ in range(L)]
+    masks = [torch.randn(B, 16, 16, 64, device="cuda") for _ in range(L)]
+    junk = torch.randn(B, 16, 16, 64, device="cuda")
+    first = None
+    for it in range(40):
+        outs_f = [torch.empty_like(x) for _ in range(L)]
+        outs_d = [torch.empty_like(x) for _ in range(L)]
+        be.convnet(x, ws_f, bs, [ACT_RELU] * (L - 1) + [ACT_NONE], [None] * (L - 1) + [x], [0] * (L - 1) + [3], outs_f, alpha=0.1)
+        be.convnet(outs_f[-1], ws_d, [None] * L, [ACT_NONE] * L, masks[:L - 1] + [x], [1] * (L - 1) + [3], outs_d)
+        be.lincomb(junk, [junk, outs_d[-1]], [0.5, 0.5])
+        torch.cuda.synchronize()
+        cur = [o.clone() for o in outs_f + outs_d]
+        if first is None:
+            first = cur
+        else:
+            for k, (a, b) in enumerate(zip(cur, first)):
+                assert torch.equal(a, b), "run %d differs from run 0 in output %d" % (it, k)
