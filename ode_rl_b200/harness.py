@@ -114,4 +114,4 @@ class GraphedTrainStep:
         if self.grad_hook is not None:
             self.grad_hook()
             self.opt.step()
-        return self.loss
+        return self.loss.detach()
