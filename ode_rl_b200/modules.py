@@ -46,6 +46,17 @@ def create_convnet(n_inputs, n_outputs, n_layers=1, n_units=128, downsize=False,
     return nn.Sequential(*layers)
 
 
+def _empty_result(shape, like: torch.Tensor, params) -> torch.Tensor:
+    """Result for an EMPTY batch (a ragged shard may hold no sample): zeros of `shape`, wired into autograd so that
+    backward() hands zero gradients to the inputs and parameters, as torch's own conv does for a 0-sample batch.
+    No kernel runs (the C ABI rejects n = 0)."""
+    out = torch.zeros(shape, dtype=torch.float32, device=like.device)
+    for t in [like] + list(params):
+        if t is not None and t.requires_grad:
+            out = out + t.sum() * 0.0
+    return out
+
+
 class _ConvNetFn(torch.autograd.Function):
     """y = f(x) for a conv stack, logical NCHW in/out."""
 
@@ -93,7 +104,10 @@ class ODEFunc(nn.Module):
     def forward(self, t_local, y, backwards=False):
         """dy/dt at y; autonomous: t_local is ignored (modules/DiffEqSolver.py:71-80)."""
         op = self.op()
-        grad = _ConvNetFn.apply(op, y, *op.params())
+        if y.shape[0] == 0:
+            grad = _empty_result((0, op.c_out) + tuple(y.shape[2:]), y, op.params())
+        else:
+            grad = _ConvNetFn.apply(op, y, *op.params())
         if backwards:
             grad = -grad
         return grad
@@ -122,6 +136,13 @@ class DiffEqSolver(nn.Module):
         if not isinstance(self.ode_func, ODEFunc):
             raise NotImplementedError("DiffEqSolver: the CUDA path integrates ode_rl_b200.ODEFunc conv stacks only")
         op = self.ode_func.op()
+        if y0.shape[0] == 0:
+            if method not in FIXED and method != 'dopri5':
+                raise ValueError('Invalid method "{}" (euler, rk4 and dopri5 are supported)'.format(method))
+            if method == 'dopri5' and self.reduce_fn is not None:
+                raise ValueError("DiffEqSolver(dopri5, sharded): an empty shard cannot take part in the batch-shared step "
+                                 "control; give every rank at least one sample")
+            return _empty_result((t.numel(), 0) + tuple(y0.shape[1:]), y0, op.params())
         if method in FIXED:
             return odeint_fixed(op, y0, t, method)
         if method == 'dopri5':
@@ -218,7 +239,10 @@ class ConvGRUCell(nn.Module):
                 x = torch.zeros(h_cur.size(0), self.input_channels, self.height, self.width, device=dev)
             else:
                 x = input_tensor[index, ...]
-            h_next = _GruStepFn.apply(op, x, h_cur, *op.params())
+            if h_cur.size(0) == 0:
+                h_next = _empty_result(tuple(h_cur.shape), h_cur, [x] + op.params())
+            else:
+                h_next = _GruStepFn.apply(op, x, h_cur, *op.params())
             output_inner.append(h_next)
             h_cur = h_next
         return torch.stack(output_inner, dim=dim), h_next
@@ -339,7 +363,10 @@ class ODEConvGRUCell(nn.Module):
     def forward(self, inputs, timesteps, mask=None):    # inputs has time dim first
         last_yi, _ = self.run_ode_conv_gru(inputs, timesteps, mask=mask)
         op = self._transform_op()
-        trans_last_yi = _ConvNetFn.apply(op, last_yi, *op.params())     # (b, self.z0_dim*2, h, w)
+        if last_yi.shape[0] == 0:
+            trans_last_yi = _empty_result((0, op.c_out) + tuple(last_yi.shape[2:]), last_yi, op.params())
+        else:
+            trans_last_yi = _ConvNetFn.apply(op, last_yi, *op.params())     # (b, self.z0_dim*2, h, w)
         mean_z0, std_z0 = torch.split(trans_last_yi, self.z0_dim, dim=1)
         std_z0 = std_z0.abs()
         return mean_z0, std_z0
@@ -372,7 +399,10 @@ class ODEConvGRUCell(nn.Module):
         deltas = self._deltas(timesteps, inputs.device, tuple(order))
         f_op, g_op = self.ode_func.op(), self.cgru_cell.op()
         params = f_op.params() + g_op.params()
-        hs = _EncoderFn.apply(f_op, g_op, len(f_op.params()), order, inputs, deltas, *params)   # [T,B,C,H,W]
+        if b == 0:
+            hs = _empty_result((t, 0, g_op.C, h, w), inputs, params)
+        else:
+            hs = _EncoderFn.apply(f_op, g_op, len(f_op.params()), order, inputs, deltas, *params)   # [T,B,C,H,W]
         yi = hs[t - 1]
         latent_ys = hs.permute(1, 0, 2, 3, 4)   # (b, t, c, h, w)
         return yi, latent_ys

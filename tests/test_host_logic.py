@@ -213,3 +213,28 @@ def test_grad_sink_merges_consecutive_slices(fake_backend):
     gw1, gb1, l1 = total(True)
     assert l1 == l0 - 2                                                      # 5 launches -> 3 (+ the same unpack)
     assert rel_err(gw1, gw0) < 1e-6 and rel_err(gb1, gb0) < 1e-6
+
+
+def test_empty_batch_returns_empty_results_with_zero_grads(fake_backend):
+    """A ragged shard may hold no sample (parallel.shard_range(2, r, 4)): the modules return empty tensors of the right
+    shape without launching anything, and backward() gives the parameters zero gradients (what torch's conv does for a
+    0-sample batch).  A sharded dopri5 solver refuses instead: every rank must contribute to the shared step control."""
+    f = make_ode_func(odex, C=32, n_units=32)
+    cell = odex.ODEConvGRUCell(f, None, (8, 16), 32)
+    obs, tp = timesteps(3, 3)
+    n0 = fake_backend.launches
+    for method in ("euler", "rk4", "dopri5"):
+        solver = odex.DiffEqSolver(f, method)
+        z0 = torch.zeros(0, 32, 8, 16, requires_grad=True)
+        sol = solver(z0, tp)
+        assert sol.shape == (3, 0, 32, 8, 16)
+        sol.sum().backward()
+        assert all(p.grad is not None and float(p.grad.abs().sum()) == 0.0 for p in solver.parameters())
+    mean, std = cell(torch.zeros(3, 0, 32, 8, 16), obs)
+    assert mean.shape == (0, 32, 8, 16) and std.shape == (0, 32, 8, 16)
+    assert f(None, torch.zeros(0, 32, 8, 16)).shape == (0, 32, 8, 16)
+    assert fake_backend.launches == n0
+    sharded = odex.DiffEqSolver(f, "dopri5")
+    sharded.reduce_fn = lambda t: t
+    with pytest.raises(ValueError):
+        sharded(torch.zeros(0, 32, 8, 16), tp)
