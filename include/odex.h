@@ -69,7 +69,8 @@ int odex_pack_weights(const float* w_oihw, int N, int C, int R, int dgrad, int t
  * modules/ODEConvGRUCell.py:54,57 (res/alpha epilogue); the 1x1 convs of modules/ODEConvGRUCell.py:27-30;
  * and, with dgrad-packed weights + dact, the autograd conv backward-data of all of those.
  * Shapes: R in {1,3,5}; W % 16 == 0, H % 8 == 0; c0, c1, N multiples of 4 (SIMT).  TC additionally needs
- * c0 (== c1 if present) % 64 == 0, N in {64, 128}, W a power of two <= 128 with (128/W) | H. */
+ * c0 (== c1 if present) % 64 == 0, N = 64 or a multiple of 128 (blocks of 128 output channels, one launch each),
+ * W a power of two <= 128 with (128/W) | H. */
 typedef struct odex_conv_desc {
     const float* x0; int ld0; int c0;
     const float* x1; int ld1; int c1;       /* x1 == NULL: single source */

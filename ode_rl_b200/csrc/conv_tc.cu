@@ -55,7 +55,8 @@ static int make_w_map(CUtensorMap* tm, const float* w, long rows) {
 
 bool conv_tc_supported(const odex_conv_desc* d) {
     if (!d->w_tc) return false;
-    if (d->N != 64 && d->N != 128) return false;
+    // more than 128 output channels: N-blocks of 128, one launch each (the VidODE ConvGRU gates: 256)
+    if (d->N != 64 && (d->N % 128 != 0 || d->N > 1024)) return false;
     if (d->R != 1 && d->R != 3 && d->R != 5) return false;
     if (d->c0 % 64 != 0) return false;
     if (d->x1 && d->c1 != d->c0) return false;
@@ -65,8 +66,10 @@ bool conv_tc_supported(const odex_conv_desc* d) {
     return true;
 }
 
+// n_total: output channels of the whole convolution (the packed weights hold [hi ; lo] rows of ALL of them per k-block);
+// n_off: first output channel of this launch.  d describes the N-block (N, out, bias, res, dact already offset).
 template <int N>
-static int launch_tc(const odex_conv_desc* d, cudaStream_t s) {
+static int launch_tc(const odex_conv_desc* d, cudaStream_t s, int n_total, int n_off) {
     constexpr int kSmemMax = 232448;
     ConvGeom g;
     g.B = d->B; g.H = d->H; g.W = d->W;
@@ -96,8 +99,9 @@ static int launch_tc(const odex_conv_desc* d, cudaStream_t s) {
     } else {
         tmA1 = tmA0;
     }
-    const long rows = static_cast<long>(G) * d->R * d->R * 2 * 2 * N;
+    const long rows = static_cast<long>(G) * d->R * d->R * 2 * 2 * n_total;
     if (int rc = make_w_map(&tmB, d->w_tc, rows)) return rc;
+    g.w_rows = 2 * n_total; g.w_lo = n_total; g.w_off = n_off;
 
     ConvEpilogue ep;
     ep.bias = d->bias; ep.out = d->out; ep.ldo = d->ldo;
@@ -123,8 +127,17 @@ int launch_conv_tc(const odex_conv_desc* d, cudaStream_t s) {
     static const bool no_v2 = getenv("ODEX_CONV_TC_V1") != nullptr;
     if (!no_v2 && conv_tc2_supported(d)) return launch_conv_tc2(d, s);
     if (!conv_tc_supported(d)) return fail(ODEX_E_UNSUPPORTED, "conv(tc): shape not supported (N=%d R=%d c0=%d c1=%d HxW=%dx%d)", d->N, d->R, d->c0, d->c1, d->H, d->W);
-    if (d->N == 64) return launch_tc<64>(d, s);
-    return launch_tc<128>(d, s);
+    if (d->N == 64) return launch_tc<64>(d, s, 64, 0);
+    for (int n_off = 0; n_off < d->N; n_off += 128) {
+        odex_conv_desc b = *d;
+        b.N = 128;
+        b.out = d->out + n_off;
+        if (d->bias) b.bias = d->bias + n_off;
+        if (d->res) b.res = d->res + n_off;
+        if (d->dact) b.dact = d->dact + n_off;
+        if (int rc = launch_tc<128>(&b, s, d->N, n_off)) return rc;
+    }
+    return 0;
 }
 
 }  // namespace odex

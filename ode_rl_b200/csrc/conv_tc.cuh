@@ -31,6 +31,9 @@ struct ConvGeom {
     int TH;            // rows per tile = 128 / W
     int log2W;
     int halo_stages;   // 1 or 2 (2 only useful with more than one 64-channel group)
+    int w_rows;        // packed-weight rows per k-block = 2 * (output channels of the whole convolution)
+    int w_lo;          // row offset of the lo half inside a k-block = output channels of the whole convolution
+    int w_off;         // first output channel of this launch (N-blocks of 128 when the convolution has more than 128)
     int halo_bytes;    // per 32-channel chunk, rounded up to 1024
 };
 
@@ -156,10 +159,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                     mbar_wait(bar_b_empty + 8 * sb, pb ^ 1u);
                     mbar_arrive_expect_tx(bar_b_full + 8 * sb, Cfg::kBStageBytes);
                     if (N == 128) {   // box rows are limited to 256: two boxes of N rows
-                        tma_load_2d(bst0 + sb * Cfg::kBStageBytes, &tmB, bar_b_full + 8 * sb, 0, kb * 2 * N);
-                        tma_load_2d(bst0 + sb * Cfg::kBStageBytes + N * 128, &tmB, bar_b_full + 8 * sb, 0, kb * 2 * N + N);
+                        tma_load_2d(bst0 + sb * Cfg::kBStageBytes, &tmB, bar_b_full + 8 * sb, 0, kb * g.w_rows + g.w_off);
+                        tma_load_2d(bst0 + sb * Cfg::kBStageBytes + N * 128, &tmB, bar_b_full + 8 * sb, 0, kb * g.w_rows + g.w_lo + g.w_off);
                     } else {
-                        tma_load_2d(bst0 + sb * Cfg::kBStageBytes, &tmB, bar_b_full + 8 * sb, 0, kb * 2 * N);
+                        tma_load_2d(bst0 + sb * Cfg::kBStageBytes, &tmB, bar_b_full + 8 * sb, 0, kb * g.w_rows);
                     }
                     if (++sb == SB) { sb = 0; pb ^= 1u; }
                 }

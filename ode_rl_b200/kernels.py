@@ -59,7 +59,7 @@ class PackedConv:
 
 def tc_shape_ok(N: int, c0: int, c1: int, H: int, W: int, R: int) -> bool:
     """Mirror of conv_tc_supported() in csrc/conv_tc.cu."""
-    if N not in (64, 128) or R not in (1, 3, 5):
+    if (N != 64 and (N % 128 != 0 or N > 1024)) or R not in (1, 3, 5):     # > 128: N-blocks of 128, one launch each
         return False
     if c0 % 64 != 0 or (c1 and c1 != c0):
         return False

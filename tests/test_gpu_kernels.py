@@ -39,6 +39,8 @@ CONV_CASES = [
     (1, 32, 32, 64, 0, 128, 3),
     (1, 8, 8, 64, 0, 64, 3),
     (2, 16, 16, 128, 0, 128, 5),
+    (1, 32, 32, 128, 128, 256, 5),      # VidODE ConvGRU gates: two N-blocks of 128
+    (2, 16, 16, 256, 0, 256, 3),
 ]
 
 
