@@ -7,10 +7,12 @@ tree is available, models/ODEConvGRU.py itself can be used instead (INTEGRATION.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.nn as nn
 
-from .modules import DiffEqSolver, ODEConvGRUCell, ODEFunc
+from .modules import DiffEqSolver, ODEConvGRUCell, ODEFunc, conv_transpose4x4s2, conv_transpose4x4s2_supported
 
 
 class _Encoder(nn.Module):          # models/ODEConvGRU.py:101-119 with n_downs == 2
@@ -28,8 +30,14 @@ class _Decoder(nn.Module):          # models/ODEConvGRU.py:122-140 with n_ups ==
         super().__init__()
         act = nn.LeakyReLU(negative_slope=0.2, inplace=True)
         self.decoder = nn.Sequential(nn.ConvTranspose2d(n_inputs, 32, 4, 2, 1), act, nn.ConvTranspose2d(32, out_ch, 4, 2, 1))
+        self.fast_first_layer = os.environ.get("ODEX_TORCH_DECODER") is None
 
     def forward(self, x):
+        d0 = self.decoder[0]
+        if self.fast_first_layer and conv_transpose4x4s2_supported(x, d0):
+            # the 64 -> 32 transposed convolution (60 % of the torch-side time under exact-fp32 cuDNN) as a
+            # 3x3 convolution to 4 x 32 phase channels on the tcgen05 path; same parameters, fp32-level result
+            return self.decoder[2](self.decoder[1](conv_transpose4x4s2(x, d0)))
         return self.decoder(x)
 
 

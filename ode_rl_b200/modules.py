@@ -20,6 +20,7 @@ import torch
 import torch.nn as nn
 
 from . import kernels as K
+from .kernels import ACT_NONE, CONV_TC
 from .ops import ConvNetOp, GradSink, GruOp, from_nhwc, to_nhwc
 from .solver import FIXED, odeint_dopri5, odeint_fixed
 
@@ -80,6 +81,113 @@ class _ConvNetFn(torch.autograd.Function):
         sink = GradSink()
         dx = ctx.op.bwd(ctx.saved, d, sink, need_dx=ctx.needs_input_grad[1])
         return (None, from_nhwc(dx) if dx is not None else None) + sink.result(ctx.params)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# ConvTranspose2d(k=4, s=2, p=1) on the tensor-core convolution (the first layer of ConvDecode,
+# models/ODEConvGRU.py:122-140, is 60 % of the torch-side time of a training step under exact-fp32 cuDNN).
+# out[co, 2Y+a, 2X+b] depends on the 2x2 inputs around (Y, X) selected by the phase (a, b): the four phases together are
+# ONE 3x3 "same" convolution Cin -> 4*Cout on the input grid (channel = (a, b, co); 4 of the 9 taps of each phase are
+# non-zero) followed by a depth-to-space reshuffle.  kh = 3 - 2r + a (r the 3x3 row tap), same for kw / s / b.
+_CT_K = ((3, 1, -1), (-1, 2, 0))            # _CT_K[a][r] = kh (or -1: the tap does not reach this phase)
+
+
+def _ct_index(device):
+    idx = torch.zeros(2, 2, 3, 3, dtype=torch.long)
+    msk = torch.zeros(2, 2, 3, 3)
+    for a in range(2):
+        for b in range(2):
+            for r in range(3):
+                for q in range(3):
+                    kh, kw = _CT_K[a][r], _CT_K[b][q]
+                    if kh >= 0 and kw >= 0:
+                        idx[a, b, r, q] = kh * 4 + kw
+                        msk[a, b, r, q] = 1.0
+    return idx.reshape(-1).to(device), msk.reshape(1, 1, -1).to(device)
+
+
+_CT_CACHE: dict = {}
+
+
+def _ct_w3(wt: torch.Tensor) -> torch.Tensor:
+    """ConvTranspose2d weight [Cin, Cout, 4, 4] -> the equivalent 3x3 correlation weight [4*Cout, Cin, 3, 3]."""
+    key = str(wt.device)
+    if key not in _CT_CACHE:
+        _CT_CACHE[key] = _ct_index(wt.device)
+    idx, msk = _CT_CACHE[key]
+    cin, cout = wt.shape[0], wt.shape[1]
+    g = wt.detach().permute(1, 0, 2, 3).reshape(cout, cin, 16)[:, :, idx] * msk          # [Cout, Cin, (a,b,r,s)]
+    return g.reshape(cout, cin, 2, 2, 3, 3).permute(2, 3, 0, 1, 4, 5).reshape(4 * cout, cin, 3, 3).contiguous()
+
+
+def _ct_dwt(dw3: torch.Tensor, cin: int, cout: int) -> torch.Tensor:
+    """Adjoint of _ct_w3: every (kh, kw) of the 4x4 kernel is used by exactly one (phase, tap)."""
+    g = dw3.reshape(2, 2, cout, cin, 3, 3)
+    sel = ((1, 2), (0, 1), (1, 1), (0, 0))           # kh -> (a, r)
+    rows = []
+    for kh in range(4):
+        a, r = sel[kh]
+        rows.append(torch.stack([g[a, sel[kw][0], :, :, r, sel[kw][1]] for kw in range(4)], dim=-1))   # [Cout, Cin, 4]
+    return torch.stack(rows, dim=-2).permute(1, 0, 2, 3).contiguous()                                  # [Cin, Cout, 4, 4]
+
+
+class _ConvT4x4s2Fn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor]):
+        be = K.backend()
+        be.require(x)
+        xn = to_nhwc(x.detach().float())                      # [n, H, W, Cin], zero-copy for a channels-last view
+        if not xn.is_contiguous():
+            xn = xn.contiguous()
+        n, H, W, cin = xn.shape
+        cout = weight.shape[1]
+        w3 = _ct_w3(weight.float())
+        b3 = bias.detach().float().repeat(4) if bias is not None else None
+        P = torch.empty((n, H, W, 4 * cout), dtype=torch.float32, device=xn.device)
+        be.conv2d(xn, None, None, be.pack_weights(w3, dgrad=False, tc=True), 4 * cout, 3, b3, ACT_NONE, P, impl=CONV_TC)
+        ctx.save_for_backward(xn, w3)
+        ctx.has_bias = bias is not None
+        # depth-to-space: P[n, Y, X, (a, b, co)] -> out[n, co, 2Y+a, 2X+b]
+        return P.view(n, H, W, 2, 2, cout).permute(0, 5, 1, 3, 2, 4).reshape(n, cout, 2 * H, 2 * W)
+
+    @staticmethod
+    def backward(ctx, dout):
+        be = K.backend()
+        xn, w3 = ctx.saved_tensors
+        n, H, W, cin = xn.shape
+        cout = w3.shape[0] // 4
+        dP = dout.float().reshape(n, cout, H, 2, W, 2).permute(0, 2, 4, 3, 5, 1).reshape(n, H, W, 4 * cout).contiguous()
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dxn = torch.empty((n, H, W, cin), dtype=torch.float32, device=xn.device)
+            be.conv2d(dP, None, None, be.pack_weights(w3, dgrad=True, tc=True), cin, 3, None, ACT_NONE, dxn, impl=CONV_TC)
+            dx = from_nhwc(dxn)
+        if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
+            dwp = torch.zeros((9, 4 * cout, cin), dtype=torch.float32, device=xn.device)
+            db3 = torch.zeros((4 * cout,), dtype=torch.float32, device=xn.device)
+            be.conv2d_wgrad_packed(xn, None, dP, 3, dwp, db3)
+            dw3 = torch.zeros((4 * cout, cin, 3, 3), dtype=torch.float32, device=xn.device)
+            be.wgrad_unpack(dwp, dw3)
+            dw = _ct_dwt(dw3, cin, cout)
+            if ctx.has_bias:
+                db = db3.view(4, cout).sum(0)
+        return dx, dw, db
+
+
+def conv_transpose4x4s2_supported(x: torch.Tensor, m: nn.Module) -> bool:
+    """True when `m` is a ConvTranspose2d(k=4, s=2, p=1) that the tensor-core convolution can take for input x."""
+    if not (isinstance(m, nn.ConvTranspose2d) and m.kernel_size == (4, 4) and m.stride == (2, 2) and m.padding == (1, 1)
+            and m.output_padding == (0, 0) and m.dilation == (1, 1) and m.groups == 1):
+        return False
+    if not x.is_cuda or x.dim() != 4 or x.shape[0] == 0:
+        return False
+    return K.tc_shape_ok(4 * m.out_channels, m.in_channels, 0, x.shape[2], x.shape[3], 3)
+
+
+def conv_transpose4x4s2(x: torch.Tensor, m: nn.ConvTranspose2d) -> torch.Tensor:
+    """F.conv_transpose2d(x, m.weight, m.bias, stride=2, padding=1) for a 4x4 kernel on the 3xTF32 tensor-core path
+    (same parameters, same result to fp32 rounding, hand-written backward)."""
+    return _ConvT4x4s2Fn.apply(x, m.weight, m.bias)
 
 
 class ODEFunc(nn.Module):

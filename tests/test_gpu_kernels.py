@@ -324,3 +324,25 @@ def test_convnet_fused_chain_is_deterministic(be):
         else:
             for k, (a, b) in enumerate(zip(cur, first)):
                 assert torch.equal(a, b), "run %d differs from run 0 in output %d" % (it, k)
+
+
+def test_conv_transpose4x4s2_matches_torch():
+    """ConvDecode's first layer (ConvTranspose2d(64, 32, 4, 2, 1), models/ODEConvGRU.py:122-140) on the tensor-core
+    convolution (modules.conv_transpose4x4s2) against torch's exact-fp32 operator: output and the three gradients."""
+    import torch.nn as nn
+    import torch.nn.functional as F
+    from ode_rl_b200.modules import conv_transpose4x4s2, conv_transpose4x4s2_supported
+
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(2)
+    m = nn.ConvTranspose2d(64, 32, 4, 2, 1).cuda()
+    x = torch.randn(10, 16, 16, 64, device="cuda").permute(0, 3, 1, 2).requires_grad_(True)     # channels-last, as sol_y is
+    assert conv_transpose4x4s2_supported(x, m)
+    y = conv_transpose4x4s2(x, m)
+    ref = F.conv_transpose2d(x, m.weight, m.bias, stride=2, padding=1)
+    assert y.shape == ref.shape == (10, 32, 32, 32)
+    assert rel_err(y, ref) < 1e-5
+    w = torch.randn_like(ref)
+    gx, gw, gb = torch.autograd.grad((y * w).sum(), [x, m.weight, m.bias])
+    rx, rw, rb = torch.autograd.grad((ref * w).sum(), [x, m.weight, m.bias])
+    assert rel_err(gx, rx) < 1e-5 and rel_err(gw, rw) < 1e-5 and rel_err(gb, rb) < 1e-5

@@ -238,3 +238,23 @@ def test_empty_batch_returns_empty_results_with_zero_grads(fake_backend):
     sharded.reduce_fn = lambda t: t
     with pytest.raises(ValueError):
         sharded(torch.zeros(0, 32, 8, 16), tp)
+
+
+def test_conv_transpose4x4s2_phase_mapping(fake_backend):
+    """ConvTranspose2d(k=4, s=2, p=1) written as one 3x3 convolution to 4*Cout phase channels + depth-to-space
+    (modules.conv_transpose4x4s2): forward and all three gradients against torch's own operator."""
+    import torch.nn as nn
+    import torch.nn.functional as F
+    from ode_rl_b200.modules import _ConvT4x4s2Fn
+
+    torch.manual_seed(2)
+    m = nn.ConvTranspose2d(64, 32, 4, 2, 1)
+    x = torch.randn(3, 64, 8, 16, requires_grad=True)
+    y = _ConvT4x4s2Fn.apply(x, m.weight, m.bias)
+    ref = F.conv_transpose2d(x, m.weight, m.bias, stride=2, padding=1)
+    assert y.shape == ref.shape == (3, 32, 16, 32)
+    assert rel_err(y, ref) < 1e-5
+    w = torch.randn_like(ref)
+    gx, gw, gb = torch.autograd.grad((y * w).sum(), [x, m.weight, m.bias])
+    rx, rw, rb = torch.autograd.grad((ref * w).sum(), [x, m.weight, m.bias])
+    assert rel_err(gx, rx) < 1e-5 and rel_err(gw, rw) < 1e-5 and rel_err(gb, rb) < 1e-5
