@@ -12,7 +12,7 @@ import os
 import torch
 import torch.nn as nn
 
-from .modules import DiffEqSolver, ODEConvGRUCell, ODEFunc, conv_transpose4x4s2, conv_transpose4x4s2_supported
+from .modules import DiffEqSolver, ODEConvGRUCell, ODEFunc, conv3x3s2, conv3x3s2_supported, conv_transpose4x4s2, conv_transpose4x4s2_supported
 
 
 class _Encoder(nn.Module):          # models/ODEConvGRU.py:101-119 with n_downs == 2
@@ -20,8 +20,17 @@ class _Encoder(nn.Module):          # models/ODEConvGRU.py:101-119 with n_downs 
         super().__init__()
         act = nn.LeakyReLU(negative_slope=0.2, inplace=True)
         self.encoder = nn.Sequential(nn.Conv2d(n_inputs, 16, 3, 2, 1), act, nn.Conv2d(16, out_ch, 3, 2, 1), act)
+        self.fast_second_layer = os.environ.get("ODEX_TORCH_ENCODER") is None
 
     def forward(self, x):
+        e = self.encoder
+        if self.fast_second_layer:
+            h = e[1](e[0](x))
+            if conv3x3s2_supported(h, e[2]):
+                # the 16 -> 64 strided convolution as a 3x3 convolution over space-to-depth cells on the
+                # tcgen05 path; its NHWC result is what the encoder recurrence reads
+                return nn.functional.leaky_relu(conv3x3s2(h, e[2]), e[3].negative_slope)     # not in place: the result is a view
+            return e[3](e[2](h))
         return self.encoder(x)
 
 

@@ -174,6 +174,111 @@ class _ConvT4x4s2Fn(torch.autograd.Function):
         return dx, dw, db
 
 
+# Conv2d(k=3, s=2, p=1) the same way (ConvEncode's second layer, models/ODEConvGRU.py:101-119): space-to-depth the input
+# (cell (Y, X), channel (a, b, c) = in[c, 2Y+a, 2X+b]); input row 2Y + kh - 1 is cell Y-1 / phase 1 for kh = 0 and cell Y /
+# phase kh-1 otherwise, so the strided convolution is a 3x3 "same" convolution 4*Cin -> Cout on the cell grid whose r = 2
+# row / s = 2 column taps are zero.  The result is produced directly in NHWC, which is what the encoder recurrence reads.
+_CS_K = {(0, 1): 0, (1, 0): 1, (1, 1): 2}     # (tap r, phase a) -> kh
+
+
+def _cs_index(device):
+    idx = torch.zeros(2, 2, 3, 3, dtype=torch.long)
+    msk = torch.zeros(2, 2, 3, 3)
+    for a in range(2):
+        for b in range(2):
+            for r in range(3):
+                for q in range(3):
+                    if (r, a) in _CS_K and (q, b) in _CS_K:
+                        idx[a, b, r, q] = _CS_K[(r, a)] * 3 + _CS_K[(q, b)]
+                        msk[a, b, r, q] = 1.0
+    return idx.reshape(-1).to(device), msk.reshape(1, 1, -1).to(device)
+
+
+_CS_CACHE: dict = {}
+
+
+def _cs_w3(w: torch.Tensor) -> torch.Tensor:
+    """Conv2d weight [Cout, Cin, 3, 3] (stride 2) -> 3x3 stride-1 weight [Cout, 4*Cin, 3, 3] over space-to-depth cells."""
+    key = str(w.device)
+    if key not in _CS_CACHE:
+        _CS_CACHE[key] = _cs_index(w.device)
+    idx, msk = _CS_CACHE[key]
+    cout, cin = w.shape[0], w.shape[1]
+    g = w.detach().reshape(cout, cin, 9)[:, :, idx] * msk                       # [Cout, Cin, (a,b,r,s)]
+    return g.reshape(cout, cin, 2, 2, 3, 3).permute(0, 2, 3, 1, 4, 5).reshape(cout, 4 * cin, 3, 3).contiguous()
+
+
+def _cs_dw(dw3: torch.Tensor, cout: int, cin: int) -> torch.Tensor:
+    g = dw3.reshape(cout, 2, 2, cin, 3, 3)
+    sel = ((0, 1), (1, 0), (1, 1))                   # kh -> (r, a)
+    rows = []
+    for kh in range(3):
+        r, a = sel[kh]
+        rows.append(torch.stack([g[:, a, sel[kw][1], :, r, sel[kw][0]] for kw in range(3)], dim=-1))   # [Cout, Cin, 3]
+    return torch.stack(rows, dim=-2).contiguous()                                                       # [Cout, Cin, 3, 3]
+
+
+class _Conv3x3s2Fn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor]):
+        be = K.backend()
+        be.require(x)
+        n, cin, H2, W2 = x.shape
+        H, W = H2 // 2, W2 // 2
+        cout = weight.shape[0]
+        xs = x.detach().float().reshape(n, cin, H, 2, W, 2).permute(0, 2, 4, 3, 5, 1).reshape(n, H, W, 4 * cin).contiguous()
+        w3 = _cs_w3(weight.float())
+        out = torch.empty((n, H, W, cout), dtype=torch.float32, device=x.device)
+        be.conv2d(xs, None, None, be.pack_weights(w3, dgrad=False, tc=True), cout, 3,
+                  bias.detach().float() if bias is not None else None, ACT_NONE, out, impl=CONV_TC)
+        ctx.save_for_backward(xs, w3)
+        ctx.has_bias = bias is not None
+        ctx.cin = cin
+        return from_nhwc(out)                                   # logical [n, Cout, H, W], channels-last memory
+
+    @staticmethod
+    def backward(ctx, dout):
+        be = K.backend()
+        xs, w3 = ctx.saved_tensors
+        n, H, W, c4 = xs.shape
+        cin, cout = ctx.cin, w3.shape[0]
+        dy = to_nhwc(dout.float())
+        if not dy.is_contiguous():
+            dy = dy.contiguous()
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dxs = torch.empty((n, H, W, c4), dtype=torch.float32, device=xs.device)
+            be.conv2d(dy, None, None, be.pack_weights(w3, dgrad=True, tc=True), c4, 3, None, ACT_NONE, dxs, impl=CONV_TC)
+            dx = dxs.view(n, H, W, 2, 2, cin).permute(0, 5, 1, 3, 2, 4).reshape(n, cin, 2 * H, 2 * W)
+        if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
+            dwp = torch.zeros((9, cout, c4), dtype=torch.float32, device=xs.device)
+            dbv = torch.zeros((cout,), dtype=torch.float32, device=xs.device)
+            be.conv2d_wgrad_packed(xs, None, dy, 3, dwp, dbv)
+            dw3 = torch.zeros((cout, c4, 3, 3), dtype=torch.float32, device=xs.device)
+            be.wgrad_unpack(dwp, dw3)
+            dw = _cs_dw(dw3, cout, cin)
+            if ctx.has_bias:
+                db = dbv
+        return dx, dw, db
+
+
+def conv3x3s2_supported(x: torch.Tensor, m: nn.Module) -> bool:
+    """True when `m` is a Conv2d(k=3, s=2, p=1) that the tensor-core convolution can take for input x."""
+    if not (isinstance(m, nn.Conv2d) and m.kernel_size == (3, 3) and m.stride == (2, 2) and m.padding == (1, 1)
+            and m.dilation == (1, 1) and m.groups == 1 and m.padding_mode == "zeros"):
+        return False
+    if not x.is_cuda or x.dim() != 4 or x.shape[0] == 0 or x.shape[2] % 2 or x.shape[3] % 2:
+        return False
+    return (4 * m.in_channels) % 64 == 0 and K.tc_shape_ok(m.out_channels, 4 * m.in_channels, 0, x.shape[2] // 2, x.shape[3] // 2, 3) \
+        and K.tc_shape_ok(4 * m.in_channels, m.out_channels, 0, x.shape[2] // 2, x.shape[3] // 2, 3)
+
+
+def conv3x3s2(x: torch.Tensor, m: nn.Conv2d) -> torch.Tensor:
+    """F.conv2d(x, m.weight, m.bias, stride=2, padding=1) for a 3x3 kernel on the 3xTF32 tensor-core path; the result is a
+    channels-last view (its memory is the NHWC tensor the encoder recurrence reads without a transpose)."""
+    return _Conv3x3s2Fn.apply(x, m.weight, m.bias)
+
+
 def conv_transpose4x4s2_supported(x: torch.Tensor, m: nn.Module) -> bool:
     """True when `m` is a ConvTranspose2d(k=4, s=2, p=1) that the tensor-core convolution can take for input x."""
     if not (isinstance(m, nn.ConvTranspose2d) and m.kernel_size == (4, 4) and m.stride == (2, 2) and m.padding == (1, 1)

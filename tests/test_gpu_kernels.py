@@ -346,3 +346,25 @@ def test_conv_transpose4x4s2_matches_torch():
     gx, gw, gb = torch.autograd.grad((y * w).sum(), [x, m.weight, m.bias])
     rx, rw, rb = torch.autograd.grad((ref * w).sum(), [x, m.weight, m.bias])
     assert rel_err(gx, rx) < 1e-5 and rel_err(gw, rw) < 1e-5 and rel_err(gb, rb) < 1e-5
+
+
+def test_conv3x3s2_matches_torch():
+    """ConvEncode's second layer (Conv2d(16, 64, 3, 2, 1), models/ODEConvGRU.py:101-119) on the tensor-core convolution
+    (modules.conv3x3s2, space-to-depth) against torch's exact-fp32 operator: output and the three gradients."""
+    import torch.nn as nn
+    import torch.nn.functional as F
+    from ode_rl_b200.modules import conv3x3s2, conv3x3s2_supported
+
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(2)
+    m = nn.Conv2d(16, 64, 3, 2, 1).cuda()
+    x = torch.randn(10, 16, 32, 32, device="cuda", requires_grad=True)
+    assert conv3x3s2_supported(x, m)
+    y = conv3x3s2(x, m)
+    ref = F.conv2d(x, m.weight, m.bias, stride=2, padding=1)
+    assert y.shape == ref.shape == (10, 64, 16, 16)
+    assert rel_err(y, ref) < 1e-5
+    w = torch.randn_like(ref)
+    gx, gw, gb = torch.autograd.grad((F.leaky_relu(y, 0.2) * w).sum(), [x, m.weight, m.bias])
+    rx, rw, rb = torch.autograd.grad((F.leaky_relu(ref, 0.2) * w).sum(), [x, m.weight, m.bias])
+    assert rel_err(gx, rx) < 1e-5 and rel_err(gw, rw) < 1e-5 and rel_err(gb, rb) < 1e-5

@@ -258,3 +258,23 @@ def test_conv_transpose4x4s2_phase_mapping(fake_backend):
     gx, gw, gb = torch.autograd.grad((y * w).sum(), [x, m.weight, m.bias])
     rx, rw, rb = torch.autograd.grad((ref * w).sum(), [x, m.weight, m.bias])
     assert rel_err(gx, rx) < 1e-5 and rel_err(gw, rw) < 1e-5 and rel_err(gb, rb) < 1e-5
+
+
+def test_conv3x3s2_space_to_depth_mapping(fake_backend):
+    """Conv2d(k=3, s=2, p=1) written as a 3x3 stride-1 convolution over space-to-depth cells (modules.conv3x3s2):
+    forward and all three gradients against torch's own operator."""
+    import torch.nn as nn
+    import torch.nn.functional as F
+    from ode_rl_b200.modules import _Conv3x3s2Fn
+
+    torch.manual_seed(2)
+    m = nn.Conv2d(16, 64, 3, 2, 1)
+    x = torch.randn(3, 16, 16, 32, requires_grad=True)
+    y = _Conv3x3s2Fn.apply(x, m.weight, m.bias)
+    ref = F.conv2d(x, m.weight, m.bias, stride=2, padding=1)
+    assert y.shape == ref.shape == (3, 64, 8, 16)
+    assert rel_err(y, ref) < 1e-5
+    w = torch.randn_like(ref)
+    gx, gw, gb = torch.autograd.grad((y * w).sum(), [x, m.weight, m.bias])
+    rx, rw, rb = torch.autograd.grad((ref * w).sum(), [x, m.weight, m.bias])
+    assert rel_err(gx, rx) < 1e-5 and rel_err(gw, rw) < 1e-5 and rel_err(gb, rb) < 1e-5
