@@ -159,9 +159,15 @@ def test_size_independent_properties_at_full_batch():
     assert torch.equal(a[:, 17:18], one)
 
 
-def test_cuda_graph_training_step_matches_eager():
-    """The captured-and-replayed training step (harness.GraphedTrainStep: zero_grad, forward, MSE, backward, Adam in one
-    CUDA graph) must walk the same trajectory as the same step enqueued eagerly from Python."""
+@pytest.mark.parametrize("opt_name", ["sgd", "adam"])
+def test_cuda_graph_training_step_matches_eager(opt_name):
+    """The captured-and-replayed training step (harness.GraphedTrainStep: zero_grad, forward, MSE, backward, optimizer in
+    one CUDA graph) must walk the same trajectory as the same step enqueued eagerly from Python.
+    sgd: the update is linear in the gradients, so the parameters of the two runs may differ only by the kernels' own
+    run-to-run noise (the weight-gradient kernels reduce with float atomics): <= 1e-5 (measured 1e-7).
+    adam: every element's update is normalised by its own second moment, which turns summation-order noise on elements
+    whose gradient is ~0 into a fraction of lr (measured: 8e-6 or 8e-3 from run to run, eager against eager as well,
+    tools/graph_vs_eager.py, tools/run_to_run_noise.py) - so there only the losses are compared."""
     import copy
 
     from ode_rl_b200.harness import GraphedTrainStep, ODEConvGRUHarness
@@ -174,8 +180,11 @@ def test_cuda_graph_training_step_matches_eager():
     g = torch.Generator().manual_seed(7)
     x = torch.rand(2, 4, 1, 64, 64, generator=g).to(dev)
     y = torch.rand(2, 4, 1, 64, 64, generator=g).to(dev)
-    o1 = torch.optim.Adam(m1.parameters(), lr=1e-3, capturable=True)
-    o2 = torch.optim.Adam(m2.parameters(), lr=1e-3, capturable=True)
+    if opt_name == "sgd":
+        o1, o2 = torch.optim.SGD(m1.parameters(), lr=0.05), torch.optim.SGD(m2.parameters(), lr=0.05)
+    else:
+        o1 = torch.optim.Adam(m1.parameters(), lr=1e-3, capturable=True)
+        o2 = torch.optim.Adam(m2.parameters(), lr=1e-3, capturable=True)
     step = GraphedTrainStep(m1, o1, torch.nn.functional.mse_loss, x, y, obs, tp, warmup=2)
     assert step.launches_per_step > 100
     losses1 = [float(step()) for _ in range(3)]
@@ -187,8 +196,9 @@ def test_cuda_graph_training_step_matches_eager():
         o2.step()
         losses2.append(float(loss))
     assert max(abs(a - b) for a, b in zip(losses1, losses2[2:])) < 1e-5 * abs(losses2[-1]) + 1e-7
-    for (n1, p1), (_, p2) in zip(m1.named_parameters(), m2.named_parameters()):
-        assert rel_err(p1, p2) < 1e-4, n1
+    if opt_name == "sgd":
+        for (n1, p1), (_, p2) in zip(m1.named_parameters(), m2.named_parameters()):
+            assert rel_err(p1, p2) < 1e-5, n1
 
 
 def test_vidode_shapes_encoder_and_solver():
