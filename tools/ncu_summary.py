@@ -66,8 +66,8 @@ def main():
             ours += v[1]
     for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1])[:24]:
         print("| %.1f %% | %.1f | %d | %.1f | `%s` |" % (100 * v[1] / tot, v[1], v[0], v[1] / v[0], k))
-    print("\nlibodex kernels: %.1f %% of the summed device time; the rest is the torch/cuDNN ConvEncode/ConvDecode, loss and"
-          " Adam (out of scope, SURVEY.md 8f n1).\n" % (100 * ours / tot))
+    print("\nlibodex kernels: %.1f %% of the summed device time; the rest is what is left of the torch-side ConvEncode/ConvDecode (their"
+          " first / last layers, activations, layout shuffles), the loss and Adam.\n" % (100 * ours / tot))
     for k in KERNELS:
         try:
             hdr, units, rows = raw("gpurun_out/prof_%s_%s.ncu-rep" % (tag, k))
