@@ -133,6 +133,17 @@ typedef struct odex_convnet_desc {
 int odex_convnet(const odex_convnet_desc* d, odex_stream_t s);
 int odex_convnet_supported(const odex_convnet_desc* d);
 
+/* ------------------------------------------------------------------------------------------------ decoder tail
+ * LeakyReLU(slope) -> ConvTranspose2d(C, 1, 4, 2, 1) of ConvDecode (models/ODEConvGRU.py:122-140, the activation and the
+ * last layer), reading the PHASE-BLOCKED pre-activation output of the first transposed convolution as the tensor-core
+ * path produces it: p[n][Y][X][(a*2+b)*C + ci] = channel ci at fine pixel (2Y+a, 2X+b).  out: [n][4*cells_h][4*cells_w].
+ * w: [C][16] (torch weight [C,1,4,4]), b: [1] or NULL.  Backward: dp (same layout as p), dw[C][16] += , db[1] += (nullable).
+ * Shapes taken: cells_h = cells_w = 16, C = 32 (config A); otherwise ODEX_E_UNSUPPORTED (the caller stays on torch). */
+int odex_decode_tail_fwd(const float* p, int n, int cells_h, int cells_w, int C, const float* w, const float* b,
+                         float slope, float* out, odex_stream_t s);
+int odex_decode_tail_bwd(const float* p, const float* dout, int n, int cells_h, int cells_w, int C, const float* w,
+                         float slope, float* dp, float* dw, float* db, odex_stream_t s);
+
 /* ------------------------------------------------------------------------------------------------ ConvGRU gates
  * GroupNorm (groups of 32 channels, biased variance, eps, affine) fused with the gate non-linearities.
  * g: conv_gates output [B,H,W,2C] (bias included).  z = sigmoid(GN(g)[:, :C]); r = sigmoid(GN(g)[:, C:]);

@@ -12,7 +12,7 @@ import os
 import torch
 import torch.nn as nn
 
-from .modules import DiffEqSolver, ODEConvGRUCell, ODEFunc, conv3x3s2, conv3x3s2_supported, conv_transpose4x4s2, conv_transpose4x4s2_supported
+from .modules import DiffEqSolver, ODEConvGRUCell, ODEFunc, conv3x3s2, conv3x3s2_supported, conv_transpose4x4s2_phases, conv_transpose4x4s2_supported, decode_tail, decode_tail_supported, phases_to_nchw
 
 
 class _Encoder(nn.Module):          # models/ODEConvGRU.py:101-119 with n_downs == 2
@@ -46,7 +46,12 @@ class _Decoder(nn.Module):          # models/ODEConvGRU.py:122-140 with n_ups ==
         if self.fast_first_layer and conv_transpose4x4s2_supported(x, d0):
             # the 64 -> 32 transposed convolution (60 % of the torch-side time under exact-fp32 cuDNN) as a
             # 3x3 convolution to 4 x 32 phase channels on the tcgen05 path; same parameters, fp32-level result
-            return self.decoder[2](self.decoder[1](conv_transpose4x4s2(x, d0)))
+            P = conv_transpose4x4s2_phases(x, d0)                      # phase-blocked, before the activation
+            if not P.is_contiguous():
+                P = P.contiguous()
+            if decode_tail_supported(P, self.decoder[1], self.decoder[2]):
+                return decode_tail(P, self.decoder[1], self.decoder[2])    # LeakyReLU + ConvTranspose2d(32, 1, 4, 2, 1), one kernel
+            return self.decoder[2](self.decoder[1](phases_to_nchw(P)))
         return self.decoder(x)
 
 

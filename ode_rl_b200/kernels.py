@@ -171,6 +171,31 @@ class Backend:
         d = self._convnet_desc(x, w_tc, bias, act, aux, aux_kind, out, alpha, alpha_dev, skip)
         _lib.check(self.lib.odex_convnet(C.byref(d), _stream()), "odex_convnet")
 
+    # ------------------------------------------------------------------ decoder tail (LeakyReLU + ConvTranspose2d(C,1,4,2,1))
+    @staticmethod
+    def decode_tail_supported(p: torch.Tensor) -> bool:
+        return p.dim() == 4 and tuple(p.shape[1:]) == (16, 16, 128) and p.shape[0] > 0 and p.is_contiguous()
+
+    def decode_tail_fwd(self, p: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor], slope: float,
+                        out: torch.Tensor) -> torch.Tensor:
+        """odex_decode_tail_fwd: p [n,Hc,Wc,4C] phase-blocked pre-activation -> out [n,4Hc,4Wc]."""
+        self.require(p)
+        n, hc, wc, c4 = p.shape
+        assert p.is_contiguous() and out.is_contiguous() and tuple(out.shape) == (n, 4 * hc, 4 * wc)
+        assert w.is_contiguous() and w.numel() == (c4 // 4) * 16
+        _lib.check(self.lib.odex_decode_tail_fwd(p.data_ptr(), n, hc, wc, c4 // 4, w.data_ptr(), _ptr(b), float(slope),
+                                                 out.data_ptr(), _stream()), "odex_decode_tail_fwd")
+        return out
+
+    def decode_tail_bwd(self, p: torch.Tensor, dout: torch.Tensor, w: torch.Tensor, slope: float, dp: torch.Tensor,
+                        dw: Optional[torch.Tensor], db: Optional[torch.Tensor]) -> None:
+        """odex_decode_tail_bwd: dp = d/dp, dw [C,16] +=, db [1] +=."""
+        n, hc, wc, c4 = p.shape
+        assert p.is_contiguous() and dout.is_contiguous() and dp.is_contiguous() and dp.shape == p.shape
+        assert dout.numel() == n * 16 * hc * wc
+        _lib.check(self.lib.odex_decode_tail_bwd(p.data_ptr(), dout.data_ptr(), n, hc, wc, c4 // 4, w.data_ptr(), float(slope),
+                                                 dp.data_ptr(), _ptr(dw), _ptr(db), _stream()), "odex_decode_tail_bwd")
+
     def conv2d_wgrad(self, x0: torch.Tensor, x1: Optional[torch.Tensor], dy: torch.Tensor, R: int,
                      dw: torch.Tensor, db: Optional[torch.Tensor]) -> None:
         """odex_conv2d_wgrad: dw (OIHW) += X^T dy, db += colsum(dy)."""

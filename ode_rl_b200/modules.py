@@ -147,16 +147,15 @@ class _ConvT4x4s2Fn(torch.autograd.Function):
         be.conv2d(xn, None, None, be.pack_weights(w3, dgrad=False, tc=True), 4 * cout, 3, b3, ACT_NONE, P, impl=CONV_TC)
         ctx.save_for_backward(xn, w3)
         ctx.has_bias = bias is not None
-        # depth-to-space: P[n, Y, X, (a, b, co)] -> out[n, co, 2Y+a, 2X+b]
-        return P.view(n, H, W, 2, 2, cout).permute(0, 5, 1, 3, 2, 4).reshape(n, cout, 2 * H, 2 * W)
+        return P                                                # phase-blocked: P[n, Y, X, (a*2+b)*Cout + co]
 
     @staticmethod
-    def backward(ctx, dout):
+    def backward(ctx, dP):
         be = K.backend()
         xn, w3 = ctx.saved_tensors
         n, H, W, cin = xn.shape
         cout = w3.shape[0] // 4
-        dP = dout.float().reshape(n, cout, H, 2, W, 2).permute(0, 2, 4, 3, 5, 1).reshape(n, H, W, 4 * cout).contiguous()
+        dP = dP.float().contiguous()
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
             dxn = torch.empty((n, H, W, cin), dtype=torch.float32, device=xn.device)
@@ -289,10 +288,66 @@ def conv_transpose4x4s2_supported(x: torch.Tensor, m: nn.Module) -> bool:
     return K.tc_shape_ok(4 * m.out_channels, m.in_channels, 0, x.shape[2], x.shape[3], 3)
 
 
+def conv_transpose4x4s2_phases(x: torch.Tensor, m: nn.ConvTranspose2d) -> torch.Tensor:
+    """The transposed convolution in phase-blocked form: P[n, Y, X, (a*2+b)*Cout + co] = out[n, co, 2Y+a, 2X+b]."""
+    return _ConvT4x4s2Fn.apply(x, m.weight, m.bias)
+
+
+def phases_to_nchw(P: torch.Tensor) -> torch.Tensor:
+    """depth-to-space of the phase-blocked tensor: [n, H, W, 4*C] -> [n, C, 2H, 2W] (torch ops; autograd handles them)."""
+    n, H, W, c4 = P.shape
+    c = c4 // 4
+    return P.view(n, H, W, 2, 2, c).permute(0, 5, 1, 3, 2, 4).reshape(n, c, 2 * H, 2 * W)
+
+
 def conv_transpose4x4s2(x: torch.Tensor, m: nn.ConvTranspose2d) -> torch.Tensor:
     """F.conv_transpose2d(x, m.weight, m.bias, stride=2, padding=1) for a 4x4 kernel on the 3xTF32 tensor-core path
     (same parameters, same result to fp32 rounding, hand-written backward)."""
-    return _ConvT4x4s2Fn.apply(x, m.weight, m.bias)
+    return phases_to_nchw(conv_transpose4x4s2_phases(x, m))
+
+
+class _DecodeTailFn(torch.autograd.Function):
+    """LeakyReLU + ConvTranspose2d(C, 1, 4, 2, 1) on the phase-blocked tensor (odex_decode_tail_fwd / _bwd)."""
+
+    @staticmethod
+    def forward(ctx, P: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], slope: float):
+        be = K.backend()
+        Pd = P.detach()
+        n, H, W, _ = Pd.shape
+        w = weight.detach().float().reshape(weight.shape[0], 16).contiguous()
+        out = torch.empty((n, 4 * H, 4 * W), dtype=torch.float32, device=Pd.device)
+        be.decode_tail_fwd(Pd, w, bias.detach().float() if bias is not None else None, slope, out)
+        ctx.save_for_backward(Pd, w)
+        ctx.slope, ctx.has_bias, ctx.wshape = slope, bias is not None, tuple(weight.shape)
+        return out.view(n, 1, 4 * H, 4 * W)
+
+    @staticmethod
+    def backward(ctx, dout):
+        be = K.backend()
+        Pd, w = ctx.saved_tensors
+        dout = dout.float().contiguous()
+        dP = torch.empty_like(Pd)
+        need_w = ctx.needs_input_grad[1]
+        need_b = ctx.has_bias and ctx.needs_input_grad[2]
+        dw = torch.zeros_like(w) if need_w else None
+        db = torch.zeros((1,), dtype=torch.float32, device=Pd.device) if need_b else None
+        be.decode_tail_bwd(Pd, dout, w, ctx.slope, dP, dw, db)
+        return dP, (dw.view(ctx.wshape) if need_w else None), db, None
+
+
+def decode_tail_supported(P: torch.Tensor, act: nn.Module, m: nn.Module) -> bool:
+    """True when (act, m) = (LeakyReLU, ConvTranspose2d(C, 1, 4, 2, 1)) can run as the fused decoder tail on P."""
+    if not (isinstance(act, nn.LeakyReLU) and isinstance(m, nn.ConvTranspose2d) and m.kernel_size == (4, 4)
+            and m.stride == (2, 2) and m.padding == (1, 1) and m.output_padding == (0, 0) and m.dilation == (1, 1)
+            and m.groups == 1 and m.out_channels == 1 and 4 * m.in_channels == P.shape[-1]):
+        return False
+    be = K.backend()
+    return hasattr(be, "decode_tail_fwd") and be.decode_tail_supported(P)
+
+
+def decode_tail(P: torch.Tensor, act: nn.LeakyReLU, m: nn.ConvTranspose2d) -> torch.Tensor:
+    """m(act(depth_to_space(P))) in one kernel each way."""
+    return _DecodeTailFn.apply(P, m.weight, m.bias, float(act.negative_slope))
 
 
 class ODEFunc(nn.Module):

@@ -92,6 +92,36 @@ class FakeBackend:
         out.copy_(v)
         return out
 
+    # ------------------------------------------------------------------ decoder tail
+    @staticmethod
+    def decode_tail_supported(p):
+        return p.dim() == 4 and tuple(p.shape[1:]) == (16, 16, 128) and p.shape[0] > 0 and p.is_contiguous()
+
+    @staticmethod
+    def _tail(p, w, b, slope):
+        n, hc, wc, c4 = p.shape
+        c = c4 // 4
+        h = p.view(n, hc, wc, 2, 2, c).permute(0, 5, 1, 3, 2, 4).reshape(n, c, 2 * hc, 2 * wc)      # depth-to-space
+        return F.conv_transpose2d(F.leaky_relu(h, slope), w.reshape(c, 1, 4, 4), b, stride=2, padding=1)[:, 0]
+
+    def decode_tail_fwd(self, p, w, b, slope, out):
+        self.launches += 1
+        out.copy_(self._tail(p.detach(), w.detach(), None if b is None else b.detach(), slope))
+        return out
+
+    def decode_tail_bwd(self, p, dout, w, slope, dp, dw, db):
+        self.launches += 1
+        with torch.enable_grad():
+            pp = p.detach().clone().requires_grad_(True)
+            ww = w.detach().clone().requires_grad_(True)
+            o = self._tail(pp, ww, None, slope)
+            gp, gw = torch.autograd.grad(o, [pp, ww], dout.reshape(o.shape))
+        dp.copy_(gp)
+        if dw is not None:
+            dw += gw.reshape(dw.shape)
+        if db is not None:
+            db += dout.sum()
+
     def conv2d_wgrad(self, x0, x1, dy, R, dw, db):
         self.launches += 1
         x = x0 if x1 is None else torch.cat((x0, x1), 3)

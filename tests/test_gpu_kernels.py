@@ -368,3 +368,26 @@ def test_conv3x3s2_matches_torch():
     gx, gw, gb = torch.autograd.grad((F.leaky_relu(y, 0.2) * w).sum(), [x, m.weight, m.bias])
     rx, rw, rb = torch.autograd.grad((F.leaky_relu(ref, 0.2) * w).sum(), [x, m.weight, m.bias])
     assert rel_err(gx, rx) < 1e-5 and rel_err(gw, rw) < 1e-5 and rel_err(gb, rb) < 1e-5
+
+
+def test_decode_tail_kernels_match_torch(be):
+    """odex_decode_tail_fwd / _bwd (LeakyReLU + ConvTranspose2d(32, 1, 4, 2, 1) on the phase-blocked tensor, one CTA per
+    image) against torch's exact-fp32 operators on the depth-to-space tensor.  Exact fp32 FMA arithmetic: <= 2e-6 forward
+    and dP; the weight / bias gradients are sums over n * 4096 outputs in a different order: <= 1e-5."""
+    import torch.nn as nn
+    from ode_rl_b200.modules import decode_tail, decode_tail_supported, phases_to_nchw
+
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(4)
+    act, m = nn.LeakyReLU(0.2), nn.ConvTranspose2d(32, 1, 4, 2, 1).cuda()
+    P = torch.randn(37, 16, 16, 128, device="cuda", requires_grad=True)
+    assert decode_tail_supported(P, act, m)
+    y = decode_tail(P, act, m)
+    ref = m(act(phases_to_nchw(P)))
+    assert y.shape == ref.shape == (37, 1, 64, 64)
+    assert rel_err(y, ref) < 2e-6
+    w = torch.randn_like(ref)
+    g = torch.autograd.grad((y * w).sum(), [P, m.weight, m.bias])
+    r = torch.autograd.grad((ref * w).sum(), [P, m.weight, m.bias])
+    assert rel_err(g[0], r[0]) < 2e-6
+    assert rel_err(g[1], r[1]) < 1e-5 and rel_err(g[2], r[2]) < 1e-5

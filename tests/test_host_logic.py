@@ -245,12 +245,12 @@ def test_conv_transpose4x4s2_phase_mapping(fake_backend):
     (modules.conv_transpose4x4s2): forward and all three gradients against torch's own operator."""
     import torch.nn as nn
     import torch.nn.functional as F
-    from ode_rl_b200.modules import _ConvT4x4s2Fn
+    from ode_rl_b200.modules import _ConvT4x4s2Fn, phases_to_nchw
 
     torch.manual_seed(2)
     m = nn.ConvTranspose2d(64, 32, 4, 2, 1)
     x = torch.randn(3, 64, 8, 16, requires_grad=True)
-    y = _ConvT4x4s2Fn.apply(x, m.weight, m.bias)
+    y = phases_to_nchw(_ConvT4x4s2Fn.apply(x, m.weight, m.bias))
     ref = F.conv_transpose2d(x, m.weight, m.bias, stride=2, padding=1)
     assert y.shape == ref.shape == (3, 32, 16, 32)
     assert rel_err(y, ref) < 1e-5
@@ -278,3 +278,22 @@ def test_conv3x3s2_space_to_depth_mapping(fake_backend):
     gx, gw, gb = torch.autograd.grad((y * w).sum(), [x, m.weight, m.bias])
     rx, rw, rb = torch.autograd.grad((ref * w).sum(), [x, m.weight, m.bias])
     assert rel_err(gx, rx) < 1e-5 and rel_err(gw, rw) < 1e-5 and rel_err(gb, rb) < 1e-5
+
+
+def test_decode_tail_function(fake_backend):
+    """modules.decode_tail (LeakyReLU + ConvTranspose2d(32, 1, 4, 2, 1) on the phase-blocked tensor) wired through autograd:
+    output and the three gradients against the torch ops on the depth-to-space tensor."""
+    import torch.nn as nn
+    from ode_rl_b200.modules import decode_tail, decode_tail_supported, phases_to_nchw
+
+    torch.manual_seed(4)
+    act, m = nn.LeakyReLU(0.2), nn.ConvTranspose2d(32, 1, 4, 2, 1)
+    P = torch.randn(2, 16, 16, 128, requires_grad=True)
+    assert decode_tail_supported(P, act, m)
+    y = decode_tail(P, act, m)
+    ref = m(act(phases_to_nchw(P)))
+    assert y.shape == ref.shape == (2, 1, 64, 64) and rel_err(y, ref) < 1e-6
+    w = torch.randn_like(ref)
+    g = torch.autograd.grad((y * w).sum(), [P, m.weight, m.bias])
+    r = torch.autograd.grad((ref * w).sum(), [P, m.weight, m.bias])
+    assert all(rel_err(a, b) < 1e-5 for a, b in zip(g, r))
