@@ -44,6 +44,9 @@ def parse():
     ap.add_argument("--cpu-batch", type=int, default=16)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="enqueue every step from Python instead of replaying a CUDA graph")
+    ap.add_argument("--workload", default="odeconvgru", choices=["odeconvgru", "vidode"],
+                    help="odeconvgru = BASELINE configs[1] (the default, the driver's line); vidode = configs[4]: VidODE forward at "
+                         "128x128x3, dopri5, 32 sequences per GPU (use --batch 32)")
     return ap.parse_args()
 
 
@@ -143,12 +146,170 @@ class Clocks:
                 "samples": len(sm)}
 
 
+# ------------------------------------------------------------------------------------------- configs[4]: VidODE forward
+def vidode_cpu(batch, steps):
+    """oracle/refmodel.vidode_forward (the reference's models/VidODE.py wiring restated, pinned by tests/golden/vidode_*.pt)
+    on the host cores: forward, dopri5 with the reference's default tolerances."""
+    from ode_rl_b200.harness import VidODEHarness
+    from oracle import refmodel
+
+    torch.set_num_threads(os.cpu_count() or 1)
+    torch.manual_seed(0)
+    sd = {k: v.detach() for k, v in VidODEHarness("dopri5").state_dict().items()}
+    x = torch.rand(batch, T_IN, 3, 128, 128, generator=torch.Generator().manual_seed(1234))
+    obs, tp = times("cpu")
+    with torch.no_grad():
+        refmodel.vidode_forward(sd, x[:1], obs, tp, "dopri5")
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            refmodel.vidode_forward(sd, x, obs, tp, "dopri5")
+    dt = (time.perf_counter() - t0) / steps
+    return batch * T_OUT / dt, dt
+
+
+def vidode_main(args, world, rank, local):
+    """BASELINE configs[4] / SURVEY.md 8d cfg5: VidODE (models/VidODE.py) forward at 128x128x3 -> 128 latent channels on
+    32x32, dopri5 (the reference's DiffEqSolver defaults rtol 1e-4 / atol 1e-5), 32 sequences per GPU (256 on 8 GPUs), masks
+    all ones.  predicted frames/s = B * 10 / forward time.  The hot path (ODEConvGRUCell + DiffEqSolver) runs on libodex;
+    BN encoder / per-step decoder / grid_sample warp are torch -- their share is reported."""
+    import torch.distributed as dist
+
+    from ode_rl_b200 import _lib, kernels as K, parallel
+    from ode_rl_b200.harness import VidODEHarness
+
+    assert torch.cuda.is_available(), "bench.py (odex arm) needs a CUDA device; there is no CPU fallback"
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    B = args.batch
+    torch.manual_seed(0)
+    model = VidODEHarness("dopri5", device=dev).to(dev)
+    model.device = dev
+    if world > 1:
+        parallel.shard_solver(model.diffeq_solver, mode="sum")     # batch-shared step size = the single-process sequence
+    xh = torch.rand(B, T_IN, 3, 128, 128, generator=torch.Generator().manual_seed(1234 + rank)).pin_memory()
+    x = xh.to(dev)
+    obs, tp = times(dev)
+    batch = {"observed_tp": obs, "tp_to_predict": tp, "observed_mask": torch.ones(B, T_IN, 1, device=dev),
+             "mask_predicted_data": torch.ones(B, T_OUT, 1, device=dev)}
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, k):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        w0 = time.perf_counter()
+        e0.record()
+        for _ in range(k):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms) / 1e3, w0, time.perf_counter()
+
+    def fwd():
+        with torch.no_grad():
+            return model(x, batch)[0]
+
+    def hot():
+        with torch.no_grad():
+            return model.latents(x, batch)[1]
+
+    xd = torch.empty_like(x)
+
+    def e2e_step():
+        xd.copy_(xh, non_blocking=True)
+        with torch.no_grad():
+            return float(model(xd, batch)[0].mean())        # 4-byte result read back (synchronising)
+
+    for _ in range(max(3, args.warmup)):
+        fwd()
+    clocks = Clocks(local) if rank == 0 else None
+    time.sleep(0.3)
+    n0 = _lib.launch_count()
+    sec, w0, w1 = timed(fwd, args.steps)
+    launches = _lib.launch_count() - n0
+    stats = model.diffeq_solver.last_stats
+    sec_hot, _, _ = timed(hot, args.steps)
+    e2e_step()
+    sec_e, _, w1 = timed(e2e_step, args.steps)
+    clk = clocks.summary(w0, w1) if clocks else None
+    value = world * B * T_OUT * args.steps / sec
+
+    roof = cpu = None
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        # dominant kernel: the ConvGRU gates convolution 5x5, cat(x, h) = 256 -> 256 channels on 32x32 (conv_tc_kernel<128>, two
+        # N-blocks), 10 launches per forward; repeated from C between two events on the launching stream
+        be = K.backend()
+        xs, hs = torch.randn(B, 32, 32, 128, device=dev), torch.randn(B, 32, 32, 128, device=dev)
+        wg = model.encoder_z0.cgru_cell.conv_gates[0]
+        wt = be.pack_weights(wg.weight, False, True)
+        g = torch.empty(B, 32, 32, 256, device=dev)
+        reps = 20
+        be.conv2d(xs, hs, None, wt, 256, 5, wg.bias, K.ACT_NONE, g, repeat=3)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        be.conv2d(xs, hs, None, wt, 256, 5, wg.bias, K.ACT_NONE, g, repeat=reps)
+        e1.record()
+        torch.cuda.synchronize()
+        avg = e0.elapsed_time(e1) / 1e3 / reps
+        fl = 2 * B * 32 * 32 * 256 * 256 * 25
+        peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
+        roof = {"bound": "tensor", "kernel": "conv_tc_kernel<128> (ConvGRU gates 5x5 256->256 on 32x32, 3xTF32, tcgen05 kind::tf32)",
+                "achieved": fl / avg / 1e12, "peak": peak, "unit": "TFLOP/s", "frac": fl / avg / 1e12 / peak, "traffic": None,
+                "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (of measured)" if peaks else "fallback 1.4 PF (of fallback)",
+                "note": "algorithmic FLOPs counted once; 3 TF32 MMAs per useful one at half the bf16 rate: frac*6 = share of tensor "
+                        "issue slots; %d launches back to back, batch %d" % (reps, B),
+                "launches_timed": reps, "avg_launch_us": avg * 1e6}
+        if not args.no_cpu_baseline and world == 1:
+            v, dt = vidode_cpu(2, 1)
+            cpu = {"value": v, "unit": "frames/s", "cores": os.cpu_count() or 1, "kind": "port",
+                   "sample": "1 timed forward at batch 2 (of the batch-%d workload) on the host cores; oracle/refmodel.vidode_forward + "
+                             "restated torchdiffeq, torch CPU fp32" % B}
+        line = {"metric": "VidODE forward predicted frames/s", "value": value, "unit": "frames/s", "n_gpus": world,
+                "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": sec / args.steps * 1e3, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f32 (3xTF32 tensor-core convs, fp32 accumulate)", "data": "synthetic",
+                "config": {"workload": "BASELINE configs[4]: VidODE forward, 128x128x3, 10 in / 10 out, dopri5 rtol=1e-4 atol=1e-5 "
+                                       "(DiffEqSolver defaults, models/VidODE.py:86), batch %d per GPU, masks all ones, BatchNorm with "
+                                       "per-rank batch statistics" % B,
+                           "global_batch": B * world,
+                           "parallelism": "batch-sharded dp%d; dopri5 error norm all-reduced (SUM) so every rank takes the global-batch "
+                                          "step sequence" % world,
+                           "l2": "no explicit flush: per-forward working set (frames 63 MB + latents + decoder activations) >> 126 MB L2"},
+                "dopri5": {"n_accept": stats.n_accept, "n_reject": stats.n_reject, "n_feval": stats.n_feval},
+                "hot_path": {"ms_per_step": sec_hot / args.steps * 1e3, "share_of_forward": sec_hot / sec,
+                             "what": "conv encoder (torch) + ODEConvGRUCell + DiffEqSolver (libodex); the rest of the forward is the "
+                                     "torch-side per-step decoder, grid_sample warp and composition (SURVEY.md 8f n3)"},
+                "e2e": {"value": world * B * T_OUT * args.steps / sec_e, "unit": "frames/s", "h2d_bytes_per_step": int(xh.numel() * 4),
+                        "d2h_bytes_per_step": 4, "ms_per_step": sec_e / args.steps * 1e3},
+                "gpu_launches": int(launches), "clocks": clk, "roofline": roof, "cpu_baseline": cpu}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 # ------------------------------------------------------------------------------------------- GPU arm
 def main():
     args = parse()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.workload == "vidode" and args.impl != "reference":
+        return vidode_main(args, world, rank, local)
 
     if args.impl == "reference":
         if rank != 0:

@@ -12,7 +12,7 @@ import os
 import torch
 import torch.nn as nn
 
-from .modules import DiffEqSolver, ODEConvGRUCell, ODEFunc, conv3x3s2, conv3x3s2_supported, conv_transpose4x4s2_phases, conv_transpose4x4s2_supported, decode_tail, decode_tail_supported, phases_to_nchw
+from .modules import DiffEqSolver, ODEConvGRUCell, ODEFunc, conv3x3s2, conv3x3s2_supported, conv_transpose4x4s2_phases, conv_transpose4x4s2_supported, conv_same, conv_same_supported, decode_tail, decode_tail_supported, phases_to_nchw
 
 
 class _Encoder(nn.Module):          # models/ODEConvGRU.py:101-119 with n_downs == 2
@@ -83,6 +83,109 @@ class ODEConvGRUHarness(nn.Module):
         if return_latents:
             return {"pred": pred, "sol": sol_y, "mean_z0": mean_z0, "std_z0": std_z0}
         return pred
+
+
+class _VidEncoder(nn.Module):        # models/VidODE.py:11-26 (BatchNorm conv encoder; stays torch)
+    def __init__(self, input_dim=3, ch=64, n_downs=2, device=None):
+        super().__init__()
+        layers = [nn.Conv2d(input_dim, ch, 3, 1, 1), nn.BatchNorm2d(ch), nn.ReLU()]
+        for _ in range(n_downs):
+            layers += [nn.Conv2d(ch, ch * 2, 4, 2, 1), nn.BatchNorm2d(ch * 2), nn.ReLU()]
+            ch *= 2
+        self.cnn_encoder = nn.Sequential(*layers).to(device)
+
+    def forward(self, x):
+        return self.cnn_encoder(x)
+
+
+class _VidDecoder(nn.Module):        # models/VidODE.py:28-44 (bilinear 2x upsample + conv/BN/ReLU; stays torch)
+    def __init__(self, input_dim=256, output_dim=3, n_ups=2, device=None):
+        super().__init__()
+        layers, ch = [], input_dim
+        for _ in range(n_ups):
+            layers += [nn.Upsample(scale_factor=2, mode='bilinear', align_corners=False),
+                       nn.Conv2d(ch, ch // 2, 3, 1, 1), nn.BatchNorm2d(ch // 2), nn.ReLU()]
+            ch //= 2
+        layers += [nn.Conv2d(ch, output_dim, 3, 1, 1)]
+        self.cnn_decoder = nn.Sequential(*layers).to(device)
+        self.fast_convs = os.environ.get("ODEX_TORCH_DECODER") is None
+
+    def forward(self, x):
+        if not (self.fast_convs and x.is_cuda):
+            return self.cnn_decoder(x)
+        # the wide 3x3 convolutions (256 -> 128 on 64x64, 128 -> 64 on 128x128) on the tensor-core
+        # convolution of the path; upsample / BatchNorm / ReLU and the 6-channel head stay torch, in channels-last memory
+        x = x.contiguous(memory_format=torch.channels_last)
+        for m in self.cnn_decoder:
+            x = conv_same(x, m) if conv_same_supported(x, m) else m(x)
+        return x
+
+
+class VidODEHarness(nn.Module):
+    """BASELINE configs[4]: the wiring of the reference's models/VidODE.py:46-141 (BN conv encoder -> ODEConvGRUCell at
+    32 * 2**n_downs = 128 channels -> DiffEqSolver -> per-step conv decoder on cat(z_t, z_{t-1}) -> recursive flow warp ->
+    mask compose) with the same constructor order (the same seed gives the same initial weights; checked against the
+    reference class in tests/test_golden.py) and the same submodule / parameter names.  Only the two starred modules
+    are ode_rl_b200's; encoder, decoder, grid_sample and the composition stay torch.
+    Two harness fixes, not path changes: the reference hands the time-first cell a batch-first
+    tensor (models/VidODE.py:101-105) and views the time-first solution as batch-first (:109-110); the harness permutes
+    in both places, as upstream Vid-ODE does.  oracle/make_golden.py applies the same two permutes around the
+    reference's own submodules to produce tests/golden/vidode_*.pt."""
+
+    def __init__(self, method="dopri5", in_channels=3, resolution=128, n_downs=2, n_layers=2, rtol=1e-4, atol=1e-5,
+                 device=torch.device("cpu")):
+        super().__init__()
+        self.device, self.in_channels = device, in_channels
+        self.resize = 2 ** n_downs
+        hw = (resolution // self.resize, resolution // self.resize)
+        ch = 32
+        in_dim = out_dim = ch * self.resize
+        self.conv_encoder = _VidEncoder(input_dim=in_channels, ch=ch, n_downs=n_downs, device=device)
+        self.ode_encoder_func = ODEFunc(n_inputs=in_dim, n_outputs=out_dim, n_layers=n_layers, n_units=in_dim // 2,
+                                        downsize=False, nonlinear='relu', final_act=False, device=device)
+        self.encoder_z0 = ODEConvGRUCell(self.ode_encoder_func, None, hw, out_dim, device=device)
+        self.ode_decoder_func = ODEFunc(n_inputs=in_dim, n_outputs=out_dim, n_layers=n_layers, n_units=in_dim // 2,
+                                        downsize=False, nonlinear='relu', final_act=False, device=device)
+        self.diffeq_solver = DiffEqSolver(self.ode_decoder_func, method, odeint_rtol=rtol, odeint_atol=atol, device=device)
+        self.conv_decoder = _VidDecoder(out_dim * 2, in_channels + 3, n_downs, device=device)
+
+    def latents(self, inputs, batch_dict):
+        """The hot path alone: frames -> (mean_z0, sol_y [B,T,C,H',W'])."""
+        b, t, c, h, w = inputs.size()
+        enc = self.conv_encoder(inputs.view(b * t, c, h, w))
+        enc = enc.view(b, t, *enc.shape[-3:]).permute(1, 0, 2, 3, 4)          # time first
+        mean_z0, _ = self.encoder_z0(enc, batch_dict['observed_tp'], batch_dict.get("observed_mask"))
+        sol_y = self.diffeq_solver(mean_z0, batch_dict['tp_to_predict'])      # [T,B,C,H',W']
+        return mean_z0, sol_y.permute(1, 0, 2, 3, 4)
+
+    def forward(self, inputs, batch_dict):
+        b, t, c, h, w = inputs.size()
+        mean_z0, sol_y = self.latents(inputs, batch_dict)
+        n_pred = sol_y.size(1)
+        # models/VidODE.py:143-160: decoder on cat(z_t, z_{t-1}); z_{-1} = the embedding of the last observed frame
+        prev = self.conv_encoder(inputs[:, -1, ...])
+        outs = []
+        for k in range(n_pred):
+            cur = sol_y[:, k, ...]
+            outs.append(self.conv_decoder(torch.cat([cur, prev], dim=1)))
+            prev = cur
+        outs = torch.stack(outs, dim=1)                                       # [B,T,2+c+1(+...),h,w]
+        flows, inter = outs[:, :, :2, ...], outs[:, :, 2:2 + c, ...]
+        masks = torch.sigmoid(outs[:, :, 2 + c:, ...])
+        # models/VidODE.py:121-128,162-186: warp the last observed frame recursively along the predicted flow
+        gx = torch.linspace(-1.0, 1.0, w, device=inputs.device).view(1, 1, w, 1).expand(b, h, -1, -1)
+        gy = torch.linspace(-1.0, 1.0, h, device=inputs.device).view(1, h, 1, 1).expand(b, -1, w, -1)
+        grid = torch.cat([gx, gy], 3).float()
+        frame, warped = inputs[:, -1, ...], []
+        for k in range(n_pred):
+            fl = torch.cat([flows[:, k, 0:1] / ((w - 1.0) / 2.0), flows[:, k, 1:2] / ((h - 1.0) / 2.0)], dim=1)
+            frame = nn.functional.grid_sample(frame, grid + fl.permute(0, 2, 3, 1), padding_mode="border", align_corners=False)   # the default the reference runs with
+            warped.append(frame)
+        warped = torch.stack(warped, dim=1)
+        pred_x = (masks * warped + (1 - masks) * inter).view(b, -1, c, h, w)
+        extra = {"optical_flow": flows, "warped_pred_x": warped, "pred_intermediates": inter, "pred_masks": masks,
+                 "mean_z0": mean_z0, "sol_y": sol_y}
+        return pred_x, extra
 
 
 class GraphedTrainStep:

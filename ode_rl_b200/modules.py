@@ -16,6 +16,8 @@ from __future__ import annotations
 
 from typing import List, Optional
 
+import weakref
+
 import torch
 import torch.nn as nn
 
@@ -348,6 +350,32 @@ def decode_tail_supported(P: torch.Tensor, act: nn.Module, m: nn.Module) -> bool
 def decode_tail(P: torch.Tensor, act: nn.LeakyReLU, m: nn.ConvTranspose2d) -> torch.Tensor:
     """m(act(depth_to_space(P))) in one kernel each way."""
     return _DecodeTailFn.apply(P, m.weight, m.bias, float(act.negative_slope))
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# A lone "same" Conv2d (3x3 / 5x5 / 1x1, stride 1) of a torch-side caller on the path's tensor-core convolution: the
+# per-step decoder of models/VidODE.py:28-44 (conv3x3 256 -> 128 on 64x64 and 128 -> 64 on 128x128 are 78 % of the VidODE
+# forward under exact-fp32 cuDNN; SURVEY.md 8f n3).  Same parameters (the module's own nn.Conv2d), fp32-level result,
+# forward and backward through ConvNetOp like the ODE function's layers.
+_LONE_OPS: "weakref.WeakKeyDictionary[nn.Conv2d, ConvNetOp]" = weakref.WeakKeyDictionary()
+
+
+def conv_same_supported(x: torch.Tensor, m: nn.Module) -> bool:
+    if not (isinstance(m, nn.Conv2d) and x.is_cuda and x.dim() == 4 and x.dtype == torch.float32 and x.shape[0] > 0):
+        return False
+    k = m.kernel_size
+    if not (k[0] == k[1] and k[0] in (1, 3, 5) and m.stride == (1, 1) and m.dilation == (1, 1) and m.groups == 1
+            and m.padding == (k[0] // 2, k[0] // 2) and m.padding_mode == "zeros"):
+        return False
+    return K.tc_shape_ok(m.out_channels, m.in_channels, 0, x.shape[2], x.shape[3], k[0])
+
+
+def conv_same(x: torch.Tensor, m: nn.Conv2d) -> torch.Tensor:
+    """m(x) on odex_conv2d (3xTF32 tcgen05); logical NCHW in / out, the result is a channels-last view."""
+    op = _LONE_OPS.get(m)
+    if op is None:
+        op = _LONE_OPS[m] = ConvNetOp(nn.Sequential(m), "conv_same")
+    return _ConvNetFn.apply(op, x, *op.params())
 
 
 class ODEFunc(nn.Module):

@@ -66,5 +66,70 @@ def main():
     torch.save({"state_dict": f.state_dict(), "y": y, "f": fy}, os.path.join(OUT, "odefunc_eval.pt"))
 
 
+def vidode_forward(model, frames, batch):
+    """models/VidODE.py:91-141 through the reference's OWN submodules and methods, with the two layout fixes of
+    SURVEY.md Appendix B (time-first tensor into encoder_z0; time-first solution permuted to batch-first)."""
+    b, t, c, h, w = frames.size()
+    enc = model.conv_encoder(frames.view(b * t, c, h, w))
+    enc = enc.view(b, t, *enc.shape[-3:]).permute(1, 0, 2, 3, 4)
+    mu, _ = model.encoder_z0(enc, batch["observed_tp"], batch["observed_mask"])
+    sol = model.diffeq_solver(mu, batch["tp_to_predict"])
+    log = tde.LAST_LOG
+    sol_y = sol.permute(1, 0, 2, 3, 4).contiguous()
+    skip = model.conv_encoder(frames[:, -1, ...])
+    outs = torch.cat(model.get_flowmaps(sol_out=sol_y, first_prev_embed=skip, mask=batch["mask_predicted_data"]), dim=1)
+    nc = model.opt.in_channels
+    flows, inter, masks = outs[:, :, :2, ...], outs[:, :, 2:2 + nc, ...], torch.sigmoid(outs[:, :, 2 + nc:, ...])
+    gx = torch.linspace(-1.0, 1.0, w).view(1, 1, w, 1).expand(b, h, -1, -1)
+    gy = torch.linspace(-1.0, 1.0, h).view(1, h, 1, 1).expand(b, -1, w, -1)
+    grid = torch.cat([gx, gy], 3).float()
+    warped = torch.cat(model.get_warped_images(pred_flows=flows, start_image=frames[:, -1, ...], grid=grid), dim=1)
+    pred = (masks * warped + (1 - masks) * inter).view(b, -1, c, h, w)
+    return mu, sol_y, pred, log
+
+
+def vidode_batch(B, T, C, S, seed=1234):
+    frames = torch.rand(B, T, C, S, S, generator=torch.Generator().manual_seed(seed))
+    ts = torch.tensor(np.arange(0, 2 * T) / (2 * T))
+    return frames, {"observed_tp": ts[:T], "tp_to_predict": ts[T:], "observed_mask": torch.ones(B, T, 1),
+                    "mask_predicted_data": torch.ones(B, T, 1)}
+
+
+def param_checksums(model):
+    return {k: float(v.double().sum()) for k, v in model.state_dict().items() if v.dtype.is_floating_point}
+
+
+def main_vidode():
+    """BASELINE configs[4] wiring at a fixture-sized shape: 64x64x3 frames (16x16 latent, 128 channels), B=2, 3 in / 3 out.
+    Weights are NOT stored (13 MB): the fixture keeps per-tensor checksums of the seeded default init and the product
+    harness re-creates them from the same seed (tests/test_golden.py checks state_dict equality against the reference
+    class where /root/reference is mounted, and the checksums everywhere)."""
+    ref = refload.load()
+    B, T, C, S = 2, 3, 3, 64
+    frames, batch = vidode_batch(B, T, C, S)
+    for method, scale in (("rk4", 1.0), ("dopri5", 1.0), ("dopri5", 4.0)):
+        torch.manual_seed(0)
+        model = ref.VidODE(refload.vidode_opt(method, S, C), torch.device("cpu"))     # train mode: BatchNorm uses batch statistics
+        if scale != 1.0:
+            with torch.no_grad():
+                for p in model.ode_decoder_func.parameters():
+                    p.mul_(scale)
+        sums = param_checksums(model)          # before the forward: BatchNorm running statistics still at their init
+        with torch.no_grad():
+            mu, sol_y, pred, log = vidode_forward(model, frames, batch)
+        rec = {"method": method, "scale": scale, "rtol": model.diffeq_solver.odeint_rtol, "atol": model.diffeq_solver.odeint_atol,
+               "frames_seed": 1234, "B": B, "T": T, "C": C, "S": S, "weights_seed": 0, "checksums": sums,
+               "mean_z0": mu.contiguous(), "sol_y": sol_y, "pred": pred.contiguous(),
+               "attempts": list(log.attempts) if method == "dopri5" else [],
+               "n_feval": log.n_feval if method == "dopri5" else None}
+        name = "vidode_%s%s.pt" % (method, "" if scale == 1.0 else "_x%d" % int(scale))
+        torch.save(rec, os.path.join(OUT, name))
+        print(name, "pred", tuple(pred.shape), "attempts", len(rec["attempts"]),
+              "rejects", sum(1 for a in rec["attempts"] if not a[3]))
+
+
 if __name__ == "__main__":
-    main()
+    if "vidode" in sys.argv[1:]:
+        main_vidode()
+    else:
+        main()

@@ -49,6 +49,7 @@ def load():
     ns.ConvGRUCell = importlib.import_module("modules.ConvGRUCell").ConvGRUCell
     ns.ODEConvGRU = importlib.import_module("models.ODEConvGRU").ODEConvGRU
     ns.create_convnet = importlib.import_module("helpers.utils").create_convnet
+    ns.VidODE = importlib.import_module("models.VidODE").VidODE
     return ns
 
 
@@ -57,3 +58,8 @@ def default_opt(method="euler", resolution=64, in_channels=1):
     return Namespace(resolution=resolution, n_downs=2, conv_encoder_out_ch=64, in_channels=in_channels,
                      n_ode_layers=3, neural_ode_n_units=64, neural_ode_decoder_out_ch=64,
                      decode_diff_method=method, mem=False, z_sample=False)
+
+
+def vidode_opt(method="dopri5", resolution=128, in_channels=3):
+    """The options models/VidODE.py:46-88 reads (n_layers=2 as in SURVEY.md 8: f = 128->64->64->64->128)."""
+    return Namespace(resolution=resolution, n_downs=2, in_channels=in_channels, n_layers=2, decode_diff_method=method)

@@ -391,3 +391,31 @@ def test_decode_tail_kernels_match_torch(be):
     r = torch.autograd.grad((ref * w).sum(), [P, m.weight, m.bias])
     assert rel_err(g[0], r[0]) < 2e-6
     assert rel_err(g[1], r[1]) < 1e-5 and rel_err(g[2], r[2]) < 1e-5
+
+
+@pytest.mark.parametrize("cin,cout,hw,n", [(256, 128, 64, 2), (128, 64, 128, 1)])
+def test_conv_same_matches_torch(cin, cout, hw, n):
+    """The VidODE decoder's wide convolutions (models/VidODE.py:28-44: conv3x3 256 -> 128 on 64x64, 128 -> 64 on 128x128)
+    on the tensor-core convolution (modules.conv_same) against torch's exact-fp32 operator: output and the three gradients
+    (relative L2; max-abs bound 3e-5 of the largest entry, the 3xTF32 bar of the path)."""
+    import torch.nn as nn
+    import torch.nn.functional as F
+    from ode_rl_b200.modules import conv_same, conv_same_supported
+    from tests.util import rel_l2
+
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(5)
+    m = nn.Conv2d(cin, cout, 3, 1, 1).cuda()
+    x = torch.randn(n, cin, hw, hw, device="cuda").contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    assert conv_same_supported(x, m)
+    y = conv_same(x, m)
+    ref = F.conv2d(x, m.weight, m.bias, padding=1)
+    assert y.shape == ref.shape
+    assert rel_l2(y, ref) < 1e-5 and rel_err(y, ref) < 3e-5
+    w = torch.randn_like(ref)
+    # smooth loss: with ReLU a pre-activation within rounding noise of 0 takes the other sub-gradient branch at ~1e-6 of the
+    # positions, which alone is ~1e-3 relative L2 on the gradients (measured 2.4e-3)
+    got = torch.autograd.grad((torch.tanh(y) * w).sum(), [x, m.weight, m.bias])
+    exp = torch.autograd.grad((torch.tanh(ref) * w).sum(), [x, m.weight, m.bias])
+    for g, r in zip(got, exp):
+        assert rel_l2(g, r) < 1e-5 and rel_err(g, r) < 3e-5

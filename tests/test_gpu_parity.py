@@ -228,3 +228,18 @@ def test_vidode_shapes_encoder_and_solver():
     errs["x"] = rel_l2(x.grad, x1.grad)
     print(errs)
     assert max(errs.values()) < 1e-4, errs
+
+
+@pytest.mark.parametrize("name", ["rk4", "dopri5", "dopri5_x4"])
+def test_vidode_golden(name):
+    """BASELINE configs[4] wiring (models/VidODE.py) against the fixtures made from the reference's own VidODE submodules:
+    128-channel ODEConvGRUCell + DiffEqSolver on the C-ABI path, BN encoder / decoder / grid_sample warp in torch."""
+    from tests.test_golden import check_vidode, load_vidode_case
+
+    rec, model, frames, batch = load_vidode_case(name, DEV)
+    n0 = _lib.launch_count()
+    with torch.no_grad():
+        pred, extra = model(frames, batch)
+    torch.cuda.synchronize()
+    assert _lib.launch_count() > n0, "no libodex kernel launched"
+    check_vidode(rec, model, pred, extra)
