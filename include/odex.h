@@ -144,6 +144,13 @@ int odex_decode_tail_fwd(const float* p, int n, int cells_h, int cells_w, int C,
 int odex_decode_tail_bwd(const float* p, const float* dout, int n, int cells_h, int cells_w, int C, const float* w,
                          float slope, float* dp, float* dw, float* db, odex_stream_t s);
 
+/* ------------------------------------------------------------------------------------------------ bilinear 2x upsample
+ * nn.Upsample(scale_factor=2, mode='bilinear', align_corners=False) of the VidODE per-step decoder (models/VidODE.py:34),
+ * NHWC fp32: x [n][H][W][C] -> out [n][2H][2W][C]; _bwd is its adjoint: dout [n][2H][2W][C] -> dx [n][H][W][C] (overwritten).
+ * C must be a multiple of 4, pointers 16-byte aligned. */
+int odex_upsample2x_fwd(const float* x, int n, int H, int W, int C, float* out, odex_stream_t s);
+int odex_upsample2x_bwd(const float* dout, int n, int H, int W, int C, float* dx, odex_stream_t s);
+
 /* ------------------------------------------------------------------------------------------------ ConvGRU gates
  * GroupNorm (groups of 32 channels, biased variance, eps, affine) fused with the gate non-linearities.
  * g: conv_gates output [B,H,W,2C] (bias included).  z = sigmoid(GN(g)[:, :C]); r = sigmoid(GN(g)[:, C:]);

@@ -196,6 +196,23 @@ class Backend:
         _lib.check(self.lib.odex_decode_tail_bwd(p.data_ptr(), dout.data_ptr(), n, hc, wc, c4 // 4, w.data_ptr(), float(slope),
                                                  dp.data_ptr(), _ptr(dw), _ptr(db), _stream()), "odex_decode_tail_bwd")
 
+    # ------------------------------------------------------------------ bilinear 2x upsample (NHWC)
+    def upsample2x_fwd(self, x: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+        """odex_upsample2x_fwd: x [n,H,W,C] -> out [n,2H,2W,C] (align_corners=False)."""
+        self.require(x)
+        n, H, W, Cc = x.shape
+        assert x.is_contiguous() and out.is_contiguous() and tuple(out.shape) == (n, 2 * H, 2 * W, Cc)
+        _lib.check(self.lib.odex_upsample2x_fwd(x.data_ptr(), n, H, W, Cc, out.data_ptr(), _stream()), "odex_upsample2x_fwd")
+        return out
+
+    def upsample2x_bwd(self, dout: torch.Tensor, dx: torch.Tensor) -> torch.Tensor:
+        """odex_upsample2x_bwd: the adjoint, dout [n,2H,2W,C] -> dx [n,H,W,C]."""
+        self.require(dout)
+        n, H, W, Cc = dx.shape
+        assert dout.is_contiguous() and dx.is_contiguous() and tuple(dout.shape) == (n, 2 * H, 2 * W, Cc)
+        _lib.check(self.lib.odex_upsample2x_bwd(dout.data_ptr(), n, H, W, Cc, dx.data_ptr(), _stream()), "odex_upsample2x_bwd")
+        return dx
+
     def conv2d_wgrad(self, x0: torch.Tensor, x1: Optional[torch.Tensor], dy: torch.Tensor, R: int,
                      dw: torch.Tensor, db: Optional[torch.Tensor]) -> None:
         """odex_conv2d_wgrad: dw (OIHW) += X^T dy, db += colsum(dy)."""

@@ -179,18 +179,22 @@ class _ConvT4x4s2Fn(torch.autograd.Function):
 # (cell (Y, X), channel (a, b, c) = in[c, 2Y+a, 2X+b]); input row 2Y + kh - 1 is cell Y-1 / phase 1 for kh = 0 and cell Y /
 # phase kh-1 otherwise, so the strided convolution is a 3x3 "same" convolution 4*Cin -> Cout on the cell grid whose r = 2
 # row / s = 2 column taps are zero.  The result is produced directly in NHWC, which is what the encoder recurrence reads.
-_CS_K = {(0, 1): 0, (1, 0): 1, (1, 1): 2}     # (tap r, phase a) -> kh
+# Conv2d(k=4, s=2, p=1) (the VidODE encoder's down-sampling layers, models/VidODE.py:17-19) is the same mapping with one more
+# tap: input row 2Y + kh - 1 for kh = 3 is cell Y+1 / phase 0.
+_CS_K = {3: {(0, 1): 0, (1, 0): 1, (1, 1): 2},                 # (tap r, phase a) -> kh
+         4: {(0, 1): 0, (1, 0): 1, (1, 1): 2, (2, 0): 3}}
 
 
-def _cs_index(device):
+def _cs_index(device, k):
+    tab = _CS_K[k]
     idx = torch.zeros(2, 2, 3, 3, dtype=torch.long)
     msk = torch.zeros(2, 2, 3, 3)
     for a in range(2):
         for b in range(2):
             for r in range(3):
                 for q in range(3):
-                    if (r, a) in _CS_K and (q, b) in _CS_K:
-                        idx[a, b, r, q] = _CS_K[(r, a)] * 3 + _CS_K[(q, b)]
+                    if (r, a) in tab and (q, b) in tab:
+                        idx[a, b, r, q] = tab[(r, a)] * k + tab[(q, b)]
                         msk[a, b, r, q] = 1.0
     return idx.reshape(-1).to(device), msk.reshape(1, 1, -1).to(device)
 
@@ -199,24 +203,26 @@ _CS_CACHE: dict = {}
 
 
 def _cs_w3(w: torch.Tensor) -> torch.Tensor:
-    """Conv2d weight [Cout, Cin, 3, 3] (stride 2) -> 3x3 stride-1 weight [Cout, 4*Cin, 3, 3] over space-to-depth cells."""
-    key = str(w.device)
+    """Conv2d weight [Cout, Cin, k, k] (k = 3 or 4, stride 2, padding 1) -> 3x3 stride-1 weight [Cout, 4*Cin, 3, 3] over
+    space-to-depth cells."""
+    k = w.shape[-1]
+    key = (str(w.device), k)
     if key not in _CS_CACHE:
-        _CS_CACHE[key] = _cs_index(w.device)
+        _CS_CACHE[key] = _cs_index(w.device, k)
     idx, msk = _CS_CACHE[key]
     cout, cin = w.shape[0], w.shape[1]
-    g = w.detach().reshape(cout, cin, 9)[:, :, idx] * msk                       # [Cout, Cin, (a,b,r,s)]
+    g = w.detach().reshape(cout, cin, k * k)[:, :, idx] * msk                   # [Cout, Cin, (a,b,r,s)]
     return g.reshape(cout, cin, 2, 2, 3, 3).permute(0, 2, 3, 1, 4, 5).reshape(cout, 4 * cin, 3, 3).contiguous()
 
 
-def _cs_dw(dw3: torch.Tensor, cout: int, cin: int) -> torch.Tensor:
+def _cs_dw(dw3: torch.Tensor, cout: int, cin: int, k: int = 3) -> torch.Tensor:
     g = dw3.reshape(cout, 2, 2, cin, 3, 3)
-    sel = ((0, 1), (1, 0), (1, 1))                   # kh -> (r, a)
+    sel = sorted(_CS_K[k], key=_CS_K[k].get)         # kh -> (r, a)
     rows = []
-    for kh in range(3):
+    for kh in range(k):
         r, a = sel[kh]
-        rows.append(torch.stack([g[:, a, sel[kw][1], :, r, sel[kw][0]] for kw in range(3)], dim=-1))   # [Cout, Cin, 3]
-    return torch.stack(rows, dim=-2).contiguous()                                                       # [Cout, Cin, 3, 3]
+        rows.append(torch.stack([g[:, a, sel[kw][1], :, r, sel[kw][0]] for kw in range(k)], dim=-1))   # [Cout, Cin, k]
+    return torch.stack(rows, dim=-2).contiguous()                                                       # [Cout, Cin, k, k]
 
 
 class _Conv3x3s2Fn(torch.autograd.Function):
@@ -234,7 +240,7 @@ class _Conv3x3s2Fn(torch.autograd.Function):
                   bias.detach().float() if bias is not None else None, ACT_NONE, out, impl=CONV_TC)
         ctx.save_for_backward(xs, w3)
         ctx.has_bias = bias is not None
-        ctx.cin = cin
+        ctx.cin, ctx.k = cin, weight.shape[-1]
         return from_nhwc(out)                                   # logical [n, Cout, H, W], channels-last memory
 
     @staticmethod
@@ -257,15 +263,15 @@ class _Conv3x3s2Fn(torch.autograd.Function):
             be.conv2d_wgrad_packed(xs, None, dy, 3, dwp, dbv)
             dw3 = torch.zeros((cout, c4, 3, 3), dtype=torch.float32, device=xs.device)
             be.wgrad_unpack(dwp, dw3)
-            dw = _cs_dw(dw3, cout, cin)
+            dw = _cs_dw(dw3, cout, cin, ctx.k)
             if ctx.has_bias:
                 db = dbv
         return dx, dw, db
 
 
 def conv3x3s2_supported(x: torch.Tensor, m: nn.Module) -> bool:
-    """True when `m` is a Conv2d(k=3, s=2, p=1) that the tensor-core convolution can take for input x."""
-    if not (isinstance(m, nn.Conv2d) and m.kernel_size == (3, 3) and m.stride == (2, 2) and m.padding == (1, 1)
+    """True when `m` is a Conv2d(k=3 or 4, s=2, p=1) that the tensor-core convolution can take for input x."""
+    if not (isinstance(m, nn.Conv2d) and m.kernel_size in ((3, 3), (4, 4)) and m.stride == (2, 2) and m.padding == (1, 1)
             and m.dilation == (1, 1) and m.groups == 1 and m.padding_mode == "zeros"):
         return False
     if not x.is_cuda or x.dim() != 4 or x.shape[0] == 0 or x.shape[2] % 2 or x.shape[3] % 2:
@@ -275,7 +281,7 @@ def conv3x3s2_supported(x: torch.Tensor, m: nn.Module) -> bool:
 
 
 def conv3x3s2(x: torch.Tensor, m: nn.Conv2d) -> torch.Tensor:
-    """F.conv2d(x, m.weight, m.bias, stride=2, padding=1) for a 3x3 kernel on the 3xTF32 tensor-core path; the result is a
+    """F.conv2d(x, m.weight, m.bias, stride=2, padding=1) for a 3x3 or 4x4 kernel on the 3xTF32 tensor-core path; the result is a
     channels-last view (its memory is the NHWC tensor the encoder recurrence reads without a transpose)."""
     return _Conv3x3s2Fn.apply(x, m.weight, m.bias)
 
@@ -376,6 +382,113 @@ def conv_same(x: torch.Tensor, m: nn.Conv2d) -> torch.Tensor:
     if op is None:
         op = _LONE_OPS[m] = ConvNetOp(nn.Sequential(m), "conv_same")
     return _ConvNetFn.apply(op, x, *op.params())
+
+
+class _ConvSameWFn(torch.autograd.Function):
+    """F.conv2d(x, weight, bias, padding=k//2) with the weight / bias given as tensors (so the caller may pad or slice them
+    under autograd), on odex_conv2d / odex_conv2d_wgrad_packed; logical NCHW in / out on NHWC memory."""
+
+    @staticmethod
+    def forward(ctx, x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor]):
+        be = K.backend()
+        be.require(x)
+        xn = to_nhwc(x.detach().float())
+        if not xn.is_contiguous():
+            xn = xn.contiguous()
+        n, H, W, cin = xn.shape
+        cout, R = weight.shape[0], weight.shape[-1]
+        w = weight.detach().float().contiguous()
+        out = torch.empty((n, H, W, cout), dtype=torch.float32, device=x.device)
+        be.conv2d(xn, None, None, be.pack_weights(w, dgrad=False, tc=True), cout, R,
+                  bias.detach().float() if bias is not None else None, ACT_NONE, out, impl=CONV_TC)
+        ctx.save_for_backward(xn, w)
+        ctx.has_bias = bias is not None
+        return from_nhwc(out)
+
+    @staticmethod
+    def backward(ctx, dout):
+        be = K.backend()
+        xn, w = ctx.saved_tensors
+        n, H, W, cin = xn.shape
+        cout, R = w.shape[0], w.shape[-1]
+        dy = to_nhwc(dout.float())
+        if not dy.is_contiguous():
+            dy = dy.contiguous()
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dxn = torch.empty((n, H, W, cin), dtype=torch.float32, device=xn.device)
+            be.conv2d(dy, None, None, be.pack_weights(w, dgrad=True, tc=True), cin, R, None, ACT_NONE, dxn, impl=CONV_TC)
+            dx = from_nhwc(dxn)
+        if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
+            dwp = torch.zeros((R * R, cout, cin), dtype=torch.float32, device=xn.device)
+            dbv = torch.zeros((cout,), dtype=torch.float32, device=xn.device)
+            be.conv2d_wgrad_packed(xn, None, dy, R, dwp, dbv)
+            dw = torch.zeros((cout, cin, R, R), dtype=torch.float32, device=xn.device)
+            be.wgrad_unpack(dwp, dw)
+            if ctx.has_bias:
+                db = dbv
+        return dx, dw, db
+
+
+def conv_same_padded_supported(x: torch.Tensor, m: nn.Module) -> bool:
+    """A "same" Conv2d with FEWER than 64 output channels (the VidODE decoder's 64 -> in_channels + 3 head) that fits the
+    tensor-core convolution once its output channels are zero-padded to 64."""
+    if not (isinstance(m, nn.Conv2d) and x.is_cuda and x.dim() == 4 and x.dtype == torch.float32 and x.shape[0] > 0):
+        return False
+    k = m.kernel_size
+    if not (k[0] == k[1] and k[0] in (1, 3, 5) and m.stride == (1, 1) and m.dilation == (1, 1) and m.groups == 1
+            and m.padding == (k[0] // 2, k[0] // 2) and m.padding_mode == "zeros" and m.out_channels < 64):
+        return False
+    return K.tc_shape_ok(64, m.in_channels, 0, x.shape[2], x.shape[3], k[0]) and \
+        K.tc_shape_ok(m.in_channels, 64, 0, x.shape[2], x.shape[3], k[0])
+
+
+def conv_same_padded(x: torch.Tensor, m: nn.Conv2d) -> torch.Tensor:
+    """m(x) for a narrow head: weight / bias zero-padded to 64 output channels (torch ops, so autograd slices the gradients
+    back), one tensor-core convolution, the first out_channels channels returned.  cuDNN's exact-fp32 kernels run such a
+    6-channel head at ~6 TFLOP/s; the padded convolution costs 10x the FLOPs and still a fifth of the time."""
+    pad = 64 - m.out_channels
+    w = nn.functional.pad(m.weight, (0, 0, 0, 0, 0, 0, 0, pad))
+    b = nn.functional.pad(m.bias, (0, pad)) if m.bias is not None else None
+    return _ConvSameWFn.apply(x, w, b)[:, :m.out_channels]
+
+
+class _Upsample2xFn(torch.autograd.Function):
+    """nn.Upsample(scale_factor=2, mode='bilinear', align_corners=False), logical NCHW in / out on NHWC memory."""
+
+    @staticmethod
+    def forward(ctx, x: torch.Tensor):
+        be = K.backend()
+        be.require(x)
+        xn = to_nhwc(x.detach().float())
+        n, H, W, C_ = xn.shape
+        out = torch.empty((n, 2 * H, 2 * W, C_), dtype=torch.float32, device=x.device)
+        be.upsample2x_fwd(xn, out)
+        return from_nhwc(out)
+
+    @staticmethod
+    def backward(ctx, dy):
+        d = to_nhwc(dy.float())
+        if not d.is_contiguous():
+            d = d.contiguous()
+        n, H2, W2, C_ = d.shape
+        dx = torch.empty((n, H2 // 2, W2 // 2, C_), dtype=torch.float32, device=d.device)
+        K.backend().upsample2x_bwd(d, dx)
+        return from_nhwc(dx)
+
+
+def upsample2x_supported(x: torch.Tensor, m: nn.Module) -> bool:
+    if not (isinstance(m, nn.Upsample) and x.is_cuda and x.dim() == 4 and x.dtype == torch.float32 and x.shape[0] > 0):
+        return False
+    sf = m.scale_factor
+    sf = tuple(sf) if isinstance(sf, (tuple, list)) else (sf, sf)
+    return m.mode == "bilinear" and not m.align_corners and sf == (2, 2) and m.size is None and x.shape[1] % 4 == 0
+
+
+def upsample2x(x: torch.Tensor) -> torch.Tensor:
+    """The VidODE decoder's bilinear 2x upsample (models/VidODE.py:34) as one HBM-bound NHWC kernel (odex_upsample2x_fwd;
+    adjoint odex_upsample2x_bwd); the result is a channels-last view, what conv_same reads without a repack."""
+    return _Upsample2xFn.apply(x)
 
 
 class ODEFunc(nn.Module):

@@ -122,6 +122,21 @@ class FakeBackend:
         if db is not None:
             db += dout.sum()
 
+    # ------------------------------------------------------------------ bilinear 2x upsample
+    def upsample2x_fwd(self, x, out):
+        self.launches += 1
+        out.copy_(F.interpolate(x.detach().permute(0, 3, 1, 2), scale_factor=2, mode="bilinear", align_corners=False).permute(0, 2, 3, 1))
+        return out
+
+    def upsample2x_bwd(self, dout, dx):
+        self.launches += 1
+        with torch.enable_grad():
+            z = torch.zeros(dx.shape, dtype=dx.dtype).permute(0, 3, 1, 2).requires_grad_(True)
+            o = F.interpolate(z, scale_factor=2, mode="bilinear", align_corners=False)
+            (g,) = torch.autograd.grad(o, [z], dout.detach().permute(0, 3, 1, 2))
+        dx.copy_(g.permute(0, 2, 3, 1))
+        return dx
+
     def conv2d_wgrad(self, x0, x1, dy, R, dw, db):
         self.launches += 1
         x = x0 if x1 is None else torch.cat((x0, x1), 3)

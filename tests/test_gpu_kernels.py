@@ -348,7 +348,8 @@ def test_conv_transpose4x4s2_matches_torch():
     assert rel_err(gx, rx) < 1e-5 and rel_err(gw, rw) < 1e-5 and rel_err(gb, rb) < 1e-5
 
 
-def test_conv3x3s2_matches_torch():
+@pytest.mark.parametrize("cin,cout,k,hw,n", [(16, 64, 3, 32, 10), (32, 64, 4, 128, 2), (64, 128, 4, 64, 3)])
+def test_conv3x3s2_matches_torch(cin, cout, k, hw, n):
     """ConvEncode's second layer (Conv2d(16, 64, 3, 2, 1), models/ODEConvGRU.py:101-119) on the tensor-core convolution
     (modules.conv3x3s2, space-to-depth) against torch's exact-fp32 operator: output and the three gradients."""
     import torch.nn as nn
@@ -357,16 +358,18 @@ def test_conv3x3s2_matches_torch():
 
     torch.backends.cudnn.allow_tf32 = False
     torch.manual_seed(2)
-    m = nn.Conv2d(16, 64, 3, 2, 1).cuda()
-    x = torch.randn(10, 16, 32, 32, device="cuda", requires_grad=True)
+    m = nn.Conv2d(cin, cout, k, 2, 1).cuda()       # k = 4: the VidODE encoder's down-sampling layers (models/VidODE.py:17-19)
+    x = torch.randn(n, cin, hw, hw, device="cuda", requires_grad=True)
     assert conv3x3s2_supported(x, m)
     y = conv3x3s2(x, m)
     ref = F.conv2d(x, m.weight, m.bias, stride=2, padding=1)
-    assert y.shape == ref.shape == (10, 64, 16, 16)
+    assert y.shape == ref.shape == (n, cout, hw // 2, hw // 2)
     assert rel_err(y, ref) < 1e-5
     w = torch.randn_like(ref)
-    gx, gw, gb = torch.autograd.grad((F.leaky_relu(y, 0.2) * w).sum(), [x, m.weight, m.bias])
-    rx, rw, rb = torch.autograd.grad((F.leaky_relu(ref, 0.2) * w).sum(), [x, m.weight, m.bias])
+    # smooth loss: a (leaky-)ReLU pre-activation within rounding noise of 0 may take the other sub-gradient branch, and one
+    # such flip among the 4e5 outputs of the larger cases is a 1e-2 max-abs difference in dx
+    gx, gw, gb = torch.autograd.grad((torch.tanh(y) * w).sum(), [x, m.weight, m.bias])
+    rx, rw, rb = torch.autograd.grad((torch.tanh(ref) * w).sum(), [x, m.weight, m.bias])
     assert rel_err(gx, rx) < 1e-5 and rel_err(gw, rw) < 1e-5 and rel_err(gb, rb) < 1e-5
 
 
@@ -415,6 +418,49 @@ def test_conv_same_matches_torch(cin, cout, hw, n):
     w = torch.randn_like(ref)
     # smooth loss: with ReLU a pre-activation within rounding noise of 0 takes the other sub-gradient branch at ~1e-6 of the
     # positions, which alone is ~1e-3 relative L2 on the gradients (measured 2.4e-3)
+    got = torch.autograd.grad((torch.tanh(y) * w).sum(), [x, m.weight, m.bias])
+    exp = torch.autograd.grad((torch.tanh(ref) * w).sum(), [x, m.weight, m.bias])
+    for g, r in zip(got, exp):
+        assert rel_l2(g, r) < 1e-5 and rel_err(g, r) < 3e-5
+
+
+@pytest.mark.parametrize("shape", [(2, 256, 32, 32), (1, 128, 64, 64), (3, 8, 5, 7)])
+def test_upsample2x_matches_torch(shape):
+    """odex_upsample2x_fwd / _bwd (bilinear, align_corners=False; the VidODE decoder's nn.Upsample, models/VidODE.py:34)
+    against torch's operator and its autograd adjoint.  Same interpolation formula in fp32: <= 1e-6."""
+    import torch.nn as nn
+    import torch.nn.functional as F
+    from ode_rl_b200.modules import upsample2x, upsample2x_supported
+
+    torch.manual_seed(6)
+    x = torch.randn(*shape, device="cuda").contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    assert upsample2x_supported(x, nn.Upsample(scale_factor=2, mode="bilinear", align_corners=False))
+    y = upsample2x(x)
+    ref = F.interpolate(x, scale_factor=2, mode="bilinear", align_corners=False)
+    assert y.shape == ref.shape and rel_err(y, ref) < 1e-6
+    w = torch.randn_like(ref)
+    (gx,) = torch.autograd.grad((y * w).sum(), [x])
+    (rx,) = torch.autograd.grad((ref * w).sum(), [x])
+    assert rel_err(gx, rx) < 1e-6
+
+
+def test_conv_same_padded_matches_torch():
+    """The VidODE decoder head (Conv2d(64, 6, 3, 1, 1) on 128x128, models/VidODE.py:42) with its output channels zero-padded
+    to 64 on the tensor-core convolution (modules.conv_same_padded): output and the three gradients against torch."""
+    import torch.nn as nn
+    import torch.nn.functional as F
+    from ode_rl_b200.modules import conv_same_padded, conv_same_padded_supported
+    from tests.util import rel_l2
+
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(8)
+    m = nn.Conv2d(64, 6, 3, 1, 1).cuda()
+    x = torch.randn(2, 64, 128, 128, device="cuda").contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    assert conv_same_padded_supported(x, m)
+    y = conv_same_padded(x, m)
+    ref = F.conv2d(x, m.weight, m.bias, padding=1)
+    assert y.shape == ref.shape and rel_l2(y, ref) < 1e-5 and rel_err(y, ref) < 3e-5
+    w = torch.randn_like(ref)
     got = torch.autograd.grad((torch.tanh(y) * w).sum(), [x, m.weight, m.bias])
     exp = torch.autograd.grad((torch.tanh(ref) * w).sum(), [x, m.weight, m.bias])
     for g, r in zip(got, exp):

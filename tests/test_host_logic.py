@@ -297,3 +297,20 @@ def test_decode_tail_function(fake_backend):
     g = torch.autograd.grad((y * w).sum(), [P, m.weight, m.bias])
     r = torch.autograd.grad((ref * w).sum(), [P, m.weight, m.bias])
     assert all(rel_err(a, b) < 1e-5 for a, b in zip(g, r))
+
+
+def test_upsample2x_autograd_wiring(fake_backend):
+    """modules.upsample2x (forward kernel + adjoint kernel behind one autograd node) against torch's interpolate."""
+    import torch.nn.functional as F
+    from ode_rl_b200 import modules
+
+    torch.manual_seed(3)
+    x = torch.randn(2, 8, 5, 6, requires_grad=True)
+    fake_backend.require = lambda t: None
+    y = modules._Upsample2xFn.apply(x)
+    ref = F.interpolate(x, scale_factor=2, mode="bilinear", align_corners=False)
+    assert rel_err(y, ref) < 1e-6
+    w = torch.randn_like(ref)
+    (g,) = torch.autograd.grad((y * w).sum(), [x])
+    (r,) = torch.autograd.grad((ref * w).sum(), [x])
+    assert rel_err(g, r) < 1e-6
