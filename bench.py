@@ -108,6 +108,10 @@ def time_cpu(method, batch, steps, warmup):
     return batch * T_OUT / dt, dt
 
 
+def print_line(text):
+    print(text, flush=True)
+
+
 # ------------------------------------------------------------------------------------------- clocks sampler
 class Clocks:
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
@@ -297,7 +301,7 @@ def vidode_main(args, world, rank, local):
                 "e2e": {"value": world * B * T_OUT * args.steps / sec_e, "unit": "frames/s", "h2d_bytes_per_step": int(xh.numel() * 4),
                         "d2h_bytes_per_step": 4, "ms_per_step": sec_e / args.steps * 1e3},
                 "gpu_launches": int(launches), "clocks": clk, "roofline": roof, "cpu_baseline": cpu}
-        print(json.dumps(line))
+        print_line(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 
@@ -308,6 +312,14 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1 and args.impl != "reference":
+        # stdout carries exactly ONE line (the JSON): NCCL prints its version banner to stdout from native code on the first
+        # collective, so file descriptor 1 points at stderr until the line is printed
+        sys.stdout.flush()
+        _saved_out = os.dup(1)
+        os.dup2(2, 1)
+        global print_line
+        print_line = lambda text: (sys.stdout.flush(), os.dup2(_saved_out, 1), print(text, flush=True))
     if args.workload == "vidode" and args.impl != "reference":
         return vidode_main(args, world, rank, local)
 
@@ -560,7 +572,7 @@ def main():
                         "pipeline": "pinned host -> staging buffer on a copy stream, overlapping the previous step; staging -> step "
                                     "inputs device-to-device at the start of the step; loss read back (synchronising) every step"},
                 "gpu_launches": int(launches), "clocks": clk, "roofline": roof, "rk_stage": rk, "cpu_baseline": cpu}
-        print(json.dumps(line))
+        print_line(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 
