@@ -243,3 +243,63 @@ def test_vidode_golden(name):
     torch.cuda.synchronize()
     assert _lib.launch_count() > n0, "no libodex kernel launched"
     check_vidode(rec, model, pred, extra)
+
+
+def test_vidode_training_gradients_vs_oracle():
+    """Backward through the whole VidODE wiring (rk4): the product (libodex hot path + the tensor-core torch-side convolutions,
+    upsample adjoint, space-to-depth encoder) against autograd through oracle/refmodel.vidode_forward on the CPU, same
+    seeded weights and frames.  ReLU / BatchNorm graph: a pre-activation within rounding noise of 0 may take the other
+    sub-gradient branch, hence the 5e-3 relative-L2 bar of the other ReLU gradient tests (measured: 1e-6 for the layers behind
+    no ReLU, ~1e-3 per ReLU crossed, 2.3e-3 at the far end); the loss itself <= 1e-5."""
+    from tests.test_golden import load_vidode_case
+
+    rec, model, frames, batch = load_vidode_case("rk4", DEV)
+    sd = {k: v.detach().cpu().clone().requires_grad_(v.dtype.is_floating_point and "running" not in k)
+          for k, v in model.state_dict().items()}
+    torch.manual_seed(12)
+    target = torch.rand(rec["B"], rec["T"], rec["C"], rec["S"], rec["S"])
+    pred, _ = model(frames, batch)
+    loss = (pred - target.to(DEV)).abs().mean()           # models/VidODE.py:188-199 get_mse is an L1 mean
+    loss.backward()
+    _, _, rpred = refmodel.vidode_forward(sd, frames.cpu(), batch["observed_tp"].cpu(), batch["tp_to_predict"].cpu(), "rk4")
+    rloss = (rpred - target).abs().mean()
+    rloss.backward()
+    assert abs(float(loss) - float(rloss)) <= 1e-5 * abs(float(rloss))
+    errs = {}
+    bn_fed_bias = {"conv_encoder.cnn_encoder.%d.bias" % i for i in (0, 3, 6)} | {"conv_decoder.cnn_decoder.%d.bias" % i for i in (1, 5)}
+    for n, p in model.named_parameters():
+        if n.startswith("diffeq_solver.") or n.startswith("encoder_z0.ode_func."):
+            continue                                       # aliases of ode_decoder_func / ode_encoder_func
+        g = sd[n].grad
+        a = sd.get("diffeq_solver.ode_func." + n[len("ode_decoder_func."):]) if n.startswith("ode_decoder_func.") else None
+        b = sd.get("encoder_z0.ode_func." + n[len("ode_encoder_func."):]) if n.startswith("ode_encoder_func.") else None
+        for alias in (a, b):                               # the functional oracle reads the aliased entries of the state_dict
+            if alias is not None and alias.grad is not None:
+                g = alias.grad if g is None else g + alias.grad
+        assert p.grad is not None and g is not None, n
+        if n in bn_fed_bias:
+            # a bias added right before a training-mode BatchNorm has an exactly-zero gradient (the batch mean removes it):
+            # both sides are rounding noise, so it is bounded against the same layer's weight gradient instead of compared
+            wg = dict(model.named_parameters())[n[:-4] + "weight"].grad
+            assert float(p.grad.norm()) < 1e-4 * float(wg.norm()) and float(g.norm()) < 1e-4 * float(wg.norm()), n
+            continue
+        errs[n] = rel_l2(p.grad, g)
+    print({k: "%.1e" % v for k, v in errs.items()})
+    assert max(errs.values()) < 5e-3, errs
+
+
+def test_convgru_multi_step_without_inputs():
+    """ConvGRUCell(input_tensor=None, seq_len=3): the plain ConvGRU model's decoding mode (modules/ConvGRUCell.py:66-84,
+    models/ConvGRU.py:144,234) loops the fused step on zero inputs."""
+    torch.manual_seed(3)
+    cell = odex.ConvGRUCell((16, 16), 64, 64, 5).to(DEV)
+    h0 = torch.randn(2, 64, 16, 16)
+    with torch.no_grad():
+        out, hn = cell(None, h0.to(DEV), seq_len=3, dim=1)
+    sd = _sd_cpu(cell)
+    h, hs = h0, []
+    for _ in range(3):
+        h = refmodel.convgru_step(sd, torch.zeros(2, 64, 16, 16), h)
+        hs.append(h)
+    assert out.shape == (2, 3, 64, 16, 16)
+    assert rel_err(hn, h) < 1e-5 and rel_err(out, torch.stack(hs, dim=1)) < 1e-5
