@@ -274,10 +274,15 @@ def vidode_main(args, world, rank, local):
         fl = 2 * B * 32 * 32 * 256 * 256 * 25
         peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
         roof = {"bound": "tensor", "kernel": "conv_tc_kernel<128> (ConvGRU gates 5x5 256->256 on 32x32, 3xTF32, tcgen05 kind::tf32)",
-                "achieved": fl / avg / 1e12, "peak": peak, "unit": "TFLOP/s", "frac": fl / avg / 1e12 / peak, "traffic": None,
+                "achieved": fl / avg / 1e12, "peak": peak, "unit": "TFLOP/s", "frac": fl / avg / 1e12 / peak,
+                # dram__bytes_read.sum + dram__bytes_write.sum of the two N-block launches of one such convolution at batch 32
+                # (ncu --set full, profiles/r01_vidode_ncu.md: 40.15 MB + 0.35 MB each; the second block's inputs hit L2)
+                "traffic": int(2 * (40151040 + 349184) * B / 32), "traffic_source": "profiles/r01_vidode_ncu.md (ncu --set full)",
                 "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (of measured)" if peaks else "fallback 1.4 PF (of fallback)",
                 "note": "algorithmic FLOPs counted once; 3 TF32 MMAs per useful one at half the bf16 rate: frac*6 = share of tensor "
-                        "issue slots; %d launches back to back, batch %d" % (reps, B),
+                        "issue slots against the SUSTAINED bf16 figure (it can exceed 1: a lone kernel runs at the burst clock, "
+                        "ceiling = bf16 burst / 6); ncu: tensor pipe active 77 %% of SM-active cycles; %d convolutions (2 N-block "
+                        "launches each) back to back, batch %d" % (reps, B),
                 "launches_timed": reps, "avg_launch_us": avg * 1e6}
         if not args.no_cpu_baseline and world == 1:
             v, dt = vidode_cpu(2, 1)

@@ -52,13 +52,20 @@ def launches(path):
 
 
 def main():
+    global KERNELS
     tag = sys.argv[1]
-    print("# %s - ncu summary of one eager training step (configs[1]: rk4, B=128, 1 x B200)\n" % tag)
-    print("Produced by `tools/profile_pass.sh` under gpurun (after the same script exited 0 without ncu), summarised by")
-    print("`tools/ncu_summary.py %s`.  Times under ncu are cold-cache and serialised: shares, not absolutes.\n" % tag)
+    vid = len(sys.argv) > 2 and sys.argv[2] == "vidode"
+    what = "one VidODE forward (configs[4]: 128x128x3, dopri5, B=32, 1 x B200)" if vid else \
+        "one eager training step (configs[1]: rk4, B=128, 1 x B200)"
+    script = "tools/vidode_one_forward.py" if vid else "tools/one_step.py"
+    if vid:
+        KERNELS = ["conv_tc_kernel128", "conv_tc_kernel64", "upsample2x_fwd_kernel", "conv_tc2_kernel"]
+    print("# %s - ncu summary of %s\n" % (tag, what))
+    print("Produced by `tools/profile_pass%s.sh` under gpurun (after the same script exited 0 without ncu), summarised by" % ("_vidode" if vid else ""))
+    print("`tools/ncu_summary.py %s`.  Times under ncu are cold-cache and serialised: shares, not absolutes.\n" % " ".join(sys.argv[1:]))
     agg, tot, n = launches("gpurun_out/launches_%s.csv" % tag)
-    print("## Launch list (`ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none python tools/one_step.py`)\n")
-    print("%d kernel launches in the step, %.2f ms summed.\n" % (n, tot / 1000))
+    print("## Launch list (`ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none python %s`)\n" % script)
+    print("%d kernel launches, %.2f ms summed.\n" % (n, tot / 1000))
     print("| share | total us | launches | avg us | kernel |\n|---|---|---|---|---|")
     ours = 0.0
     for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1]):
@@ -66,8 +73,9 @@ def main():
             ours += v[1]
     for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1])[:24]:
         print("| %.1f %% | %.1f | %d | %.1f | `%s` |" % (100 * v[1] / tot, v[1], v[0], v[1] / v[0], k))
-    print("\nlibodex kernels: %.1f %% of the summed device time; the rest is what is left of the torch-side ConvEncode/ConvDecode (their"
-          " first / last layers, activations, layout shuffles), the loss and Adam.\n" % (100 * ours / tot))
+    print("\nlibodex kernels: %.1f %% of the summed device time; the rest is what is left on the torch side (%s).\n" % (
+        100 * ours / tot, "BatchNorm / ReLU passes, the 3-channel stem, cat, layout copies, grid_sample" if vid else
+        "first / last layers of ConvEncode / ConvDecode, activations, layout shuffles, the loss and Adam"))
     for k in KERNELS:
         try:
             hdr, units, rows = raw("gpurun_out/prof_%s_%s.ncu-rep" % (tag, k))
