@@ -328,6 +328,22 @@ def main():
     if args.workload == "vidode" and args.impl != "reference":
         return vidode_main(args, world, rank, local)
 
+    if args.impl == "reference" and args.workload == "vidode":
+        if rank != 0:
+            return
+        cb = min(args.cpu_batch, 4)
+        val, dt = vidode_cpu(cb, max(1, args.steps))
+        cores = os.cpu_count() or 1
+        print(json.dumps({
+            "impl": "reference", "metric": "VidODE forward predicted frames/s", "value": val, "unit": "frames/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "VidODE forward, 128x128x3, 10 in / 10 out, dopri5 rtol=1e-4 atol=1e-5", "batch_per_step": cb},
+            "cpu_baseline": {"value": val, "unit": "frames/s", "cores": cores, "kind": "port",
+                             "sample": "batch %d forwards of the configs[4] workload (models/VidODE.py wiring restated in "
+                                       "oracle/refmodel.vidode_forward + restated torchdiffeq 0.2.1; torch CPU, %d threads)" % (cb, cores)},
+            "e2e": {"value": val, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
     if args.impl == "reference":
         if rank != 0:
             return
@@ -364,7 +380,11 @@ def main():
     model = ODEConvGRUHarness(args.method, rtol=1e-3, atol=1e-4, device=dev).to(dev)
     params = [p for p in model.parameters()]
     use_graph = (not args.no_graph) and args.method != "dopri5"   # dopri5 reads its controller state on the host
-    opt = torch.optim.Adam(params, lr=1e-3, capturable=use_graph)
+    # torch's single-kernel Adam (same update rule as the reference's torch.optim.Adam, train_test.py; 20.31 -> 20.14 ms/step);
+    # ODEX_FUSED_ADAM=0 selects the default foreach implementation
+    fused_adam = os.environ.get("ODEX_FUSED_ADAM", "1") == "1"
+    opt = torch.optim.Adam(params, lr=1e-3, capturable=use_graph, fused=fused_adam) if fused_adam else \
+        torch.optim.Adam(params, lr=1e-3, capturable=use_graph)
     from ode_rl_b200 import parallel
     if world > 1:
         parallel.shard_solver(model.diffeq_solver, mode="sum")                # dopri5: batch-shared step size (SUM = parity mode)
@@ -571,7 +591,7 @@ def main():
                                                                                   " adaptive rtol=1e-3 atol=1e-4, device-resident controller"), B),
                            "global_batch": B * world, "parallelism": "batch-sharded dp%d, NCCL flat-bucket gradient allreduce" % world,
                            "l2": "no explicit flush: the per-step working set (saved activations ~2 GB) is >> the 126 MB L2",
-                           "cuda_graph": graphed is not None},
+                           "cuda_graph": graphed is not None, "optimizer": "torch.optim.Adam(fused=%s)" % fused_adam},
                 "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": int(xh.numel() * 4 + yh.numel() * 4),
                         "d2h_bytes_per_step": 4, "ms_per_step": sec_e / args.steps * 1e3,
                         "pipeline": "pinned host -> staging buffer on a copy stream, overlapping the previous step; staging -> step "
