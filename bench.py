@@ -44,6 +44,8 @@ def parse():
     ap.add_argument("--cpu-batch", type=int, default=16)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="enqueue every step from Python instead of replaying a CUDA graph")
+    ap.add_argument("--forward-only", action="store_true",
+                    help="time the model forward alone (no_grad) instead of the training step: SURVEY.md 8d cfg3 (dopri5, batch 512)")
     ap.add_argument("--workload", default="odeconvgru", choices=["odeconvgru", "vidode"],
                     help="odeconvgru = BASELINE configs[1] (the default, the driver's line); vidode = configs[4]: VidODE forward at "
                          "128x128x3, dopri5, 32 sequences per GPU (use --batch 32)")
@@ -379,7 +381,7 @@ def main():
     torch.manual_seed(0)
     model = ODEConvGRUHarness(args.method, rtol=1e-3, atol=1e-4, device=dev).to(dev)
     params = [p for p in model.parameters()]
-    use_graph = (not args.no_graph) and args.method != "dopri5"   # dopri5 reads its controller state on the host
+    use_graph = (not args.no_graph) and args.method != "dopri5" and not args.forward_only   # dopri5 reads its controller state on the host
     # torch's single-kernel Adam (same update rule as the reference's torch.optim.Adam, train_test.py; 20.31 -> 20.14 ms/step);
     # ODEX_FUSED_ADAM=0 selects the default foreach implementation
     fused_adam = os.environ.get("ODEX_FUSED_ADAM", "1") == "1"
@@ -394,6 +396,9 @@ def main():
     obs, tp = times(dev)
 
     def step_eager(xd, yd):
+        if args.forward_only:
+            with torch.no_grad():
+                return torch.nn.functional.mse_loss(model(xd, obs, tp, return_latents=False), yd)
         opt.zero_grad(set_to_none=True)
         pred = model(xd, obs, tp, return_latents=False)
         loss = torch.nn.functional.mse_loss(pred, yd)
@@ -581,12 +586,14 @@ def main():
             cpu = {"value": v, "unit": "frames/s", "cores": os.cpu_count() or 1, "kind": "port",
                    "sample": "2 timed training steps at batch %d (of the batch-%d workload) on the host cores; oracle/refmodel.py + "
                              "restated torchdiffeq, torch CPU fp32, anomaly mode off" % (args.cpu_batch, B)}
-        line = {"metric": "ODEConvGRU training-step predicted frames/s", "value": value, "unit": "frames/s",
-                "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": sec / args.steps * 1e3,
+        line = {"metric": "ODEConvGRU %s predicted frames/s" % ("forward" if args.forward_only else "training-step"), "value": value,
+                "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": sec / args.steps * 1e3,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32 (3xTF32 tensor-core convs, fp32 accumulate)",
                 "data": "synthetic",
-                "config": {"workload": "BASELINE configs[%s]: ODEConvGRU forward+backward+Adam, %s, batch %d per GPU, "
-                                       "10 in / 10 out 64x64x1" % ("1" if args.method != "dopri5" else "2 (as a training step)",
+                "config": {"workload": "BASELINE configs[%s]: ODEConvGRU %s, %%s, batch %%d per GPU, "
+                                       "10 in / 10 out 64x64x1" % (("1" if args.method != "dopri5" else "2 (as a training step)") if not args.forward_only else
+                                                                   ("2" if args.method == "dopri5" else "1 (forward only)"),
+                                                                   "forward (no_grad)" if args.forward_only else "forward+backward+Adam") % (
                                                                    args.method + (" fixed-step" if args.method != "dopri5" else
                                                                                   " adaptive rtol=1e-3 atol=1e-4, device-resident controller"), B),
                            "global_batch": B * world, "parallelism": "batch-sharded dp%d, NCCL flat-bucket gradient allreduce" % world,
