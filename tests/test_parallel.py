@@ -142,3 +142,84 @@ def test_shard_range_ragged_and_empty():
     assert covered == list(range(513))
     with pytest.raises(ValueError):
         shard_range(4, 2, 2)
+
+
+# ---- BASELINE configs[4]: VidODE sharded by batch (bench.py --workload vidode --gpus N) -------------------------------------
+def _vidode_model_and_batch():
+    import numpy as np
+    from ode_rl_b200.harness import VidODEHarness
+
+    torch.manual_seed(0)
+    model = VidODEHarness("dopri5", in_channels=3, resolution=32).eval()      # eval: BatchNorm per sample, so shards == whole
+    with torch.no_grad():
+        for p in model.ode_decoder_func.parameters():
+            p.mul_(4.0)                                                       # several attempts, some rejected
+    B, T = 4, 3
+    frames = torch.rand(B, T, 3, 32, 32, generator=torch.Generator().manual_seed(7))
+    frames[2:] *= 3.0                                                         # the shards' error norms differ
+    ts = torch.tensor(np.arange(0, 2 * T) / (2 * T))
+    batch = {"observed_tp": ts[:T], "tp_to_predict": ts[T:], "observed_mask": torch.ones(B, T, 1),
+             "mask_predicted_data": torch.ones(B, T, 1)}
+    return model, frames, batch
+
+
+def _vidode_worker(rank, world, port, q):
+    if ROOT not in sys.path:
+        sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.set_num_threads(2)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from ode_rl_b200 import kernels, parallel
+        from tests.fake_backend import FakeBackend
+
+        kernels.set_backend(FakeBackend())
+        model, frames, batch = _vidode_model_and_batch()
+        parallel.shard_solver(model.diffeq_solver, mode="sum")
+        lo, hi = parallel.shard_range(frames.shape[0], rank, world)
+        with torch.no_grad():
+            pred, extra = model(frames[lo:hi], batch)
+        st = model.diffeq_solver.last_stats
+        q.put((rank, pred.contiguous().numpy().copy(), extra["sol_y"].contiguous().numpy().copy(),
+               [(a[1], a[3]) for a in st.attempts]))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_gloo_vidode_forward_equals_single_process():
+    """Each rank runs the VidODE forward on its half of the sequences with the dopri5 error norm all-reduced (SUM): the
+    ranks take the step sequence of one process on the whole batch and the concatenated predictions equal its output."""
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_vidode_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = {}
+    for _ in range(world):
+        r = q.get(timeout=240)
+        res[r[0]] = r
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    assert res[0][3] == res[1][3]
+
+    from ode_rl_b200 import kernels
+    from tests.fake_backend import FakeBackend
+
+    prev = kernels.set_backend(FakeBackend())
+    try:
+        model, frames, batch = _vidode_model_and_batch()
+        with torch.no_grad():
+            pred, extra = model(frames, batch)
+        st = model.diffeq_solver.last_stats
+    finally:
+        kernels.set_backend(prev)
+    assert len(st.attempts) == len(res[0][3]) and st.n_reject + st.n_accept >= 2
+    for (dt_a, acc_a), b in zip(res[0][3], st.attempts):
+        assert bool(acc_a) == bool(b[3]) and abs(dt_a - b[1]) <= 1e-9 * abs(b[1])
+    sol = torch.cat([torch.from_numpy(res[0][2]), torch.from_numpy(res[1][2])], dim=0)
+    prd = torch.cat([torch.from_numpy(res[0][1]), torch.from_numpy(res[1][1])], dim=0)
+    assert (sol - extra["sol_y"]).abs().max() <= 1e-5 * extra["sol_y"].abs().max()
+    assert (prd - pred).abs().max() <= 1e-5 * pred.abs().max()
