@@ -30,7 +30,7 @@ FEVAL_FLOPS = 94371840            # per sample, 5 x conv3x3 64->64 at 16x16 (SUR
 CONV3_FLOPS = 2 * 256 * 64 * 576  # one 3x3 64->64 conv, per sample
 
 
-NET_TRAFFIC_B128 = 10488704  # bytes per launch at batch 128: dram read 9.95 MB + written 0.54 MB (ncu --set full, profiles/r01_final_ncu.md)
+NET_TRAFFIC_B128 = 10654848  # bytes per launch at batch 128: dram read 9.95 MB + written 0.42-0.98 MB (mean of the two launches captured; ncu --set full, profiles/r01_final_ncu.md)
 
 
 def parse():

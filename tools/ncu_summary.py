@@ -91,6 +91,10 @@ def main():
                 continue
             i = hdr.index(m)
             print("| %s | " % label + " | ".join("%s %s" % (r[i], units[i]) for r in rows) + " |")
+        if k == "conv_tc2_kernel" and not vid and any(", 1>" in nm for nm in names):
+            print("\nThe instances captured here are the 1x1 `transform_z0` convolutions (`<N, 1>`: 6 MFLOP per sample, latency-bound "
+                  "by construction); in this build the 3x3 64->64 shapes run inside `convnet_tc_kernel`, and the 3x3 `conv_tc2` "
+                  "instances of the step (ConvEncode / ConvDecode helpers) are in the launch list above.")
         print()
 
 
