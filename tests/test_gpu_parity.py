@@ -347,3 +347,9 @@ def test_dopri5_properties_at_full_batch():
     assert sa.n_accept >= 1 and sa.t_final >= float(tp[-1]) - 1e-12
     assert sb.host_syncs == 1
     assert bool(torch.isfinite(a).all())
+
+
+def test_dopri5_error_behaviour_on_device():
+    from tests.test_host_logic import _dopri_error_cases
+
+    _dopri_error_cases(odex, DEV)

@@ -314,3 +314,31 @@ def test_upsample2x_autograd_wiring(fake_backend):
     (g,) = torch.autograd.grad((y * w).sum(), [x])
     (r,) = torch.autograd.grad((ref * w).sum(), [x])
     assert rel_err(g, r) < 1e-6
+
+
+def _dopri_error_cases(odex, device):
+    """torchdiffeq's asserts (rk_common._adaptive_step; SURVEY.md 8b 'Errors') raised once per forward from the device-side
+    sticky status word: non-finite state (surfacing as torchdiffeq does, through the dt check), max_num_steps."""
+    f = make_ode_func(odex, C=32, n_units=32, scale=4.0).to(device)
+    _, tp = timesteps(4, 4)
+    tp = tp.to(device)
+    torch.manual_seed(1)
+    z0 = torch.randn(2, 32, 8, 16, device=device)
+    solver = odex.DiffEqSolver(f, "dopri5", odeint_rtol=1e-3, odeint_atol=1e-4)
+    bad = z0.clone()
+    bad[1, 3, 2, 5] = float("nan")
+    with torch.no_grad():
+        # a NaN in y0 makes the initial step NaN, and torchdiffeq's FIRST assert in _adaptive_step is `t0 + dt > t0`:
+        # the oracle raises 'underflow in dt nan' for this input and so must the product
+        with pytest.raises(AssertionError, match="underflow in dt nan"):
+            solver(bad, tp)
+        tight = odex.DiffEqSolver(f, "dopri5", odeint_rtol=1e-9, odeint_atol=1e-10)
+        tight.max_attempts = 3
+        with pytest.raises(AssertionError, match="max_num_steps"):
+            tight(z0, tp)
+        sol = solver(z0, tp)                    # the sticky flags do not leak into the next forward
+    assert bool(torch.isfinite(sol).all()) and solver.last_stats.status == 0
+
+
+def test_dopri5_error_behaviour(fake_backend):
+    _dopri_error_cases(odex, torch.device("cpu"))
