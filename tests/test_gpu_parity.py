@@ -353,3 +353,26 @@ def test_dopri5_error_behaviour_on_device():
     from tests.test_host_logic import _dopri_error_cases
 
     _dopri_error_cases(odex, DEV)
+
+
+def test_large_batch_indexing():
+    """Maximum sizes: B=4096 (sol is 2.7 GB: byte offsets pass 2^31, element offsets of [T,B,...] arenas pass 2^29).  The path
+    is per-sample, so the LAST sample of the large run must equal the same sample run alone, bitwise -- for the rk4 solver
+    (solution rows beyond the 2 GiB mark) and for the encoder recurrence (T=3)."""
+    f = make_ode_func(odex, C=64, n_units=64).to(DEV)
+    solver = odex.DiffEqSolver(f, "rk4")
+    _, tp = timesteps(10, 10, device=DEV)
+    torch.manual_seed(8)
+    z0 = torch.randn(4096, 64, 16, 16, device=DEV)
+    with torch.no_grad():
+        big = solver(z0, tp)
+        one = solver(z0[4095:4096], tp)
+    assert torch.equal(big[:, 4095:4096], one) and torch.equal(big[0], z0)
+    del big
+    cell = odex.ODEConvGRUCell(f, None, (16, 16), 64).to(DEV)
+    obs, _ = timesteps(3, 3, device=DEV)
+    x = torch.randn(3, 4096, 64, 16, 16, device=DEV)
+    with torch.no_grad():
+        m_big, _ = cell(x, obs)
+        m_one, _ = cell(x[:, 4095:4096].contiguous(), obs)
+    assert torch.equal(m_big[4095:4096], m_one)
