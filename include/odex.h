@@ -144,6 +144,17 @@ int odex_decode_tail_fwd(const float* p, int n, int cells_h, int cells_w, int C,
 int odex_decode_tail_bwd(const float* p, const float* dout, int n, int cells_h, int cells_w, int C, const float* w,
                          float slope, float* dp, float* dw, float* db, odex_stream_t s);
 
+/* ------------------------------------------------------------------------------------------------ encoder stem
+ * Conv2d(1, C, 3, 2, 1) + LeakyReLU(slope) of ConvEncode (models/ODEConvGRU.py:101-119, the first layer and its activation)
+ * on [n][H][W] single-channel frames, written in the space-to-depth layout the strided tensor-core convolution reads:
+ * cells[n][Y][X][(a*2+b)*C + c] = leaky(conv(x) + b)[n][c][2Y+a][2X+b], Y < H/4, X < W/4.  w: [C][9] (torch [C,1,3,3]), b: [C]
+ * or NULL.  Backward (no gradient for the frames): dw[C][9] +=, db[C] += (nullable) from dcells and the saved cells.
+ * Shapes taken: H = W = 64, C = 16 (config A); otherwise ODEX_E_UNSUPPORTED (the caller stays on torch). */
+int odex_encode_stem_fwd(const float* x, int n, int H, int W, int C, const float* w, const float* b, float slope,
+                         float* cells, odex_stream_t s);
+int odex_encode_stem_bwd(const float* x, const float* cells, const float* dcells, int n, int H, int W, int C, float slope,
+                         float* dw, float* db, odex_stream_t s);
+
 /* ------------------------------------------------------------------------------------------------ bilinear 2x upsample
  * nn.Upsample(scale_factor=2, mode='bilinear', align_corners=False) of the VidODE per-step decoder (models/VidODE.py:34),
  * NHWC fp32: x [n][H][W][C] -> out [n][2H][2W][C]; _bwd is its adjoint: dout [n][2H][2W][C] -> dx [n][H][W][C] (overwritten).

@@ -99,6 +99,8 @@ SIGNATURES = {
     "odex_convnet_supported": (_i, [C.POINTER(ConvNetDesc)]),
     "odex_decode_tail_fwd": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _f, _vp, _vp]),
     "odex_decode_tail_bwd": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _f, _vp, _vp, _vp, _vp]),
+    "odex_encode_stem_fwd": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _f, _vp, _vp]),
+    "odex_encode_stem_bwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _f, _vp, _vp, _vp]),
     "odex_upsample2x_fwd": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "odex_upsample2x_bwd": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "odex_conv2d_wgrad": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp]),

@@ -12,7 +12,7 @@ import os
 import torch
 import torch.nn as nn
 
-from .modules import conv_same_padded, conv_same_padded_supported, DiffEqSolver, ODEConvGRUCell, ODEFunc, conv3x3s2, conv3x3s2_supported, conv_transpose4x4s2_phases, conv_transpose4x4s2_supported, conv_same, conv_same_supported, decode_tail, decode_tail_supported, phases_to_nchw, upsample2x, upsample2x_supported
+from .modules import encode_stem_supported, encode_stem_then_conv, conv_same_padded, conv_same_padded_supported, DiffEqSolver, ODEConvGRUCell, ODEFunc, conv3x3s2, conv3x3s2_supported, conv_transpose4x4s2_phases, conv_transpose4x4s2_supported, conv_same, conv_same_supported, decode_tail, decode_tail_supported, phases_to_nchw, upsample2x, upsample2x_supported
 
 
 class _Encoder(nn.Module):          # models/ODEConvGRU.py:101-119 with n_downs == 2
@@ -25,6 +25,10 @@ class _Encoder(nn.Module):          # models/ODEConvGRU.py:101-119 with n_downs 
     def forward(self, x):
         e = self.encoder
         if self.fast_second_layer:
+            if encode_stem_supported(x, e[0], e[1], e[2]):
+                # the 1 -> 16 stem + LeakyReLU as one HBM-bound kernel that writes the space-to-depth cells the strided
+                # tensor-core convolution reads (no cuDNN SGEMM / activation / shuffle passes; backward: dw, db in one kernel)
+                return nn.functional.leaky_relu(encode_stem_then_conv(x, e[0], e[1], e[2]), e[3].negative_slope)
             h = e[1](e[0](x))
             if conv3x3s2_supported(h, e[2]):
                 # the 16 -> 64 strided convolution as a 3x3 convolution over space-to-depth cells on the

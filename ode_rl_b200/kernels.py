@@ -196,6 +196,29 @@ class Backend:
         _lib.check(self.lib.odex_decode_tail_bwd(p.data_ptr(), dout.data_ptr(), n, hc, wc, c4 // 4, w.data_ptr(), float(slope),
                                                  dp.data_ptr(), _ptr(dw), _ptr(db), _stream()), "odex_decode_tail_bwd")
 
+    # ------------------------------------------------------------------ encoder stem (Conv2d(1,16,3,2,1) + LeakyReLU -> cells)
+    @staticmethod
+    def encode_stem_supported(x: torch.Tensor, cout: int) -> bool:
+        return x.dim() == 4 and tuple(x.shape[1:]) == (1, 64, 64) and cout == 16 and x.shape[0] > 0
+
+    def encode_stem_fwd(self, x: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor], slope: float,
+                        cells: torch.Tensor) -> torch.Tensor:
+        """odex_encode_stem_fwd: x [n,1,64,64] -> cells [n,16,16,64] (space-to-depth of the activated 16-channel output)."""
+        self.require(x)
+        n = x.shape[0]
+        assert x.is_contiguous() and w.is_contiguous() and cells.is_contiguous() and tuple(cells.shape) == (n, 16, 16, 64)
+        _lib.check(self.lib.odex_encode_stem_fwd(x.data_ptr(), n, 64, 64, 16, w.data_ptr(), _ptr(b), float(slope),
+                                                 cells.data_ptr(), _stream()), "odex_encode_stem_fwd")
+        return cells
+
+    def encode_stem_bwd(self, x: torch.Tensor, cells: torch.Tensor, dcells: torch.Tensor, slope: float,
+                        dw: Optional[torch.Tensor], db: Optional[torch.Tensor]) -> None:
+        """odex_encode_stem_bwd: dw [16,9] +=, db [16] += from the saved cells and their gradient."""
+        n = x.shape[0]
+        assert x.is_contiguous() and cells.is_contiguous() and dcells.is_contiguous() and dcells.shape == cells.shape
+        _lib.check(self.lib.odex_encode_stem_bwd(x.data_ptr(), cells.data_ptr(), dcells.data_ptr(), n, 64, 64, 16, float(slope),
+                                                 _ptr(dw), _ptr(db), _stream()), "odex_encode_stem_bwd")
+
     # ------------------------------------------------------------------ bilinear 2x upsample (NHWC)
     def upsample2x_fwd(self, x: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
         """odex_upsample2x_fwd: x [n,H,W,C] -> out [n,2H,2W,C] (align_corners=False)."""

@@ -269,6 +269,105 @@ class _Conv3x3s2Fn(torch.autograd.Function):
         return dx, dw, db
 
 
+class _ConvCellsFn(torch.autograd.Function):
+    """The strided convolution of _Conv3x3s2Fn on an input that already IS in space-to-depth cells [n, H, W, 4*Cin] (what
+    odex_encode_stem_fwd writes): no shuffle on the way in, and the data gradient goes back in the same layout."""
+
+    @staticmethod
+    def forward(ctx, xs: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor]):
+        be = K.backend()
+        be.require(xs)
+        n, H, W, c4 = xs.shape
+        cout = weight.shape[0]
+        xs = xs.detach()
+        w3 = _cs_w3(weight.float())
+        out = torch.empty((n, H, W, cout), dtype=torch.float32, device=xs.device)
+        be.conv2d(xs, None, None, be.pack_weights(w3, dgrad=False, tc=True), cout, 3,
+                  bias.detach().float() if bias is not None else None, ACT_NONE, out, impl=CONV_TC)
+        ctx.save_for_backward(xs, w3)
+        ctx.has_bias = bias is not None
+        ctx.cin, ctx.k = c4 // 4, weight.shape[-1]
+        return from_nhwc(out)
+
+    @staticmethod
+    def backward(ctx, dout):
+        be = K.backend()
+        xs, w3 = ctx.saved_tensors
+        n, H, W, c4 = xs.shape
+        cin, cout = ctx.cin, w3.shape[0]
+        dy = to_nhwc(dout.float())
+        if not dy.is_contiguous():
+            dy = dy.contiguous()
+        dxs = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dxs = torch.empty((n, H, W, c4), dtype=torch.float32, device=xs.device)
+            be.conv2d(dy, None, None, be.pack_weights(w3, dgrad=True, tc=True), c4, 3, None, ACT_NONE, dxs, impl=CONV_TC)
+        if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
+            dwp = torch.zeros((9, cout, c4), dtype=torch.float32, device=xs.device)
+            dbv = torch.zeros((cout,), dtype=torch.float32, device=xs.device)
+            be.conv2d_wgrad_packed(xs, None, dy, 3, dwp, dbv)
+            dw3 = torch.zeros((cout, c4, 3, 3), dtype=torch.float32, device=xs.device)
+            be.wgrad_unpack(dwp, dw3)
+            dw = _cs_dw(dw3, cout, cin, ctx.k)
+            if ctx.has_bias:
+                db = dbv
+        return dxs, dw, db
+
+
+class _EncodeStemFn(torch.autograd.Function):
+    """Conv2d(1, 16, 3, 2, 1) + LeakyReLU on [n,1,64,64] frames -> space-to-depth cells [n,16,16,64] (odex_encode_stem_fwd);
+    backward gives dw / db only: the frames are data."""
+
+    @staticmethod
+    def forward(ctx, x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], slope: float):
+        be = K.backend()
+        be.require(x)
+        xc = x.detach().float().contiguous()
+        w = weight.detach().float().reshape(16, 9).contiguous()
+        cells = torch.empty((x.shape[0], 16, 16, 64), dtype=torch.float32, device=x.device)
+        be.encode_stem_fwd(xc, w, bias.detach().float() if bias is not None else None, slope, cells)
+        ctx.save_for_backward(xc, cells)
+        ctx.slope, ctx.has_bias = slope, bias is not None
+        return cells
+
+    @staticmethod
+    def backward(ctx, dcells):
+        if ctx.needs_input_grad[0]:
+            raise RuntimeError("encode_stem: the frames do not get a gradient on this path (use the torch layers)")
+        xc, cells = ctx.saved_tensors
+        d = dcells.float()
+        if not d.is_contiguous():
+            d = d.contiguous()
+        dw = torch.zeros((16, 9), dtype=torch.float32, device=xc.device)
+        db = torch.zeros((16,), dtype=torch.float32, device=xc.device) if ctx.has_bias else None
+        K.backend().encode_stem_bwd(xc, cells, d, ctx.slope, dw, db)
+        return None, dw.view(16, 1, 3, 3), db, None
+
+
+def encode_stem_supported(x: torch.Tensor, conv: nn.Module, act: nn.Module, nxt: nn.Module) -> bool:
+    """True when (conv, act) are ConvEncode's Conv2d(1, 16, 3, 2, 1) + LeakyReLU on 64x64 frames that need no gradient and
+    `nxt` is a strided convolution the tensor-core path takes on the resulting 16x16 cells."""
+    if not (isinstance(conv, nn.Conv2d) and isinstance(act, nn.LeakyReLU) and isinstance(nxt, nn.Conv2d)):
+        return False
+    if not (conv.in_channels == 1 and conv.kernel_size == (3, 3) and conv.stride == (2, 2) and conv.padding == (1, 1)
+            and conv.dilation == (1, 1) and conv.padding_mode == "zeros" and act.negative_slope > 0):
+        return False
+    if not (x.is_cuda and x.dtype == torch.float32 and not x.requires_grad
+            and K.backend().encode_stem_supported(x, conv.out_channels)):
+        return False
+    return nxt.in_channels == conv.out_channels and nxt.kernel_size in ((3, 3), (4, 4)) and nxt.stride == (2, 2) \
+        and nxt.padding == (1, 1) and nxt.dilation == (1, 1) and nxt.groups == 1 and nxt.padding_mode == "zeros" \
+        and K.tc_shape_ok(nxt.out_channels, 4 * nxt.in_channels, 0, 16, 16, 3) \
+        and K.tc_shape_ok(4 * nxt.in_channels, nxt.out_channels, 0, 16, 16, 3)
+
+
+def encode_stem_then_conv(x: torch.Tensor, conv: nn.Conv2d, act: nn.LeakyReLU, nxt: nn.Conv2d) -> torch.Tensor:
+    """nxt(act(conv(x))) for ConvEncode's first two layers: the stem kernel writes the activated 16-channel map as
+    space-to-depth cells, which the strided tensor-core convolution reads directly (no NCHW intermediate, no shuffle)."""
+    cells = _EncodeStemFn.apply(x, conv.weight, conv.bias, float(act.negative_slope))
+    return _ConvCellsFn.apply(cells, nxt.weight, nxt.bias)
+
+
 def conv3x3s2_supported(x: torch.Tensor, m: nn.Module) -> bool:
     """True when `m` is a Conv2d(k=3 or 4, s=2, p=1) that the tensor-core convolution can take for input x."""
     if not (isinstance(m, nn.Conv2d) and m.kernel_size in ((3, 3), (4, 4)) and m.stride == (2, 2) and m.padding == (1, 1)

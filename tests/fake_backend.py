@@ -122,6 +122,38 @@ class FakeBackend:
         if db is not None:
             db += dout.sum()
 
+    # ------------------------------------------------------------------ encoder stem
+    @staticmethod
+    def encode_stem_supported(x, cout):
+        return x.dim() == 4 and tuple(x.shape[1:]) == (1, 64, 64) and cout == 16 and x.shape[0] > 0
+
+    @staticmethod
+    def _stem(x, w, b, slope):
+        y = F.leaky_relu(F.conv2d(x, w.reshape(16, 1, 3, 3), b, stride=2, padding=1), slope)       # [n,16,32,32]
+        n = y.shape[0]
+        return y.reshape(n, 16, 16, 2, 16, 2).permute(0, 2, 4, 3, 5, 1).reshape(n, 16, 16, 64)
+
+    def encode_stem_fwd(self, x, w, b, slope, cells):
+        self.launches += 1
+        cells.copy_(self._stem(x.detach(), w.detach(), None if b is None else b.detach(), slope))
+        return cells
+
+    def encode_stem_bwd(self, x, cells, dcells, slope, dw, db):
+        self.launches += 1
+        with torch.enable_grad():
+            ww = torch.zeros(16, 9).requires_grad_(True)
+            bb = torch.zeros(16).requires_grad_(True)
+            # leaky' from the saved output's sign; the linear part's gradient does not depend on the weights
+            mask = torch.where(cells > 0, torch.ones_like(cells), torch.full_like(cells, slope))
+            n = x.shape[0]
+            pre = F.conv2d(x.detach(), ww.reshape(16, 1, 3, 3), bb, stride=2, padding=1)
+            pre = pre.reshape(n, 16, 16, 2, 16, 2).permute(0, 2, 4, 3, 5, 1).reshape(n, 16, 16, 64)
+            gw, gb = torch.autograd.grad(pre, [ww, bb], dcells.detach() * mask)
+        if dw is not None:
+            dw += gw.reshape(dw.shape)
+        if db is not None:
+            db += gb
+
     # ------------------------------------------------------------------ bilinear 2x upsample
     def upsample2x_fwd(self, x, out):
         self.launches += 1

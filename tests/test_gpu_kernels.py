@@ -465,3 +465,31 @@ def test_conv_same_padded_matches_torch():
     exp = torch.autograd.grad((torch.tanh(ref) * w).sum(), [x, m.weight, m.bias])
     for g, r in zip(got, exp):
         assert rel_l2(g, r) < 1e-5 and rel_err(g, r) < 3e-5
+
+
+def test_encode_stem_matches_torch():
+    """odex_encode_stem_fwd / _bwd + the strided convolution on its cells (modules.encode_stem_then_conv: ConvEncode's
+    Conv2d(1,16,3,2,1) + LeakyReLU + Conv2d(16,64,3,2,1), models/ODEConvGRU.py:101-119) against torch's exact-fp32 layers:
+    output and the four parameter gradients.  The stem is exact fp32 FMA arithmetic (<= 2e-6 on the cells)."""
+    import torch.nn as nn
+    import torch.nn.functional as F
+    from ode_rl_b200.modules import _EncodeStemFn, encode_stem_supported, encode_stem_then_conv
+
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(9)
+    c0, act, c2 = nn.Conv2d(1, 16, 3, 2, 1).cuda(), nn.LeakyReLU(0.2), nn.Conv2d(16, 64, 3, 2, 1).cuda()
+    x = torch.rand(37, 1, 64, 64, device="cuda")
+    assert encode_stem_supported(x, c0, act, c2)
+    cells = _EncodeStemFn.apply(x, c0.weight, c0.bias, 0.2)
+    h = F.leaky_relu(c0(x), 0.2)
+    ref_cells = h.reshape(37, 16, 16, 2, 16, 2).permute(0, 2, 4, 3, 5, 1).reshape(37, 16, 16, 64)
+    assert rel_err(cells, ref_cells) < 2e-6
+    y = encode_stem_then_conv(x, c0, act, c2)
+    ref = c2(h)
+    assert y.shape == ref.shape and rel_err(y, ref) < 1e-5
+    w = torch.randn_like(ref)
+    ps = [c0.weight, c0.bias, c2.weight, c2.bias]
+    got = torch.autograd.grad((torch.tanh(y) * w).sum(), ps)
+    exp = torch.autograd.grad((torch.tanh(ref) * w).sum(), ps)
+    for g_, r_ in zip(got, exp):
+        assert g_.shape == r_.shape and rel_err(g_, r_) < 1e-5

@@ -342,3 +342,25 @@ def _dopri_error_cases(odex, device):
 
 def test_dopri5_error_behaviour(fake_backend):
     _dopri_error_cases(odex, torch.device("cpu"))
+
+
+def test_encode_stem_autograd_wiring(fake_backend):
+    """modules.encode_stem_then_conv (stem kernel -> space-to-depth cells -> strided convolution on the cells, one autograd
+    node each) against torch's layers: output and the four parameter gradients."""
+    import torch.nn as nn
+    import torch.nn.functional as F
+    from ode_rl_b200 import modules
+
+    fake_backend.require = lambda t: None
+    torch.manual_seed(0)
+    c0, c2 = nn.Conv2d(1, 16, 3, 2, 1), nn.Conv2d(16, 64, 3, 2, 1)
+    x = torch.rand(3, 1, 64, 64)
+    y = modules.encode_stem_then_conv(x, c0, nn.LeakyReLU(0.2), c2)
+    ref = c2(F.leaky_relu(c0(x), 0.2))
+    assert rel_err(y, ref) < 1e-6
+    w = torch.randn_like(ref)
+    ps = [c0.weight, c0.bias, c2.weight, c2.bias]
+    got = torch.autograd.grad((torch.tanh(y) * w).sum(), ps)
+    exp = torch.autograd.grad((torch.tanh(ref) * w).sum(), ps)
+    for g, r in zip(got, exp):
+        assert rel_err(g, r) < 1e-5
