@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define ODEX_VERSION 100
+#define ODEX_VERSION 200
 
 enum {
     ODEX_E_ARG = 1,         /* bad argument (null pointer, negative size ...) */
@@ -216,47 +216,63 @@ typedef struct odex_dopri_state {
     double ratio;       /* error ratio of the last attempt */
     double h0, d0, d1, d2; /* initial-step heuristic scratch */
     int accept;         /* last attempt accepted */
-    int done;           /* every output time has been produced -- this is what `skip` points at */
-    int done_next;      /* latched into done after the dense-output kernel of the final step */
+    int done;           /* the integration is over (every output time decided, or an error bit set) -- this is what
+                           `skip` points at */
+    int adv_seq;        /* number (`seq`, given by the host) of the last ACCEPTED attempt: odex_dopri_advance(seq) runs
+                           iff it finds its own number here; -1 before the first accepted step */
     int jnext;          /* next output index to produce */
     int jlo, jhi;       /* outputs [jlo, jhi) lie inside the step accepted by the last attempt */
     int n_out;          /* number of output times */
     int n_accept, n_reject, n_feval, n_attempt;
-    int status;         /* bit0: underflow in dt, bit1: non-finite state, bit2: max attempts exceeded */
+    int status;         /* bit0: underflow in dt, bit1: non-finite state, bit2: max attempts exceeded,
+                           bit3: more accepted steps than backward checkpoints (save_cap) */
     int max_attempts;
-    int pad_;
+    int save_cap;       /* capacity of the (y, f) checkpoint arrays handed to odex_dopri_advance; 0 = none kept */
+    double dt_acc;      /* size of the last accepted step (what odex_dopri_advance interpolates with) */
 } odex_dopri_state;
 size_t odex_dopri_state_bytes(void);
 
-/* state <- zeros, t0 = t1 = t[0], tolerances, n_out; done if n_out <= 1.  (torchdiffeq solvers.py setup) */
+/* state <- zeros, t0 = t1 = t[0], tolerances, n_out, save_cap; done if n_out <= 1.  (torchdiffeq solvers.py setup) */
 int odex_dopri_init(odex_dopri_state* st, const double* t_dev, int n_out, double rtol, double atol,
-                    int max_attempts, odex_stream_t s);
+                    int max_attempts, int save_cap, odex_stream_t s);
 /* phase 0: red <- {sum (y0/scale)^2, sum (f0/scale)^2, 0, n}; scale = atol + rtol*|y0|.
  * phase 1: red <- {sum ((f1 - f0)/scale)^2, 0, 0, n}.
- * Replaces torchdiffeq misc._select_initial_step's three RMS norms. */
+ * Replaces torchdiffeq misc._select_initial_step's three RMS norms.  fuse_ctrl != 0: the last block to finish also does
+ * odex_dopri_initctrl(phase) (single-GPU mode: one launch instead of two). */
 int odex_dopri_initnorm(odex_dopri_state* st, int phase, const float* y0, const float* f0, const float* f1,
-                        long long n, odex_stream_t s);
+                        long long n, int fuse_ctrl, odex_stream_t s);
 /* phase 0: h0 from d0, d1 (st->h0; the host then forms y0 + h0*f0 with odex_lincomb(dt_dev = &st->h0)).
- * phase 1: dt from d1, d2, h0.  fp32 arithmetic like the reference. */
+ * phase 1: dt from d1, d2, h0, latched as dt_try of the first attempt together with rk_common._adaptive_step's
+ * `t + dt > t` assert (status bit0).  fp32 arithmetic like the reference. */
 int odex_dopri_initctrl(odex_dopri_state* st, int phase, odex_stream_t s);
-/* latch dt_try = dt for the attempt and check `t + dt > t` / max attempts (rk_common._adaptive_step asserts). */
-int odex_dopri_begin(odex_dopri_state* st, odex_stream_t s);
-/* red <- {sum_i (err_i / (atol + rtol*max(|y0_i|,|y1_i|)))^2, #non-finite y0 vectors, 0, n},
- * err = dt_try * sum_j c_error[j] k_j.  k[1] is never read (c_error[1] == 0).
- * Replaces rk_common._runge_kutta_step's error estimate + misc._compute_error_ratio (8 launches + a D2H sync). */
+/* K4, single-GPU form -- ONE kernel for everything between the last f-eval of an attempt and the step decision:
+ *   err = dt_try * sum_j c_error[j] k_j (k[1] never read, c_error[1] == 0);  ratio = RMS(err / (atol + rtol*max(|y0|,|y1|)))
+ *   over the whole batch tensor (vectorised loads, warp-shuffle -> block -> last-block reduction in a fixed order);
+ *   non-finite check of y0;  and, in the last block: accept = ratio <= 1, t / dt update (misc._optimal_step_size), counters,
+ *   the range [jlo, jhi) of output times inside the accepted step, the attempt log (4 doubles per attempt: t0, dt, ratio,
+ *   accept) into log_dev when non-NULL, `done`, and the asserts of the NEXT attempt (dt underflow, max attempts).
+ * `seq` = the caller's running number of this attempt (0, 1, 2, ... per integration), see odex_dopri_advance.
+ * Replaces rk_common._runge_kutta_step's error estimate + misc._compute_error_ratio + _optimal_step_size + the accept
+ * branch of _adaptive_step (~15 launches and >= 4 D2H syncs in the reference). */
+int odex_dopri_errctrl(odex_dopri_state* st, const double* t_dev, const float* y0, const float* y1,
+                       const float* const* k7_host, long long n, double* log_dev, int log_cap, int seq, odex_stream_t s);
+/* K4, multi-GPU form: odex_dopri_errnorm leaves the per-rank partial sums in st->red (the caller all-reduces those 4
+ * doubles over the ranks), odex_dopri_ctrl then takes the decision exactly as odex_dopri_errctrl's last block does. */
 int odex_dopri_errnorm(odex_dopri_state* st, const float* y0, const float* y1, const float* const* k7_host,
                        long long n, odex_stream_t s);
-/* accept = ratio <= 1 with ratio = sqrt(red[0]/red[3]); t/dt update (misc._optimal_step_size), counters, the
- * range [jlo, jhi) of output times inside the accepted step, done_next, attempt log (4 doubles per attempt:
- * t0, dt, ratio, accept) into log_dev when non-NULL. */
-int odex_dopri_ctrl(odex_dopri_state* st, const double* t_dev, double* log_dev, int log_cap, odex_stream_t s);
-/* On accept: quartic dense output (interp._interp_fit/_interp_evaluate) for every output j in [jlo, jhi)
- * into sol + j*n, then advance the state y0 <- y1, k[0] <- k[6] (FSAL) and latch `done`.  On reject: no-op.
- * ysave/fsave (nullable, together): [save_cap][n] checkpoints of (y, f) at the start of every accepted step
- * (for the backward replay). */
+int odex_dopri_ctrl(odex_dopri_state* st, const double* t_dev, double* log_dev, int log_cap, int seq, odex_stream_t s);
+/* K5: runs iff attempt `seq` was accepted (st->adv_seq == seq): quartic dense output (interp._interp_fit/_interp_evaluate)
+ * for every output j in [jlo, jhi) into sol + j*n, then the FSAL advance y0 <- y1, k[0] <- k[6].  Otherwise a no-op.
+ * ysave/fsave (nullable, together): [save_cap][n] checkpoints of (y, f) at the start of every accepted step (for the
+ * backward replay); the controller stops with status bit3 before a step that would not fit. */
 int odex_dopri_advance(odex_dopri_state* st, const double* t_dev, float* y0, const float* y1,
-                       float* const* k7_host, float* sol, long long n, float* ysave, float* fsave, int save_cap,
+                       float* const* k7_host, float* sol, long long n, float* ysave, float* fsave, int save_cap, int seq,
                        odex_stream_t s);
+
+/* *flag |= bit if x[0..n) holds a NaN (n % 4 == 0).  The encoder recurrence's per-frame `assert not torch.isnan(...)`
+ * (modules/ODEConvGRUCell.py:56,59) as a sticky device word: a NaN produced in any iteration reaches the last hidden
+ * state, so one pass over it per forward is equivalent, and the host reads the word once (or never, under graph capture). */
+int odex_nan_flag(const float* x, long long n, int* flag, int bit, odex_stream_t s);
 
 /* fp32 NCHW <-> NHWC repack of [B, C, HW] planes (tiled transpose). */
 int odex_nchw_to_nhwc(const float* in, float* out, int B, int C, int HW, odex_stream_t s);

@@ -13,7 +13,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libodex.so")
 
-ODEX_VERSION = 100
+ODEX_VERSION = 200
 ACT_NONE, ACT_RELU, ACT_TANH = 0, 1, 2
 CONV_AUTO, CONV_SIMT, CONV_TC = 0, 1, 2
 STATE_HEAD_BYTES = 256
@@ -71,10 +71,11 @@ class DopriState(C.Structure):
         ("red", C.c_double * 4),
         ("ratio", C.c_double),
         ("h0", C.c_double), ("d0", C.c_double), ("d1", C.c_double), ("d2", C.c_double),
-        ("accept", C.c_int), ("done", C.c_int), ("done_next", C.c_int), ("jnext", C.c_int),
+        ("accept", C.c_int), ("done", C.c_int), ("adv_seq", C.c_int), ("jnext", C.c_int),
         ("jlo", C.c_int), ("jhi", C.c_int), ("n_out", C.c_int),
         ("n_accept", C.c_int), ("n_reject", C.c_int), ("n_feval", C.c_int), ("n_attempt", C.c_int),
-        ("status", C.c_int), ("max_attempts", C.c_int), ("pad_", C.c_int),
+        ("status", C.c_int), ("max_attempts", C.c_int), ("save_cap", C.c_int),
+        ("dt_acc", C.c_double),
     ]
 
 
@@ -113,13 +114,14 @@ SIGNATURES = {
     "odex_lincomb": (_i, [_vp, _i, C.POINTER(_vp), c_double_p, _u32, _vp, _ll, _vp, _vp]),
     "odex_act_bwd": (_i, [_vp, _vp, _vp, _i, _ll, _vp]),
     "odex_dopri_state_bytes": (_sz, []),
-    "odex_dopri_init": (_i, [_vp, _vp, _i, _d, _d, _i, _vp]),
-    "odex_dopri_initnorm": (_i, [_vp, _i, _vp, _vp, _vp, _ll, _vp]),
+    "odex_dopri_init": (_i, [_vp, _vp, _i, _d, _d, _i, _i, _vp]),
+    "odex_dopri_initnorm": (_i, [_vp, _i, _vp, _vp, _vp, _ll, _i, _vp]),
     "odex_dopri_initctrl": (_i, [_vp, _i, _vp]),
-    "odex_dopri_begin": (_i, [_vp, _vp]),
+    "odex_dopri_errctrl": (_i, [_vp, _vp, _vp, _vp, C.POINTER(_vp), _ll, _vp, _i, _i, _vp]),
     "odex_dopri_errnorm": (_i, [_vp, _vp, _vp, C.POINTER(_vp), _ll, _vp]),
-    "odex_dopri_ctrl": (_i, [_vp, _vp, _vp, _i, _vp]),
-    "odex_dopri_advance": (_i, [_vp, _vp, _vp, _vp, C.POINTER(_vp), _vp, _ll, _vp, _vp, _i, _vp]),
+    "odex_dopri_ctrl": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
+    "odex_dopri_advance": (_i, [_vp, _vp, _vp, _vp, C.POINTER(_vp), _vp, _ll, _vp, _vp, _i, _i, _vp]),
+    "odex_nan_flag": (_i, [_vp, _ll, _vp, _i, _vp]),
     "odex_nchw_to_nhwc": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "odex_nhwc_to_nchw": (_i, [_vp, _vp, _i, _i, _i, _vp]),
 }

@@ -79,7 +79,9 @@ struct DopriDev {          // device view of odex_dopri_state (same layout) + re
     odex_dopri_state s;
 };
 
-__device__ __forceinline__ void finish_reduce(odex_dopri_state* st, double p0, double p1, double p2, double count,
+// Returns true in thread 0 of the LAST block, after st->red[] holds the full sums: the fused kernels run the 1-thread
+// controller right there instead of in a launch of their own.
+__device__ __forceinline__ bool finish_reduce(odex_dopri_state* st, double p0, double p1, double p2, double count,
                                               double* sh) {
     double* partial = reinterpret_cast<double*>(reinterpret_cast<char*>(st) + ODEX_STATE_HEAD_BYTES);
     unsigned int* ticket = reinterpret_cast<unsigned int*>(partial + 3 * kRedBlocks);
@@ -107,13 +109,94 @@ __device__ __forceinline__ void finish_reduce(odex_dopri_state* st, double p0, d
         if (threadIdx.x == 0) {
             st->red[0] = a0; st->red[1] = a1; st->red[2] = a2; st->red[3] = count;
             *ticket = 0u;
+            return true;
         }
     }
+    return false;
+}
+
+// rk_common._adaptive_step's asserts for the NEXT attempt (`t + dt > t`, max_num_steps), evaluated as soon as its dt is known
+__device__ __forceinline__ void begin_next_attempt(odex_dopri_state* st) {
+    st->dt_try = st->dt;
+    if (!(st->t1 + st->dt > st->t1)) { st->status |= 1; st->done = 1; }
+    if (st->n_attempt >= st->max_attempts) { st->status |= 4; st->done = 1; }
+}
+
+// torchdiffeq misc._select_initial_step, computed in fp32 like the reference (y0.dtype), order = 4
+__device__ __forceinline__ void initctrl_body(odex_dopri_state* st, int phase) {
+    if (phase == 0) {
+        const float d0 = static_cast<float>(sqrt(st->red[0] / st->red[3]));
+        const float d1 = static_cast<float>(sqrt(st->red[1] / st->red[3]));
+        st->d0 = d0; st->d1 = d1;
+        const float h0 = (d0 < 1e-5f || d1 < 1e-5f) ? 1e-6f : 0.01f * d0 / d1;
+        st->h0 = h0;
+        st->n_feval += 2;    // f0 and the probe evaluation f(y0 + h0*f0)
+    } else {
+        const float h0 = static_cast<float>(st->h0), d1 = static_cast<float>(st->d1);
+        const float d2 = static_cast<float>(sqrt(st->red[0] / st->red[3])) / h0;
+        st->d2 = d2;
+        float h1;
+        if (d1 <= 1e-15f && d2 <= 1e-15f) h1 = fmaxf(1e-6f, h0 * 1e-3f);
+        else h1 = powf(0.01f / fmaxf(d1, d2), 1.0f / 5.0f);
+        st->dt = static_cast<double>(fminf(100.f * h0, h1));
+        begin_next_attempt(st);
+    }
+}
+
+// accept/reject + misc._optimal_step_size (safety 0.9, ifactor 10, dfactor 0.2, order 5), all fp64; one thread.
+// `seq` is the host's running number of this attempt: an accepted attempt publishes it in st->adv_seq, which is what the
+// dense-output / advance kernel of the SAME attempt checks (st->done may already be set by then: the last step).
+__device__ __forceinline__ void ctrl_body(odex_dopri_state* st, const double* t, double* log, int log_cap, int seq) {
+    const double dt = st->dt_try;
+    if (st->red[1] > 0.0) { st->status |= 2; st->done = 1; return; }
+    // the reference's ratio is an fp32 tensor (mean of fp32 squares, sqrt) cast to fp64 for the controller
+    const double ratio = static_cast<double>(static_cast<float>(sqrt(st->red[0] / st->red[3])));
+    st->ratio = ratio;
+    const int accept = ratio <= 1.0 ? 1 : 0;
+    st->accept = accept;
+    st->n_feval += 6;
+    const int a = st->n_attempt;
+    if (log != nullptr && a < log_cap) {
+        log[4 * a + 0] = st->t1; log[4 * a + 1] = dt; log[4 * a + 2] = ratio; log[4 * a + 3] = accept;
+    }
+    st->n_attempt = a + 1;
+    bool finished = false;
+    if (accept) {
+        if (st->save_cap > 0 && st->n_accept >= st->save_cap) {
+            // the backward checkpoints are full: stop HERE (sticky bit 3) instead of silently dropping this step's checkpoint
+            st->status |= 8; st->done = 1;
+            return;
+        }
+        st->t0 = st->t1;
+        st->t1 = st->t1 + dt;
+        st->n_accept += 1;
+        st->dt_acc = dt;
+        st->adv_seq = seq;
+        int j = st->jnext;
+        st->jlo = j;
+        while (j < st->n_out && !(t[j] > st->t1)) ++j;
+        st->jhi = j;
+        st->jnext = j;
+        finished = j >= st->n_out;
+    } else {
+        st->n_reject += 1;
+        st->jlo = st->jhi = st->jnext;
+    }
+    double factor;
+    if (ratio == 0.0) {
+        factor = 10.0;
+    } else {
+        const double dfactor = ratio < 1.0 ? 1.0 : 0.2;
+        factor = fmin(10.0, fmax(0.9 / pow(ratio, 0.2), dfactor));
+    }
+    st->dt = dt * factor;
+    if (finished) { st->done = 1; return; }
+    begin_next_attempt(st);
 }
 
 __global__ void __launch_bounds__(256) dopri_initnorm_kernel(odex_dopri_state* st, int phase, const float* __restrict__ y0,
                                                              const float* __restrict__ f0, const float* __restrict__ f1,
-                                                             long n4) {
+                                                             long n4, int fuse_ctrl) {
     __shared__ double sh[33];
     if (st->done) return;
     const float rtol = static_cast<float>(st->rtol), atol = static_cast<float>(st->atol);
@@ -138,11 +221,11 @@ __global__ void __launch_bounds__(256) dopri_initnorm_kernel(odex_dopri_state* s
         }
         a += sa; b += sb;
     }
-    finish_reduce(st, a, b, 0.0, static_cast<double>(n4) * 4.0, sh);
+    if (finish_reduce(st, a, b, 0.0, static_cast<double>(n4) * 4.0, sh) && fuse_ctrl) initctrl_body(st, phase);
 }
 
 __global__ void dopri_init_kernel(odex_dopri_state* st, const double* t, int n_out, double rtol, double atol,
-                                  int max_attempts) {
+                                  int max_attempts, int save_cap) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     char* raw = reinterpret_cast<char*>(st);
     for (int i = 0; i < ODEX_STATE_HEAD_BYTES; ++i) raw[i] = 0;
@@ -152,42 +235,22 @@ __global__ void dopri_init_kernel(odex_dopri_state* st, const double* t, int n_o
     st->rtol = rtol; st->atol = atol;
     st->n_out = n_out; st->jnext = 1;
     st->max_attempts = max_attempts;
+    st->save_cap = save_cap;
+    st->adv_seq = -1;
     st->done = n_out <= 1 ? 1 : 0;
 }
 
-// torchdiffeq misc._select_initial_step, computed in fp32 like the reference (y0.dtype), order = 4
 __global__ void dopri_initctrl_kernel(odex_dopri_state* st, int phase) {
     if (threadIdx.x != 0 || blockIdx.x != 0 || st->done) return;
-    if (phase == 0) {
-        const float d0 = static_cast<float>(sqrt(st->red[0] / st->red[3]));
-        const float d1 = static_cast<float>(sqrt(st->red[1] / st->red[3]));
-        st->d0 = d0; st->d1 = d1;
-        const float h0 = (d0 < 1e-5f || d1 < 1e-5f) ? 1e-6f : 0.01f * d0 / d1;
-        st->h0 = h0;
-        st->n_feval += 2;    // f0 and the probe evaluation f(y0 + h0*f0)
-    } else {
-        const float h0 = static_cast<float>(st->h0), d1 = static_cast<float>(st->d1);
-        const float d2 = static_cast<float>(sqrt(st->red[0] / st->red[3])) / h0;
-        st->d2 = d2;
-        float h1;
-        if (d1 <= 1e-15f && d2 <= 1e-15f) h1 = fmaxf(1e-6f, h0 * 1e-3f);
-        else h1 = powf(0.01f / fmaxf(d1, d2), 1.0f / 5.0f);
-        st->dt = static_cast<double>(fminf(100.f * h0, h1));
-    }
-}
-
-__global__ void dopri_begin_kernel(odex_dopri_state* st) {
-    if (threadIdx.x != 0 || blockIdx.x != 0 || st->done) return;
-    st->dt_try = st->dt;
-    if (!(st->t1 + st->dt > st->t1)) { st->status |= 1; st->done = 1; }
-    if (st->n_attempt >= st->max_attempts) { st->status |= 4; st->done = 1; }
+    initctrl_body(st, phase);
 }
 
 struct K7 { const float* k[7]; };
 struct K7w { float* k[7]; };
 
 __global__ void __launch_bounds__(256) dopri_errnorm_kernel(odex_dopri_state* st, const float* __restrict__ y0,
-                                                            const float* __restrict__ y1, const K7 k, long n4) {
+                                                            const float* __restrict__ y1, const K7 k, long n4,
+                                                            const double* t, double* log, int log_cap, int seq, int fuse_ctrl) {
     __shared__ double sh[33];
     if (st->done) return;
     const float rtol = static_cast<float>(st->rtol), atol = static_cast<float>(st->atol);
@@ -215,59 +278,24 @@ __global__ void __launch_bounds__(256) dopri_errnorm_kernel(odex_dopri_state* st
         acc += static_cast<double>((r0 * r0 + r1 * r1) + (r2 * r2 + r3 * r3));
         if (!(isfinite(a.x) && isfinite(a.y) && isfinite(a.z) && isfinite(a.w))) bad += 1.0;
     }
-    finish_reduce(st, acc, bad, 0.0, static_cast<double>(n4) * 4.0, sh);
+    if (finish_reduce(st, acc, bad, 0.0, static_cast<double>(n4) * 4.0, sh) && fuse_ctrl) ctrl_body(st, t, log, log_cap, seq);
 }
 
-// accept/reject + misc._optimal_step_size (safety 0.9, ifactor 10, dfactor 0.2, order 5), all fp64
-__global__ void dopri_ctrl_kernel(odex_dopri_state* st, const double* t, double* log, int log_cap) {
+__global__ void dopri_ctrl_kernel(odex_dopri_state* st, const double* t, double* log, int log_cap, int seq) {
     if (threadIdx.x != 0 || blockIdx.x != 0 || st->done) return;
-    const double dt = st->dt_try;
-    if (st->red[1] > 0.0) { st->status |= 2; st->done = 1; return; }
-    // the reference's ratio is an fp32 tensor (mean of fp32 squares, sqrt) cast to fp64 for the controller
-    const double ratio = static_cast<double>(static_cast<float>(sqrt(st->red[0] / st->red[3])));
-    st->ratio = ratio;
-    const int accept = ratio <= 1.0 ? 1 : 0;
-    st->accept = accept;
-    st->n_feval += 6;
-    const int a = st->n_attempt;
-    if (log != nullptr && a < log_cap) {
-        log[4 * a + 0] = st->t1; log[4 * a + 1] = dt; log[4 * a + 2] = ratio; log[4 * a + 3] = accept;
-    }
-    st->n_attempt = a + 1;
-    if (accept) {
-        st->t0 = st->t1;
-        st->t1 = st->t1 + dt;
-        st->n_accept += 1;
-        int j = st->jnext;
-        st->jlo = j;
-        while (j < st->n_out && !(t[j] > st->t1)) ++j;
-        st->jhi = j;
-        st->jnext = j;
-        if (j >= st->n_out) st->done_next = 1;
-    } else {
-        st->n_reject += 1;
-        st->jlo = st->jhi = st->jnext;
-    }
-    double factor;
-    if (ratio == 0.0) {
-        factor = 10.0;
-    } else {
-        const double dfactor = ratio < 1.0 ? 1.0 : 0.2;
-        factor = fmin(10.0, fmax(0.9 / pow(ratio, 0.2), dfactor));
-    }
-    st->dt = dt * factor;
+    ctrl_body(st, t, log, log_cap, seq);
 }
 
-// dense output + state advance.  Runs after dopri_ctrl_kernel; sets `done` itself (last thread to leave is
-// irrelevant: every block reads st->done_next, block 0 latches it at the end of the kernel via a ticket).
+// dense output + state advance of the attempt numbered `seq`, iff the controller accepted it (st->adv_seq == seq; a
+// speculative launch past the end of the integration, or after a rejection, finds another number there and returns).
 __global__ void __launch_bounds__(256) dopri_advance_kernel(odex_dopri_state* st, const double* __restrict__ t,
                                                             float* __restrict__ y0, const float* __restrict__ y1,
                                                             const K7w k, float* __restrict__ sol, long n4,
                                                             float* __restrict__ ysave, float* __restrict__ fsave,
-                                                            int save_cap) {
-    if (st->done || !st->accept) return;
+                                                            int save_cap, int seq) {
+    if (st->adv_seq != seq) return;
     const int jlo = st->jlo, jhi = st->jhi;
-    const float dt = static_cast<float>(st->dt_try);
+    const float dt = static_cast<float>(st->dt_acc);
     const double T0 = st->t0, T1 = st->t1;
     const int step = st->n_accept - 1;
     float cm[7];
@@ -314,12 +342,6 @@ __global__ void __launch_bounds__(256) dopri_advance_kernel(odex_dopri_state* st
         st4(y0 + 4 * i, b);
         st4(k.k[0] + 4 * i, f1);
     }
-}
-
-// latch done after the advance kernel (separate 1-thread kernel so every advance block sees done == 0)
-__global__ void dopri_latch_kernel(odex_dopri_state* st) {
-    if (threadIdx.x != 0 || blockIdx.x != 0 || st->done) return;
-    if (st->done_next) st->done = 1;
 }
 
 inline int ew_blocks(long n4) { return static_cast<int>(std::min<long>((n4 + 255) / 256, static_cast<long>(kRedBlocks))); }
@@ -371,16 +393,16 @@ extern "C" size_t odex_dopri_state_bytes(void) {
 }
 
 extern "C" int odex_dopri_init(odex_dopri_state* st, const double* t, int n_out, double rtol, double atol,
-                               int max_attempts, odex_stream_t s) {
-    if (!st || !t || n_out < 1) return fail(ODEX_E_ARG, "dopri_init: bad argument");
-    dopri_init_kernel<<<1, 32, 0, static_cast<cudaStream_t>(s)>>>(st, t, n_out, rtol, atol, max_attempts);
+                               int max_attempts, int save_cap, odex_stream_t s) {
+    if (!st || !t || n_out < 1 || save_cap < 0) return fail(ODEX_E_ARG, "dopri_init: bad argument");
+    dopri_init_kernel<<<1, 32, 0, static_cast<cudaStream_t>(s)>>>(st, t, n_out, rtol, atol, max_attempts, save_cap);
     return launched("dopri_init_kernel");
 }
 
 extern "C" int odex_dopri_initnorm(odex_dopri_state* st, int phase, const float* y0, const float* f0, const float* f1,
-                                   long long n, odex_stream_t s) {
+                                   long long n, int fuse_ctrl, odex_stream_t s) {
     if (!st || !y0 || !f0 || (phase == 1 && !f1) || n <= 0 || n % 4) return fail(ODEX_E_ARG, "dopri_initnorm: bad argument");
-    dopri_initnorm_kernel<<<ew_blocks(n / 4), 256, 0, static_cast<cudaStream_t>(s)>>>(st, phase, y0, f0, f1, n / 4);
+    dopri_initnorm_kernel<<<ew_blocks(n / 4), 256, 0, static_cast<cudaStream_t>(s)>>>(st, phase, y0, f0, f1, n / 4, fuse_ctrl);
     return launched("dopri_initnorm_kernel");
 }
 
@@ -390,37 +412,60 @@ extern "C" int odex_dopri_initctrl(odex_dopri_state* st, int phase, odex_stream_
     return launched("dopri_initctrl_kernel");
 }
 
-extern "C" int odex_dopri_begin(odex_dopri_state* st, odex_stream_t s) {
-    if (!st) return fail(ODEX_E_ARG, "dopri_begin: null state");
-    dopri_begin_kernel<<<1, 32, 0, static_cast<cudaStream_t>(s)>>>(st);
-    return launched("dopri_begin_kernel");
-}
-
 extern "C" int odex_dopri_errnorm(odex_dopri_state* st, const float* y0, const float* y1, const float* const* k7,
                                   long long n, odex_stream_t s) {
     if (!st || !y0 || !y1 || !k7 || n <= 0 || n % 4) return fail(ODEX_E_ARG, "dopri_errnorm: bad argument");
     K7 k;
     for (int j = 0; j < 7; ++j) k.k[j] = k7[j];
-    dopri_errnorm_kernel<<<ew_blocks(n / 4), 256, 0, static_cast<cudaStream_t>(s)>>>(st, y0, y1, k, n / 4);
+    dopri_errnorm_kernel<<<ew_blocks(n / 4), 256, 0, static_cast<cudaStream_t>(s)>>>(st, y0, y1, k, n / 4, nullptr, nullptr, 0, 0, 0);
     return launched("dopri_errnorm_kernel");
 }
 
-extern "C" int odex_dopri_ctrl(odex_dopri_state* st, const double* t, double* log, int log_cap, odex_stream_t s) {
-    if (!st || !t) return fail(ODEX_E_ARG, "dopri_ctrl: bad argument");
-    dopri_ctrl_kernel<<<1, 32, 0, static_cast<cudaStream_t>(s)>>>(st, t, log, log_cap);
+extern "C" int odex_dopri_errctrl(odex_dopri_state* st, const double* t, const float* y0, const float* y1,
+                                  const float* const* k7, long long n, double* log, int log_cap, int seq, odex_stream_t s) {
+    if (!st || !t || !y0 || !y1 || !k7 || n <= 0 || n % 4 || seq < 0) return fail(ODEX_E_ARG, "dopri_errctrl: bad argument");
+    K7 k;
+    for (int j = 0; j < 7; ++j) k.k[j] = k7[j];
+    dopri_errnorm_kernel<<<ew_blocks(n / 4), 256, 0, static_cast<cudaStream_t>(s)>>>(st, y0, y1, k, n / 4, t, log, log_cap, seq, 1);
+    return launched("dopri_errnorm_kernel");
+}
+
+extern "C" int odex_dopri_ctrl(odex_dopri_state* st, const double* t, double* log, int log_cap, int seq, odex_stream_t s) {
+    if (!st || !t || seq < 0) return fail(ODEX_E_ARG, "dopri_ctrl: bad argument");
+    dopri_ctrl_kernel<<<1, 32, 0, static_cast<cudaStream_t>(s)>>>(st, t, log, log_cap, seq);
     return launched("dopri_ctrl_kernel");
 }
 
 extern "C" int odex_dopri_advance(odex_dopri_state* st, const double* t, float* y0, const float* y1, float* const* k7,
-                                  float* sol, long long n, float* ysave, float* fsave, int save_cap, odex_stream_t s_) {
+                                  float* sol, long long n, float* ysave, float* fsave, int save_cap, int seq,
+                                  odex_stream_t s_) {
     cudaStream_t s = static_cast<cudaStream_t>(s_);
-    if (!st || !t || !y0 || !y1 || !k7 || !sol || n <= 0 || n % 4) return fail(ODEX_E_ARG, "dopri_advance: bad argument");
+    if (!st || !t || !y0 || !y1 || !k7 || !sol || n <= 0 || n % 4 || seq < 0) return fail(ODEX_E_ARG, "dopri_advance: bad argument");
     if ((ysave == nullptr) != (fsave == nullptr)) return fail(ODEX_E_ARG, "dopri_advance: ysave and fsave go together");
     K7w k;
     for (int j = 0; j < 7; ++j) k.k[j] = k7[j];
-    dopri_advance_kernel<<<ew_blocks(n / 4), 256, 0, s>>>(st, t, y0, y1, k, sol, n / 4, ysave, fsave, save_cap);
-    int rc = launched("dopri_advance_kernel");
-    if (rc) return rc;
-    dopri_latch_kernel<<<1, 32, 0, s>>>(st);
-    return launched("dopri_latch_kernel");
+    dopri_advance_kernel<<<ew_blocks(n / 4), 256, 0, s>>>(st, t, y0, y1, k, sol, n / 4, ysave, fsave, save_cap, seq);
+    return launched("dopri_advance_kernel");
+}
+
+// *flag |= bit when x holds a NaN: the encoder recurrence's `assert not torch.isnan(...)` (modules/ODEConvGRUCell.py:56,59)
+// as a sticky device word the host reads once per forward.  A NaN in any iteration reaches the last hidden state (every
+// later update reads it through the convolutions), so one pass over the final state replaces the reference's 2 syncs per frame.
+namespace odex {
+__global__ void __launch_bounds__(256) nan_flag_kernel(const float* __restrict__ x, long n4, int* flag, int bit) {
+    bool bad = false;
+    for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n4;
+         i += static_cast<long>(gridDim.x) * blockDim.x) {
+        const float4 v = ld4(x + 4 * i);
+        bad = bad || isnan(v.x) || isnan(v.y) || isnan(v.z) || isnan(v.w);
+    }
+    if (__syncthreads_or(bad ? 1 : 0) && threadIdx.x == 0) atomicOr(flag, bit);
+}
+}  // namespace odex
+
+extern "C" int odex_nan_flag(const float* x, long long n, int* flag, int bit, odex_stream_t s) {
+    if (!x || !flag || n <= 0 || n % 4) return fail(ODEX_E_ARG, "nan_flag: bad argument");
+    if (!aligned16(x)) return fail(ODEX_E_ALIGN, "nan_flag: x not 16-byte aligned");
+    nan_flag_kernel<<<ew_blocks(n / 4), 256, 0, static_cast<cudaStream_t>(s)>>>(x, n / 4, flag, bit);
+    return launched("nan_flag_kernel");
 }

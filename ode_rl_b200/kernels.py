@@ -336,34 +336,42 @@ class Backend:
     def dopri_state_bytes(self) -> int:
         return int(self.lib.odex_dopri_state_bytes())
 
-    def dopri_init(self, st, t_dev, n_out, rtol, atol, max_attempts) -> None:
-        _lib.check(self.lib.odex_dopri_init(st.data_ptr(), t_dev.data_ptr(), n_out, rtol, atol, max_attempts, _stream()),
-                   "odex_dopri_init")
+    def dopri_init(self, st, t_dev, n_out, rtol, atol, max_attempts, save_cap=0) -> None:
+        _lib.check(self.lib.odex_dopri_init(st.data_ptr(), t_dev.data_ptr(), n_out, rtol, atol, max_attempts, save_cap,
+                                            _stream()), "odex_dopri_init")
 
-    def dopri_initnorm(self, st, phase, y0, f0, f1) -> None:
+    def dopri_initnorm(self, st, phase, y0, f0, f1, fuse_ctrl=False) -> None:
         _lib.check(self.lib.odex_dopri_initnorm(st.data_ptr(), phase, _flat(y0), _flat(f0), _ptr(f1), y0.numel(),
-                                                _stream()), "odex_dopri_initnorm")
+                                                1 if fuse_ctrl else 0, _stream()), "odex_dopri_initnorm")
 
     def dopri_initctrl(self, st, phase) -> None:
         _lib.check(self.lib.odex_dopri_initctrl(st.data_ptr(), phase, _stream()), "odex_dopri_initctrl")
 
-    def dopri_begin(self, st) -> None:
-        _lib.check(self.lib.odex_dopri_begin(st.data_ptr(), _stream()), "odex_dopri_begin")
+    def dopri_errctrl(self, st, t_dev, y0, y1, k7: List[torch.Tensor], log, log_cap, seq) -> None:
+        """K4 fused: error estimate + RMS norm + accept/reject + step-size controller in one launch."""
+        arr = (C.c_void_p * 7)(*[_flat(t) for t in k7])
+        _lib.check(self.lib.odex_dopri_errctrl(st.data_ptr(), t_dev.data_ptr(), _flat(y0), _flat(y1), arr, y0.numel(),
+                                               _ptr(log), log_cap, seq, _stream()), "odex_dopri_errctrl")
 
     def dopri_errnorm(self, st, y0, y1, k7: List[torch.Tensor]) -> None:
         arr = (C.c_void_p * 7)(*[_flat(t) for t in k7])
         _lib.check(self.lib.odex_dopri_errnorm(st.data_ptr(), _flat(y0), _flat(y1), arr, y0.numel(), _stream()),
                    "odex_dopri_errnorm")
 
-    def dopri_ctrl(self, st, t_dev, log, log_cap) -> None:
-        _lib.check(self.lib.odex_dopri_ctrl(st.data_ptr(), t_dev.data_ptr(), _ptr(log), log_cap, _stream()),
+    def dopri_ctrl(self, st, t_dev, log, log_cap, seq) -> None:
+        _lib.check(self.lib.odex_dopri_ctrl(st.data_ptr(), t_dev.data_ptr(), _ptr(log), log_cap, seq, _stream()),
                    "odex_dopri_ctrl")
 
-    def dopri_advance(self, st, t_dev, y0, y1, k7: List[torch.Tensor], sol, ysave, fsave, save_cap) -> None:
+    def dopri_advance(self, st, t_dev, y0, y1, k7: List[torch.Tensor], sol, ysave, fsave, save_cap, seq) -> None:
         arr = (C.c_void_p * 7)(*[_flat(t) for t in k7])
         _lib.check(self.lib.odex_dopri_advance(st.data_ptr(), t_dev.data_ptr(), _flat(y0), _flat(y1), arr, _flat(sol),
-                                               y0.numel(), _ptr(ysave), _ptr(fsave), save_cap, _stream()),
+                                               y0.numel(), _ptr(ysave), _ptr(fsave), save_cap, seq, _stream()),
                    "odex_dopri_advance")
+
+    def nan_flag(self, x: torch.Tensor, flag: torch.Tensor, bit: int) -> None:
+        """odex_nan_flag: *flag |= bit when x holds a NaN (sticky device word, read by the host once per forward)."""
+        assert flag.dtype == torch.int32 and x.is_contiguous()
+        _lib.check(self.lib.odex_nan_flag(x.data_ptr(), x.numel(), flag.data_ptr(), bit, _stream()), "odex_nan_flag")
 
     # ------------------------------------------------------------------ layout
     def nchw_to_nhwc(self, x: torch.Tensor, out: torch.Tensor) -> torch.Tensor:

@@ -23,7 +23,7 @@ import torch.nn as nn
 
 from . import kernels as K
 from .kernels import ACT_NONE, CONV_TC
-from .ops import ConvNetOp, GradSink, GruOp, from_nhwc, to_nhwc
+from .ops import ConvNetOp, GradSink, GruOp, from_nhwc, live, live_input, to_nhwc
 from .solver import FIXED, odeint_dopri5, odeint_fixed
 
 
@@ -480,7 +480,7 @@ def conv_same(x: torch.Tensor, m: nn.Conv2d) -> torch.Tensor:
     op = _LONE_OPS.get(m)
     if op is None:
         op = _LONE_OPS[m] = ConvNetOp(nn.Sequential(m), "conv_same")
-    return _ConvNetFn.apply(op, x, *op.params())
+    return _ConvNetFn.apply(op, live_input(x), *live(op.params()))
 
 
 class _ConvSameWFn(torch.autograd.Function):
@@ -615,7 +615,7 @@ class ODEFunc(nn.Module):
         if y.shape[0] == 0:
             grad = _empty_result((0, op.c_out) + tuple(y.shape[2:]), y, op.params())
         else:
-            grad = _ConvNetFn.apply(op, y, *op.params())
+            grad = _ConvNetFn.apply(op, live_input(y), *live(op.params()))
         if backwards:
             grad = -grad
         return grad
@@ -652,7 +652,7 @@ class DiffEqSolver(nn.Module):
                                  "control; give every rank at least one sample")
             return _empty_result((t.numel(), 0) + tuple(y0.shape[1:]), y0, op.params())
         if method in FIXED:
-            return odeint_fixed(op, y0, t, method)
+            return odeint_fixed(op, y0, t, method)          # (validates t when that needs no device sync)
         if method == 'dopri5':
             return odeint_dopri5(op, self, y0, t, self.odeint_rtol, self.odeint_atol)
         raise ValueError('Invalid method "{}" (euler, rk4 and dopri5 are supported)'.format(method))
@@ -750,7 +750,7 @@ class ConvGRUCell(nn.Module):
             if h_cur.size(0) == 0:
                 h_next = _empty_result(tuple(h_cur.shape), h_cur, [x] + op.params())
             else:
-                h_next = _GruStepFn.apply(op, x, h_cur, *op.params())
+                h_next = _GruStepFn.apply(op, live_input(x), live_input(h_cur), *live(op.params()))
             output_inner.append(h_next)
             h_cur = h_next
         return torch.stack(output_inner, dim=dim), h_next
@@ -797,6 +797,9 @@ class _EncoderFn(torch.autograd.Function):
     def backward(ctx, dhs):
         be = K.backend()
         f_op, g_op, order, deltas, saved = ctx.f_op, ctx.g_op, ctx.order, ctx.deltas, ctx.saved
+        if saved is None:
+            raise RuntimeError("ODEConvGRUCell: this recurrence was already back-propagated through once; its saved "
+                               "activations are freed during that pass (no retain_graph) -- run the forward again")
         d = to_nhwc(dhs.float())
         if not d.is_contiguous():
             d = d.contiguous()
@@ -862,6 +865,9 @@ class ODEConvGRUCell(nn.Module):
             nn.ReLU(),
             nn.Conv2d(z, out_ch * 2, 1, 1, 0)).to(device)
         self._z0_op: Optional[ConvNetOp] = None
+        self._delta_idx: dict = {}
+        self._flag: Optional[torch.Tensor] = None     # sticky device error word (bit0: NaN in the recurrence)
+        self.check_nan = True
 
     def _transform_op(self) -> ConvNetOp:
         if self._z0_op is None or self._z0_op.layers[0][0] is not self.transform_z0[0]:
@@ -874,27 +880,37 @@ class ODEConvGRUCell(nn.Module):
         if last_yi.shape[0] == 0:
             trans_last_yi = _empty_result((0, op.c_out) + tuple(last_yi.shape[2:]), last_yi, op.params())
         else:
-            trans_last_yi = _ConvNetFn.apply(op, last_yi, *op.params())     # (b, self.z0_dim*2, h, w)
+            trans_last_yi = _ConvNetFn.apply(op, live_input(last_yi), *live(op.params()))     # (b, self.z0_dim*2, h, w)
         mean_z0, std_z0 = torch.split(trans_last_yi, self.z0_dim, dim=1)
         std_z0 = std_z0.abs()
         return mean_z0, std_z0
 
     def _deltas(self, timesteps, device, order):
         """Step sizes exactly as the reference forms them (fp64): prev_t, t_i = t[-1]+0.01, t[-1]; then prev_t, t_i =
-        t[i], t[i-1] after visiting frame i (modules/ODEConvGRUCell.py:48,73).  Cached per timesteps tensor: the index
-        tensor below is a pageable host->device copy, which must not happen while a CUDA graph is being captured."""
-        key = (timesteps.data_ptr(), timesteps._version, tuple(timesteps.shape), str(device), order)
-        if getattr(self, "_delta_key", None) == key:
-            return self._delta_val
+        t[i], t[i-1] after visiting frame i (modules/ODEConvGRUCell.py:48,73; index -1 wraps like the reference's).
+        Recomputed from the VALUES of `timesteps` on every call, on the device (three tiny torch ops, capturable in a CUDA
+        graph); only the gather index -- a function of (order, device) alone -- is cached, because building it is a
+        pageable host->device copy, which must not happen during graph capture."""
         t = len(order)
         ts = timesteps.detach().to(device=device, dtype=torch.float64)
-        deltas = torch.empty(t, dtype=torch.float64, device=device)
-        deltas[0] = ts[-1] - (ts[-1] + 0.01)
-        if t > 1:
-            idx = torch.tensor(list(order[:-1]), device=device)
-            deltas[1:] = ts[idx - 1] - ts[idx]
-        self._delta_key, self._delta_val = key, deltas
-        return deltas
+        key = (str(device), order)
+        idx = self._delta_idx.get(key)
+        if idx is None:
+            idx = self._delta_idx[key] = (torch.tensor(list(order[:-1]), dtype=torch.long, device=device),
+                                          torch.tensor([(i - 1) % t for i in order[:-1]], dtype=torch.long, device=device))
+        first = (ts[-1] - (ts[-1] + 0.01)).reshape(1)
+        if t == 1:
+            return first
+        return torch.cat((first, ts[idx[1]] - ts[idx[0]]))
+
+    def check_errors(self) -> None:
+        """Raise what the reference's per-frame asserts would have raised (modules/ODEConvGRUCell.py:56,59: NaN in the Euler
+        increment / the updated state) from the sticky device word: ONE device->host read, after the forward.  forward()
+        calls it itself unless a CUDA graph is being captured or `self.check_nan` is False; a caller that replays a captured
+        step calls it whenever it wants the check (e.g. together with reading the loss)."""
+        if self._flag is not None and int(self._flag.item()) != 0:
+            self._flag.zero_()
+            raise AssertionError("NaN in the ODE-ConvGRU encoder state (modules/ODEConvGRUCell.py:56,59)")
 
     def run_ode_conv_gru(self, inputs, timesteps, run_backwards=True, mask=None):
         t, b, c, h, w = inputs.size()
@@ -910,7 +926,14 @@ class ODEConvGRUCell(nn.Module):
         if b == 0:
             hs = _empty_result((t, 0, g_op.C, h, w), inputs, params)
         else:
-            hs = _EncoderFn.apply(f_op, g_op, len(f_op.params()), order, inputs, deltas, *params)   # [T,B,C,H,W]
+            hs = _EncoderFn.apply(f_op, g_op, len(f_op.params()), order, live_input(inputs), deltas, *live(params))   # [T,B,C,H,W]
+            if self.check_nan:
+                if self._flag is None or self._flag.device != hs.device:
+                    self._flag = torch.zeros(1, dtype=torch.int32, device=hs.device)
+                last = hs.detach()[t - 1].movedim(-3, -1)            # the kernels' NHWC buffer of the final hidden state
+                K.backend().nan_flag(last if last.is_contiguous() else last.contiguous(), self._flag, 1)
+                if not (hs.is_cuda and torch.cuda.is_current_stream_capturing()):
+                    self.check_errors()
         yi = hs[t - 1]
         latent_ys = hs.permute(1, 0, 2, 3, 4)   # (b, t, c, h, w)
         return yi, latent_ys

@@ -63,6 +63,18 @@ def from_nhwc(x: torch.Tensor, dense_nchw: bool = False) -> torch.Tensor:
     return K.backend().nhwc_to_nchw(x, out)
 
 
+def live(params):
+    """The parameter list an autograd Function of this package is applied to: the parameters themselves when a backward may
+    follow, NOTHING under torch.no_grad() -- ctx.needs_input_grad still reports True there for a tensor that requires grad,
+    and the Functions key "save activations for the backward" on it (an inference rollout must not keep 36 f-evals of
+    activations alive, nor write dopri5's per-step checkpoints)."""
+    return tuple(params) if torch.is_grad_enabled() else ()
+
+
+def live_input(x: torch.Tensor) -> torch.Tensor:
+    return x if torch.is_grad_enabled() else x.detach()
+
+
 class GradSink:
     """fp32 accumulators for parameter gradients, keyed by parameter identity (kernels accumulate with +=)."""
 

@@ -17,7 +17,7 @@ import torch
 
 from . import _lib
 from . import kernels as K
-from .ops import ConvNetOp, GradSink, from_nhwc, to_nhwc
+from .ops import ConvNetOp, GradSink, from_nhwc, live, live_input, to_nhwc
 
 
 class Tableau:
@@ -167,6 +167,9 @@ class _FixedGridFn(torch.autograd.Function):
     def backward(ctx, dsol):
         be = K.backend()
         op, tab, dts, saved = ctx.op, ctx.tab, ctx.dts, ctx.saved
+        if saved is None:
+            raise RuntimeError("DiffEqSolver: this rollout was already back-propagated through once; its saved stage "
+                               "activations are freed during that pass (no retain_graph) -- run the forward again")
         d = to_nhwc(dsol.float())
         if not d.is_contiguous():
             d = d.contiguous()
@@ -188,12 +191,25 @@ class _FixedGridFn(torch.autograd.Function):
         return (None, None, dy0, None) + sink.result(ctx.params)
 
 
+def check_time_grid(t: torch.Tensor) -> None:
+    """odeint._check_inputs: t strictly monotone.  Checked on the host when that costs nothing (t still on the CPU, as
+    helpers/utils.py:118-120 creates it) or when no CUDA graph is being captured; a decreasing grid is fine for the
+    fixed-grid solvers (torchdiffeq flips the sign of t and f: dt * f is the same number)."""
+    if t.numel() < 3 or (t.is_cuda and torch.cuda.is_current_stream_capturing()):
+        return
+    d = t.detach()[1:] - t.detach()[:-1]
+    if not (bool((d > 0).all()) or bool((d < 0).all())):
+        raise AssertionError("t must be strictly increasing or decreasing")
+
+
 def odeint_fixed(op: ConvNetOp, y0: torch.Tensor, t: torch.Tensor, method: str) -> torch.Tensor:
     """euler / rk4 on the output grid.  y0: logical [B,C,H,W]; returns logical [T,B,C,H,W] (channels-last memory)."""
     tab = FIXED[method]
+    if not t.is_cuda:
+        check_time_grid(t)
     td = t.detach().to(device=y0.device, dtype=torch.float64)
     dts = (td[1:] - td[:-1]).contiguous()
-    return _FixedGridFn.apply(op, tab, y0, dts, *op.params())
+    return _FixedGridFn.apply(op, tab, live_input(y0), dts, *live(op.params()))
 
 
 # ------------------------------------------------------------------------------------------------- dopri5
@@ -208,24 +224,34 @@ _I_DONE = _lib.OFF_DONE // 4
 class DopriStats:
     """What the device-resident controller reported for one forward (read back once, after the last chunk)."""
 
-    def __init__(self, st: _lib.DopriState, log: Optional[torch.Tensor], syncs: int):
+    def __init__(self, st: _lib.DopriState, attempts, syncs: int, t_host=None):
         self.n_accept, self.n_reject = st.n_accept, st.n_reject
         self.n_feval, self.n_attempt = st.n_feval, st.n_attempt
         self.status, self.host_syncs = st.status, syncs
         self.t_final, self.dt_final = st.t1, st.dt
-        n = min(st.n_attempt, 0 if log is None else log.shape[0])
-        self.attempts = [tuple(r) for r in log[:n].tolist()] if n else []   # (t0, dt, err_ratio, accepted)
+        self.attempts = attempts            # [(t0, dt, err_ratio, accepted)] (the first log_cap of them)
+        self.t_host = t_host                # the output times, from the same read
 
     def __repr__(self):
         return "DopriStats(accept=%d reject=%d feval=%d syncs=%d status=%d)" % (
             self.n_accept, self.n_reject, self.n_feval, self.host_syncs, self.status)
 
 
-def _read_state(st_dev: torch.Tensor) -> _lib.DopriState:
-    """One device->host read of the controller header (this is the forward's host sync)."""
-    host = st_dev[:_lib.STATE_HEAD_BYTES].cpu()
-    raw = bytes(host.numpy().tobytes())
-    return _lib.DopriState.from_buffer_copy(raw[:ctypes.sizeof(_lib.DopriState)])
+def _read_back(ws: "Dopri5Workspace", t_dev: torch.Tensor, issued: int):
+    """THE device->host read of a forward (one per speculative chunk): the 256-byte controller header, the output times
+    and the log rows of the attempts issued so far, gathered on the device into one buffer and copied once."""
+    n_log = max(0, min(issued, ws.log.shape[0]))
+    parts = [ws.st[:_lib.STATE_HEAD_BYTES], t_dev.view(torch.uint8)]
+    if n_log:
+        parts.append(ws.log[:n_log].view(torch.uint8).reshape(-1))
+    host = torch.cat(parts).cpu()
+    raw = host.numpy().tobytes()
+    st = _lib.DopriState.from_buffer_copy(raw[:ctypes.sizeof(_lib.DopriState)])
+    o = _lib.STATE_HEAD_BYTES
+    T = t_dev.numel()
+    t_host = host[o:o + 8 * T].view(torch.float64).tolist()
+    rows = host[o + 8 * T:].view(torch.float64).reshape(-1, 4).tolist() if n_log else []
+    return st, t_host, [tuple(r) for r in rows[:min(st.n_attempt, n_log)]]
 
 
 class Dopri5Workspace:
@@ -254,7 +280,7 @@ class Dopri5Workspace:
 
 def dopri5_forward(op: ConvNetOp, y: torch.Tensor, t_dev: torch.Tensor, rtol: float, atol: float,
                    reduce_fn=None, chunk_hint: int = 8, max_attempts: int = 4096, save_cap: int = 0,
-                   log_cap: int = 4096):
+                   log_cap: Optional[int] = None):
     """Adaptive Dormand-Prince 5(4) (torchdiffeq rk_common / dopri5 / interp) over dense NHWC
     state y.  Returns (sol [T, ...], stats, workspace).  Attempts are enqueued speculatively in chunks; every
     kernel of an attempt is a no-op once the device `done` flag is set, so a chunk that overshoots only costs
@@ -262,64 +288,76 @@ def dopri5_forward(op: ConvNetOp, y: torch.Tensor, t_dev: torch.Tensor, rtol: fl
     a batch sharded over ranks takes the step sequence of the global batch."""
     be = K.backend()
     T = t_dev.numel()
+    if log_cap is None:
+        log_cap = max(1, min(int(max_attempts), 1 << 16))
     ws = Dopri5Workspace(y, T, log_cap, save_cap, be)
     sol = torch.empty((T,) + tuple(y.shape), dtype=torch.float32, device=y.device)
     be.lincomb(sol[0], [y], [1.0])
     be.lincomb(ws.y, [y], [1.0])
-    be.dopri_init(ws.st, t_dev, T, rtol, atol, max_attempts)
+    be.dopri_init(ws.st, t_dev, T, rtol, atol, max_attempts, save_cap)
     syncs = 0
+    issued = 0
+    fused = reduce_fn is None          # single GPU: the norm kernels' last block runs the controller (no 1-thread launches)
     if T > 1:
         # ---- initial step size (misc._select_initial_step, order 4): two f-evals and three RMS norms
         op.fwd(ws.y, out=ws.k[0])
-        be.dopri_initnorm(ws.st, 0, ws.y, ws.k[0], None)
-        if reduce_fn is not None:
+        be.dopri_initnorm(ws.st, 0, ws.y, ws.k[0], None, fuse_ctrl=fused)
+        if not fused:
             reduce_fn(ws.red)
-        be.dopri_initctrl(ws.st, 0)
+            be.dopri_initctrl(ws.st, 0)
         be.lincomb(ws.y1, [ws.y, ws.k[0]], [1.0, 1.0], dtmask=2, dt_dev=ws.h0)
         op.fwd(ws.y1, out=ws.k[1])
-        be.dopri_initnorm(ws.st, 1, ws.y, ws.k[0], ws.k[1])
-        if reduce_fn is not None:
+        be.dopri_initnorm(ws.st, 1, ws.y, ws.k[0], ws.k[1], fuse_ctrl=fused)
+        if not fused:
             reduce_fn(ws.red)
-        be.dopri_initctrl(ws.st, 1)
+            be.dopri_initctrl(ws.st, 1)
         # ---- attempts
         chunk = max(1, int(chunk_hint))
-        issued = 0
         while True:
             for _ in range(chunk):
-                _dopri_attempt(be, op, ws, t_dev, sol, reduce_fn)
-            issued += chunk
-            st = _read_state(ws.st)
+                _dopri_attempt(be, op, ws, t_dev, sol, reduce_fn, issued)
+                issued += 1
+            st, t_host, attempts = _read_back(ws, t_dev, issued)
             syncs += 1
             if st.done or issued >= max_attempts:
                 break
             chunk = max(2, min(64, st.n_attempt // 2))
     else:
-        st = _read_state(ws.st)
+        st, t_host, attempts = _read_back(ws, t_dev, 0)
         syncs += 1
-    stats = DopriStats(st, ws.log, syncs)
-    # torchdiffeq's asserts (rk_common._adaptive_step), raised once per forward from the device-side sticky flags
+    stats = DopriStats(st, attempts, syncs, t_host)
+    # torchdiffeq's asserts (odeint._check_inputs, rk_common._adaptive_step), raised once per forward from the host copy of t
+    # and the device-side sticky flags
+    if any(not (b > a) for a, b in zip(t_host[:-1], t_host[1:])):
+        raise AssertionError("t must be strictly increasing (dopri5 on a decreasing or unsorted time grid is not supported)")
     if st.status & 1:
         raise AssertionError("underflow in dt {}".format(st.dt))
     if st.status & 2:
         raise AssertionError("non-finite values in state `y`")
+    if st.status & 8:
+        raise RuntimeError("dopri5: more than %d accepted steps -- the backward checkpoint capacity; the integration was "
+                           "stopped there.  Raise DiffEqSolver.save_budget_bytes" % save_cap)
     if st.status & 4 or not st.done:
         raise AssertionError("max_num_steps exceeded ({} attempts)".format(st.n_attempt))
     return sol, stats, ws
 
 
-def _dopri_attempt(be, op: ConvNetOp, ws: Dopri5Workspace, t_dev, sol, reduce_fn):
-    """One speculative attempt: 6 stage combinations + 6 f-evals, error norm, controller, dense output/advance."""
+def _dopri_attempt(be, op: ConvNetOp, ws: Dopri5Workspace, t_dev, sol, reduce_fn, seq: int):
+    """One speculative attempt: 6 x (stage combination + f-eval), then K4 (error estimate + RMS norm + accept/reject +
+    step-size controller, one kernel) and K5 (dense output + FSAL advance): 14 launches, none of them single-threaded.
+    With a sharded batch the 4 partial sums are all-reduced between the norm and the decision (one more small launch)."""
     skip = ws.done
-    be.dopri_begin(ws.st)
     for s in range(6):
         dst = ws.y1 if s == 5 else ws.ystage[s & 1]
         _lin(be, dst, [ws.y] + ws.k[:s + 1], [1.0] + DP_BETA[s], dt_dev=ws.dt_try, dt_from=1, skip=skip)
         op.fwd(dst, out=ws.k[s + 1], skip=skip)
-    be.dopri_errnorm(ws.st, ws.y, ws.y1, ws.k)
-    if reduce_fn is not None:
+    if reduce_fn is None:
+        be.dopri_errctrl(ws.st, t_dev, ws.y, ws.y1, ws.k, ws.log, ws.log.shape[0], seq)
+    else:
+        be.dopri_errnorm(ws.st, ws.y, ws.y1, ws.k)
         reduce_fn(ws.red)
-    be.dopri_ctrl(ws.st, t_dev, ws.log, ws.log.shape[0])
-    be.dopri_advance(ws.st, t_dev, ws.y, ws.y1, ws.k, sol, ws.ysave, ws.fsave, ws.save_cap)
+        be.dopri_ctrl(ws.st, t_dev, ws.log, ws.log.shape[0], seq)
+    be.dopri_advance(ws.st, t_dev, ws.y, ws.y1, ws.k, sol, ws.ysave, ws.fsave, ws.save_cap, seq)
 
 
 def _interp_polys(x: float):
@@ -364,17 +402,20 @@ class _Dopri5Fn(torch.autograd.Function):
         solver._chunk_hint = stats.n_attempt + 1        # next forward: one chunk, one host sync
         solver.last_stats = stats
         if save:
-            if stats.n_accept > save_cap:
-                raise RuntimeError("dopri5: %d accepted steps exceed the backward checkpoint capacity %d; raise "
-                                   "DiffEqSolver.save_budget_bytes" % (stats.n_accept, save_cap))
+            if stats.n_attempt > len(stats.attempts):
+                raise RuntimeError("dopri5: %d attempts exceed the step log (%d rows) the backward replays; lower "
+                                   "DiffEqSolver.max_attempts" % (stats.n_attempt, len(stats.attempts)))
             ctx.op, ctx.ws, ctx.stats, ctx.params = op, ws, stats, params
-            ctx.t_host = t_dev.detach().cpu().tolist()
+            ctx.t_host = stats.t_host               # from the forward's single read-back
         return from_nhwc(sol)
 
     @staticmethod
     def backward(ctx, dsol):
         be = K.backend()
         op, ws, stats = ctx.op, ctx.ws, ctx.stats
+        if ws is None:
+            raise RuntimeError("DiffEqSolver(dopri5): this rollout was already back-propagated through once; its step "
+                               "checkpoints are freed during that pass (no retain_graph) -- run the forward again")
         d = to_nhwc(dsol.float())
         if not d.is_contiguous():
             d = d.contiguous()
@@ -474,4 +515,4 @@ class _Dopri5Fn(torch.autograd.Function):
 
 def odeint_dopri5(op: ConvNetOp, solver, y0: torch.Tensor, t: torch.Tensor, rtol: float, atol: float) -> torch.Tensor:
     td = t.detach().to(device=y0.device, dtype=torch.float64).contiguous()
-    return _Dopri5Fn.apply(op, solver, y0, td, float(rtol), float(atol), *op.params())
+    return _Dopri5Fn.apply(op, solver, live_input(y0), td, float(rtol), float(atol), *live(op.params()))

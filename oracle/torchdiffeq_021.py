@@ -7,9 +7,12 @@ reference tree, not installed in this image and not downloadable (no network).  
 restates the published algorithm of that release (odeint.py, misc.py, solvers.py,
 fixed_grid.py, rk_common.py, dopri5.py, interp.py) as specified in SURVEY.md Appendix A.
 The reference holds no tests / golden vectors for the path, so this oracle is pinned only by
-(i) its own self-tests (analytic ODEs, convergence order, scipy RK45 cross-check, FSAL
-identity -- tests/test_oracle_odeint.py) and (ii) the reference's call sites
-(`modules/DiffEqSolver.py:37,45-46`).
+(i) its self-tests in tests/test_oracle_odeint.py -- closed-form solutions, measured convergence
+orders 1 / 4 / 5, and an INDEPENDENT implementation of the same published method: scipy 1.x
+`integrate._ivp.rk.RK45` (same Dormand-Prince tableau and Shampine dense output; single steps,
+the error estimate up to the known 2/3 factor between the two embedded pairs, the dense output
+and `select_initial_step` agree to fp64 rounding; whole solves to O(tol)) -- and (ii) the
+reference's call sites (`modules/DiffEqSolver.py:37,45-46`).
 
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference leg may
 import this module.  The product (ode_rl_b200/) never does.
@@ -156,8 +159,43 @@ def _interp_evaluate(coeffs, t0, t1, t):
     return total
 
 
+def _runge_kutta_step(func, y, f, t0, dt, log=None):
+    """rk_common._runge_kutta_step with the Dormand-Prince tableau: (y1, f1, y1_error, k[0..6]).  t0 / dt fp64 0-dim
+    tensors (or floats); the stage sums run j = 0..i ascending in the state dtype, as `k[..., :i+1].matmul(beta_i * dt)`."""
+    dtype = y.dtype
+    dt32 = torch.as_tensor(dt, dtype=torch.float64).to(dtype)
+    k = [f]
+    yi = y
+    for s in range(6):
+        acc = None
+        for j in range(s + 1):
+            term = k[j] * (dt32 * torch.tensor(DP_BETA[s][j], dtype=dtype))
+            acc = term if acc is None else acc + term
+        yi = y + acc
+        k.append(func(t0 + DP_ALPHA[s] * dt, yi))
+        if log is not None:
+            log.n_feval += 1
+    y1, f1 = yi, k[6]                       # FSAL: c_sol[:-1] == beta[5] and c_sol[6] == 0
+    err = None
+    for j in range(7):
+        term = k[j] * (dt32 * torch.tensor(DP_C_ERROR[j], dtype=dtype))
+        err = term if err is None else err + term
+    return y1, f1, err, k
+
+
+def _dopri5_interp_fit(y, y1, k, dt):
+    """dopri5.Dopri5Solver._interp_fit: y_mid from c_mid, then the quartic through (y0, f0, y_mid, y1, f1)."""
+    dtype = y.dtype
+    dt32 = torch.as_tensor(dt, dtype=torch.float64).to(dtype)
+    mid = None
+    for j in range(7):
+        term = k[j] * (dt32 * torch.tensor(DP_C_MID[j], dtype=dtype))
+        mid = term if mid is None else mid + term
+    y_mid = y + mid
+    return _interp_fit(y, y1, y_mid, k[0], k[6], dt32)
+
+
 def _dopri5(func, y0, t, rtol, atol, log, detach_dt0=True, max_num_steps=2 ** 31 - 1):  # noqa
-    dtype = y0.dtype
     t = t.to(torch.float64)
     f0 = func(t[0], y0)
     log.n_feval += 1
@@ -176,33 +214,13 @@ def _dopri5(func, y0, t, rtol, atol, log, detach_dt0=True, max_num_steps=2 ** 31
             assert t1 + dt > t1, "underflow in dt {}".format(float(dt))
             assert torch.isfinite(y).all(), "non-finite values in state `y`: {}".format(y)
             t0_a = t1
-            dt32 = dt.to(dtype)
-            k = [f]
-            yi = y
-            for s in range(6):
-                acc = None
-                for j in range(s + 1):
-                    term = k[j] * (dt32 * torch.tensor(DP_BETA[s][j], dtype=dtype))
-                    acc = term if acc is None else acc + term
-                yi = y + acc
-                k.append(func(t0_a + DP_ALPHA[s] * dt, yi))
-                log.n_feval += 1
-            y1, f1 = yi, k[6]
-            err = None
-            for j in range(7):
-                term = k[j] * (dt32 * torch.tensor(DP_C_ERROR[j], dtype=dtype))
-                err = term if err is None else err + term
+            y1, f1, err, k = _runge_kutta_step(func, y, f, t0_a, dt, log)
             tol = atol + rtol * torch.max(y.abs(), y1.abs())
             ratio = _rms_norm(err / tol)
             accept = bool(ratio <= 1)
-            log.attempts.append((float(t0_a), float(dt), float(ratio), accept))
+            log.attempts.append((float(t0_a), float(dt), float(ratio.detach()), accept))
             if accept:
-                mid = None
-                for j in range(7):
-                    term = k[j] * (dt32 * torch.tensor(DP_C_MID[j], dtype=dtype))
-                    mid = term if mid is None else mid + term
-                y_mid = y + mid
-                coeffs = _interp_fit(y, y1, y_mid, k[0], f1, dt32)
+                coeffs = _dopri5_interp_fit(y, y1, k, dt)
                 t0_prev, t1 = t0_a, t0_a + dt
                 y, f = y1, f1
             dt = _optimal_step_size(dt, ratio.detach().to(torch.float64))

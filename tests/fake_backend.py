@@ -285,16 +285,17 @@ class FakeBackend:
     def dopri_state_bytes(self):
         return _lib.STATE_HEAD_BYTES + 3 * 592 * 8 + 64
 
-    def dopri_init(self, st, t_dev, n_out, rtol, atol, max_attempts):
+    def dopri_init(self, st, t_dev, n_out, rtol, atol, max_attempts, save_cap=0):
         self.launches += 1
         st.zero_()
         s = _State(st).s
         s.t0 = s.t1 = float(t_dev[0])
         s.rtol, s.atol = rtol, atol
         s.n_out, s.jnext, s.max_attempts = n_out, 1, max_attempts
+        s.save_cap, s.adv_seq = save_cap, -1
         s.done = 1 if n_out <= 1 else 0
 
-    def dopri_initnorm(self, st, phase, y0, f0, f1):
+    def dopri_initnorm(self, st, phase, y0, f0, f1, fuse_ctrl=False):
         self.launches += 1
         s = _State(st).s
         if s.done:
@@ -308,12 +309,27 @@ class FakeBackend:
             s.red[1] = 0.0
         s.red[2] = 0.0
         s.red[3] = float(y0.numel())
+        if fuse_ctrl:
+            self._initctrl(s, phase)
 
     def dopri_initctrl(self, st, phase):
         self.launches += 1
         s = _State(st).s
         if s.done:
             return
+        self._initctrl(s, phase)
+
+    @staticmethod
+    def _begin_next(s):
+        s.dt_try = s.dt
+        if not (s.t1 + s.dt > s.t1):
+            s.status |= 1
+            s.done = 1
+        if s.n_attempt >= s.max_attempts:
+            s.status |= 4
+            s.done = 1
+
+    def _initctrl(self, s, phase):
         if phase == 0:
             d0 = f32(math.sqrt(s.red[0] / s.red[3]))
             d1 = f32(math.sqrt(s.red[1] / s.red[3]))
@@ -330,25 +346,9 @@ class FakeBackend:
             else:
                 h1 = f32(np.power(f32(0.01) / max(d1, d2), f32(0.2)))
             s.dt = float(min(f32(100) * h0, h1))
+            self._begin_next(s)
 
-    def dopri_begin(self, st):
-        self.launches += 1
-        s = _State(st).s
-        if s.done:
-            return
-        s.dt_try = s.dt
-        if not (s.t1 + s.dt > s.t1):
-            s.status |= 1
-            s.done = 1
-        if s.n_attempt >= s.max_attempts:
-            s.status |= 4
-            s.done = 1
-
-    def dopri_errnorm(self, st, y0, y1, k7):
-        self.launches += 1
-        s = _State(st).s
-        if s.done:
-            return
+    def _errnorm(self, s, y0, y1, k7):
         dt = f32(s.dt_try)
         err = None
         for j in (0, 2, 3, 4, 5, 6):
@@ -361,11 +361,29 @@ class FakeBackend:
         s.red[2] = 0.0
         s.red[3] = float(y0.numel())
 
-    def dopri_ctrl(self, st, t_dev, log, log_cap):
+    def dopri_errnorm(self, st, y0, y1, k7):
         self.launches += 1
         s = _State(st).s
         if s.done:
             return
+        self._errnorm(s, y0, y1, k7)
+
+    def dopri_errctrl(self, st, t_dev, y0, y1, k7, log, log_cap, seq):
+        self.launches += 1
+        s = _State(st).s
+        if s.done:
+            return
+        self._errnorm(s, y0, y1, k7)
+        self._ctrl(s, t_dev, log, log_cap, seq)
+
+    def dopri_ctrl(self, st, t_dev, log, log_cap, seq):
+        self.launches += 1
+        s = _State(st).s
+        if s.done:
+            return
+        self._ctrl(s, t_dev, log, log_cap, seq)
+
+    def _ctrl(self, s, t_dev, log, log_cap, seq):
         dt = s.dt_try
         if s.red[1] > 0:
             s.status |= 2
@@ -380,18 +398,24 @@ class FakeBackend:
         if log is not None and a < log_cap:
             log[a, 0], log[a, 1], log[a, 2], log[a, 3] = s.t1, dt, ratio, accept
         s.n_attempt = a + 1
+        finished = False
         if accept:
+            if s.save_cap > 0 and s.n_accept >= s.save_cap:
+                s.status |= 8
+                s.done = 1
+                return
             s.t0 = s.t1
             s.t1 = s.t1 + dt
             s.n_accept += 1
+            s.dt_acc = dt
+            s.adv_seq = seq
             j = s.jnext
             s.jlo = j
             while j < s.n_out and not (float(t_dev[j]) > s.t1):
                 j += 1
             s.jhi = j
             s.jnext = j
-            if j >= s.n_out:
-                s.done_next = 1
+            finished = j >= s.n_out
         else:
             s.n_reject += 1
             s.jlo = s.jhi = s.jnext
@@ -401,13 +425,17 @@ class FakeBackend:
             dfactor = 1.0 if ratio < 1.0 else 0.2
             factor = min(10.0, max(0.9 / ratio ** 0.2, dfactor))
         s.dt = dt * factor
-
-    def dopri_advance(self, st, t_dev, y0, y1, k7, sol, ysave, fsave, save_cap):
-        self.launches += 2
-        s = _State(st).s
-        if s.done or not s.accept:
+        if finished:
+            s.done = 1
             return
-        dt = float(f32(s.dt_try))
+        self._begin_next(s)
+
+    def dopri_advance(self, st, t_dev, y0, y1, k7, sol, ysave, fsave, save_cap, seq):
+        self.launches += 1
+        s = _State(st).s
+        if s.adv_seq != seq:
+            return
+        dt = float(f32(s.dt_acc))
         step = s.n_accept - 1
         f0, f1 = k7[0].clone(), k7[6].clone()
         if ysave is not None and step < save_cap:
@@ -428,8 +456,11 @@ class FakeBackend:
                 sol[j].copy_((((y0 + x * cd) + x * x * cc) + x * x * x * cb) + x * x * x * x * ca)
         y0.copy_(y1)
         k7[0].copy_(f1)
-        if s.done_next:
-            s.done = 1
+
+    def nan_flag(self, x, flag, bit):
+        self.launches += 1
+        if bool(torch.isnan(x).any()):
+            flag |= bit
 
     # ------------------------------------------------------------------ layout
     def nchw_to_nhwc(self, x, out):

@@ -364,3 +364,132 @@ def test_encode_stem_autograd_wiring(fake_backend):
     exp = torch.autograd.grad((torch.tanh(ref) * w).sum(), ps)
     for g, r in zip(got, exp):
         assert rel_err(g, r) < 1e-5
+
+
+# ---- round-2 robustness items (ADVICE r1, VERDICT r1 weak #12 / missing #7) ------------------------------------------
+def _robustness_cases(odex, device):
+    """Runs on the fake backend here and on the CUDA kernels in tests/test_gpu_parity.py."""
+    import gc
+    import numpy as np
+
+    f = make_ode_func(odex, C=32, n_units=32, scale=2.0).to(device)
+    cell = odex.ODEConvGRUCell(f, None, (8, 16), 32).to(device)
+    torch.manual_seed(5)
+    x = torch.randn(4, 2, 32, 8, 16, device=device)
+    sd = {k: v.detach().cpu().clone() for k, v in cell.state_dict().items()}
+
+    # (1) the encoder step sizes follow the VALUES of `timesteps`: a second tensor of the same shape (allocated where the
+    #     first one lived after it is freed) must not hit a stale cache (ADVICE: modules.py:886)
+    for denom in (8.0, 12.0, 8.0):
+        ts = torch.tensor(np.arange(4) / denom).to(device)
+        with torch.no_grad():
+            m, _ = cell(x, ts)
+        rm, _ = refmodel.encoder_z0(sd, x.cpu(), ts.cpu())
+        assert rel_err(m, rm) < 1e-5, denom
+        del ts
+        gc.collect()
+    irregular = torch.tensor([0.0, 0.03, 0.2, 0.21], dtype=torch.float64)
+    with torch.no_grad():
+        m, _ = cell(x, irregular.to(device))
+    assert rel_err(m, refmodel.encoder_z0(sd, x.cpu(), irregular)[0]) < 1e-5
+
+    # (2) NaN in the recurrence -> AssertionError from the sticky device word, once per forward; the word is cleared
+    bad = x.clone()
+    bad[2, 1, 3, 4, 5] = float("nan")
+    with torch.no_grad():
+        with pytest.raises(AssertionError, match="NaN"):
+            cell(bad, irregular.to(device))
+        cell(x, irregular.to(device))
+
+    # (3) a second backward through the same graph fails loudly instead of with an AttributeError deep inside
+    solver = odex.DiffEqSolver(f, "rk4")
+    z0 = torch.randn(2, 32, 8, 16, device=device, requires_grad=True)
+    _, tp = timesteps(3, 3)
+    for make in (lambda: solver(z0, tp.to(device)), lambda: cell(x.clone().requires_grad_(True), irregular.to(device))[0],
+                 lambda: odex.DiffEqSolver(f, "dopri5", odeint_rtol=1e-3, odeint_atol=1e-4)(z0, tp.to(device))):
+        out = make()
+        loss = out.square().sum()
+        loss.backward(retain_graph=True)
+        with pytest.raises(RuntimeError, match="already back-propagated"):
+            loss.backward()
+
+    # (4) time grids: unsorted t is an error (torchdiffeq asserts), for dopri5 from the host copy the forward reads anyway;
+    #     a decreasing grid is exact for the fixed-grid solvers (negative dt)
+    unsorted = torch.tensor([0.5, 0.7, 0.6, 0.8], dtype=torch.float64)
+    with torch.no_grad():
+        with pytest.raises(AssertionError, match="strictly increasing"):
+            odex.DiffEqSolver(f, "dopri5", odeint_rtol=1e-3, odeint_atol=1e-4)(z0.detach(), unsorted.to(device))
+        with pytest.raises(AssertionError, match="strictly increasing or decreasing"):
+            odex.DiffEqSolver(f, "euler")(z0.detach(), unsorted)
+        dec = torch.tensor([0.8, 0.7, 0.55, 0.5], dtype=torch.float64)
+        sol = odex.DiffEqSolver(f, "rk4")(z0.detach(), dec.to(device))
+    fsd = {k: v.detach().cpu().clone() for k, v in solver.state_dict().items()}
+    y, ref = z0.detach().cpu(), [z0.detach().cpu()]
+    for a, b in zip(dec[:-1], dec[1:]):
+        y = y + tde._rk4_alt_step(lambda t_, v: refmodel.ode_func({k[len("ode_func."):]: w for k, w in fsd.items()}, v), a, b - a, y)
+        ref.append(y)
+    assert rel_err(sol, torch.stack(ref)) < 1e-5
+
+    # (5) more accepted steps than backward checkpoints: the device stops there and the host says so (no silent drop)
+    tight = odex.DiffEqSolver(f, "dopri5", odeint_rtol=1e-7, odeint_atol=1e-9)
+    tight.save_budget_bytes = 1                          # -> the minimum capacity of 4 steps
+    with pytest.raises(RuntimeError, match="checkpoint capacity"):
+        tight(z0, timesteps(10, 10)[1].to(device))
+    with torch.no_grad():                                # without a backward there is no capacity to exceed
+        tight(z0.detach(), timesteps(10, 10)[1].to(device))
+    assert tight.last_stats.n_accept > 4 and tight.last_stats.host_syncs >= 1
+
+
+def test_robustness_cases(fake_backend):
+    _robustness_cases(odex, torch.device("cpu"))
+
+
+def test_dopri5_one_read_back_carries_state_times_and_log(fake_backend):
+    """The forward's single device->host copy holds the controller header, the output times (the backward needs them) and
+    the attempt log: no other host read on the training path (VERDICT r1 weak #12)."""
+    f = make_ode_func(odex, C=32, n_units=32, scale=3.0)
+    solver = odex.DiffEqSolver(f, "dopri5", odeint_rtol=1e-3, odeint_atol=1e-4)
+    _, tp = timesteps(10, 10)
+    z0 = torch.randn(2, 32, 8, 16, requires_grad=True)
+    solver(z0, tp)                                        # learns the chunk size
+    calls = []
+    orig = torch.Tensor.cpu
+
+    def counting_cpu(self, *a, **k):
+        calls.append(tuple(self.shape))
+        return orig(self, *a, **k)
+
+    torch.Tensor.cpu = counting_cpu
+    try:
+        sol = solver(z0, tp)
+    finally:
+        torch.Tensor.cpu = orig
+    st = solver.last_stats
+    assert len(calls) == 1 and st.host_syncs == 1
+    assert st.t_host == tp.tolist() and len(st.attempts) == st.n_attempt
+    sol.sum().backward()
+
+
+@pytest.mark.parametrize("rtol,atol", [(1e-3, 1e-4), (1e-5, 1e-6)])
+def test_dt0_detach_deviation_is_of_the_order_of_rtol(rtol, atol):
+    """DESIGN.md section 2: the product (and the oracle's default) treat the initial step dt0 as a constant in the backward;
+    torchdiffeq 0.2.1 does not detach _select_initial_step (SURVEY A.4, A.7).  dt0 only enters through the FIRST attempt's
+    step size, and the converged solution depends on step sizes at the level of the local error, so the extra gradient path
+    is O(rtol) relative to the gradient -- the same size as the solver's own discretisation error.  Measured on the oracle,
+    both ways (1.7e-3 at rtol 1e-3)."""
+    torch.manual_seed(0)
+    f = make_ode_func(odex, C=16, n_units=16, scale=3.0, nonlinear="tanh")
+    sd = _sd(odex.DiffEqSolver(f, "dopri5"))
+    _, tp = timesteps(5, 5)
+    z0 = torch.randn(2, 16, 8, 8)
+    grads = []
+    for detach in (True, False):
+        ps = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+        z = z0.clone().requires_grad_(True)
+        fn = lambda t_, y: refmodel.ode_func({k[len("ode_func."):]: w for k, w in ps.items()}, y, "tanh")   # noqa: E731
+        sol = tde.odeint(fn, z, tp, rtol=rtol, atol=atol, method="dopri5", detach_dt0=detach)
+        sol[-1].square().sum().backward()
+        grads.append(torch.cat([z.grad.flatten()] + [p.grad.flatten() for p in ps.values() if p.grad is not None]))
+    gap = float((grads[0] - grads[1]).norm() / grads[1].norm())
+    print("dt0 gradient path at rtol %g: relative gap %.2e" % (rtol, gap))
+    assert gap < 5 * rtol
