@@ -41,8 +41,12 @@ def parse():
     ap.add_argument("--impl", default="odex", choices=["odex", "reference"])
     ap.add_argument("--batch", type=int, default=128, help="per-GPU batch (configs[1]: 128)")
     ap.add_argument("--method", default="rk4")
-    ap.add_argument("--cpu-batch", type=int, default=16)
+    ap.add_argument("--cpu-batch", type=int, default=0,
+                    help="batch of the CPU arm: 0 = the same batch as the GPU arm for --impl reference (same config), 16 for the "
+                         "bounded cpu_baseline sample inside the default line")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip the sub-records of the default line (dopri5 configs[2], small_batch configs[0], K4/K5 GB/s, strong scaling)")
     ap.add_argument("--no-graph", action="store_true", help="enqueue every step from Python instead of replaying a CUDA graph")
     ap.add_argument("--forward-only", action="store_true",
                     help="time the model forward alone (no_grad) instead of the training step: SURVEY.md 8d cfg3 (dopri5, batch 512)")
@@ -108,6 +112,14 @@ def time_cpu(method, batch, steps, warmup):
         step()
     dt = (time.perf_counter() - t0) / steps
     return batch * T_OUT / dt, dt
+
+
+def workload_name(method, forward_only, batch):
+    """config.workload, identical for the GPU arm and the --impl reference arm."""
+    cfg = ("1" if method != "dopri5" else "2 (as a training step)") if not forward_only else ("2" if method == "dopri5" else "1 (forward only)")
+    what = "forward (no_grad)" if forward_only else "forward+backward+Adam"
+    m = method + (" fixed-step" if method != "dopri5" else " adaptive rtol=1e-3 atol=1e-4")
+    return "BASELINE configs[%s]: ODEConvGRU %s, %s, batch %d per GPU, 10 in / 10 out 64x64x1" % (cfg, what, m, batch)
 
 
 def print_line(text):
@@ -327,6 +339,193 @@ def vidode_main(args, world, rank, local):
         dist.destroy_process_group()
 
 
+
+# ------------------------------------------------------------------------------------------- sub-records of the default line
+def _ev_time(fn, k, warm=2):
+    """seconds per call of fn over k calls, CUDA events on the current stream, after `warm` untimed calls."""
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(k):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / 1e3 / k
+
+
+def sub_dopri5(dev, B=512):
+    """BASELINE configs[2]: ODEConvGRU dopri5 (rtol 1e-3 / atol 1e-4), batch 512, device-resident step control, batch-shared
+    step size: forward (no_grad) and training step, with the solver's counters; default-init weights and the x3 'stiff-ish'
+    variant of SURVEY.md 8d in which attempts get rejected."""
+    from ode_rl_b200.harness import ODEConvGRUHarness
+
+    out = {"batch": B, "rtol": 1e-3, "atol": 1e-4}
+    x, y = synth(B, 4321, dev)
+    obs, tp = times(dev)
+    for name, scale in (("default_init", 1.0), ("stiff_x3", 3.0)):
+        torch.manual_seed(0)
+        model = ODEConvGRUHarness("dopri5", rtol=1e-3, atol=1e-4, device=dev).to(dev)
+        if scale != 1.0:
+            with torch.no_grad():
+                for p_ in model.ode_decoder_func.parameters():
+                    p_.mul_(scale)
+        opt = torch.optim.Adam(model.parameters(), lr=1e-3, fused=True)
+
+        def fwd():
+            with torch.no_grad():
+                return model(x, obs, tp, return_latents=False)
+
+        def train():
+            opt.zero_grad(set_to_none=True)
+            loss = torch.nn.functional.mse_loss(model(x, obs, tp, return_latents=False), y)
+            loss.backward()
+            opt.step()
+
+        t_f = _ev_time(fwd, 5)
+        st = model.diffeq_solver.last_stats
+        rec = {"forward_ms": t_f * 1e3, "forward_frames_per_s": B * T_OUT / t_f, "n_accept": st.n_accept, "n_reject": st.n_reject,
+               "n_feval": st.n_feval, "host_reads_per_forward": st.host_syncs}
+        if scale == 1.0:
+            opt_state = None
+            t_t = _ev_time(train, 3)
+            rec.update({"training_ms": t_t * 1e3, "training_frames_per_s": B * T_OUT / t_t})
+        out[name] = rec
+        del model, opt
+    torch.cuda.empty_cache()
+    return out
+
+
+def sub_small_batch(dev, with_cpu=True):
+    """BASELINE configs[0]: ODEConvGRU forward, batch 16, euler -- the reference's own CPU-runnable case -- on the GPU (eager
+    and as one replayed CUDA graph: at this size the ~260 launches, not the tensor work, decide the time) beside the CPU oracle
+    at the SAME batch; and the reference's test-time rollout length (configs.yaml:628-630: up to 190 predicted frames)."""
+    from ode_rl_b200 import _lib
+    from ode_rl_b200.harness import ODEConvGRUHarness
+
+    B = 16
+    torch.manual_seed(0)
+    model = ODEConvGRUHarness("euler", device=dev).to(dev).eval()
+    x, _ = synth(B, 99, dev)
+    obs, tp = times(dev)
+    out = {"batch": B, "method": "euler"}
+
+    def fwd(tp_=tp):
+        with torch.no_grad():
+            return model(x, obs, tp_, return_latents=False)
+
+    n0 = _lib.launch_count()
+    fwd()
+    launches = _lib.launch_count() - n0
+    t_e = _ev_time(fwd, 20)
+    # the same forward captured once and replayed
+    static_x = x.clone()
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for _ in range(2):
+            with torch.no_grad():
+                model(static_x, obs, tp, return_latents=False)
+    torch.cuda.current_stream().wait_stream(side)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        with torch.no_grad():
+            static_out = model(static_x, obs, tp, return_latents=False)
+    t_g = _ev_time(g.replay, 50)
+    out.update({"forward_ms_eager": t_e * 1e3, "forward_ms_graph": t_g * 1e3, "frames_per_s": B * T_OUT / t_g,
+                "libodex_launches_per_forward": int(launches), "launches_per_predicted_frame": launches / T_OUT})
+    # long rollout: 10 observed frames -> 190 predicted (rk4), batch 16
+    model.diffeq_solver.ode_method = "rk4"
+    ts = torch.tensor(np.arange(0, 200) / 200.0)
+    tp_long = ts[10:].to(dev)
+    n0 = _lib.launch_count()
+    t_l = _ev_time(lambda: fwd(tp_long), 3, warm=1)
+    n_l = (_lib.launch_count() - n0) / 4
+    out["long_rollout"] = {"predicted_frames": 190, "method": "rk4", "forward_ms": t_l * 1e3, "frames_per_s": B * 190 / t_l,
+                           "libodex_launches_per_predicted_frame": n_l / 190}
+    model.diffeq_solver.ode_method = "euler"
+    if with_cpu:
+        from oracle import refmodel
+        torch.set_num_threads(os.cpu_count() or 1)
+        sd = {k: v.detach().cpu() for k, v in model.state_dict().items()}
+        xc = x.cpu()
+        oc, tc = times("cpu")
+        with torch.no_grad():
+            ref = refmodel.odeconvgru_forward(sd, xc, oc, tc, "euler")
+            t0 = time.perf_counter()
+            for _ in range(3):
+                refmodel.odeconvgru_forward(sd, xc, oc, tc, "euler")
+            t_c = (time.perf_counter() - t0) / 3
+        err = float((static_out.cpu() - ref).abs().max())
+        out.update({"cpu_forward_ms": t_c * 1e3, "cpu_frames_per_s": B * T_OUT / t_c, "cpu_cores": os.cpu_count() or 1,
+                    "gpu_over_cpu": t_c / t_g, "max_abs_diff_vs_cpu_oracle": err})
+    del model
+    return out
+
+
+def sub_rk_kernels(dev, be, hbm, batches=(512, 2048)):
+    """Achieved GB/s (algorithmic bytes of SURVEY.md 8d / kernel time) of the dopri5 kernels north_star names: K4 =
+    dopri_errnorm_kernel (error estimate + RMS norm + accept/reject + controller in one launch: 8 planes read = 32 B/elem) and
+    K5 = dopri_advance_kernel (dense output for n_out output times + FSAL advance: 8 reads + n_out writes for the outputs, plus
+    the y / k0 advance writes, 2 more planes)."""
+    from ode_rl_b200 import _lib
+
+    res = {}
+    for nB in batches:
+        planes = [torch.randn(nB, 16, 16, 64, device=dev) * 0.1 for _ in range(9)]
+        y0, y1, k7 = planes[0], planes[1], planes[2:9]
+        n_el = y0.numel()
+        st = torch.zeros(be.dopri_state_bytes(), dtype=torch.uint8, device=dev)
+        t_dev = torch.tensor([0.0, 0.01, 1e300], dtype=torch.float64, device=dev)     # the last output is never reached
+        sol = torch.empty((3,) + tuple(y0.shape), device=dev)
+        log = torch.zeros((4096, 4), dtype=torch.float64, device=dev)
+        st64 = st[:_lib.STATE_HEAD_BYTES].view(torch.float64)
+
+        def reset():
+            be.dopri_init(st, t_dev, 3, 1e9, 1e9, 1 << 30, 0)        # huge tolerances: every attempt is accepted
+            st64[_lib.OFF_DT // 8] = 1e-3
+            st64[_lib.OFF_DT_TRY // 8] = 1e-3
+
+        reps = 20
+        reset()
+        for i in range(3):
+            be.dopri_errctrl(st, t_dev, y0, y1, k7, log, 4096, i)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reset()
+        e0.record()
+        for i in range(reps):
+            be.dopri_errctrl(st, t_dev, y0, y1, k7, log, 4096, i)
+        e1.record()
+        torch.cuda.synchronize()
+        t4 = e0.elapsed_time(e1) / 1e3 / reps
+        # K5: every launch finds its own sequence number published -> runs the full dense-output + advance pass (1 output inside)
+        st32 = st[:_lib.STATE_HEAD_BYTES].view(torch.int32)
+        adv, jlo, jhi = _lib.DopriState.adv_seq.offset // 4, _lib.DopriState.jlo.offset // 4, _lib.DopriState.jhi.offset // 4
+        reset()
+        st64[_lib.DopriState.dt_acc.offset // 8] = 1e-3
+        st64[_lib.DopriState.t1.offset // 8] = 0.02
+        st32[adv], st32[jlo], st32[jhi] = 7, 1, 2
+        for _ in range(3):
+            be.dopri_advance(st, t_dev, y0, y1, k7, sol, None, None, 0, 7)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(reps):
+            be.dopri_advance(st, t_dev, y0, y1, k7, sol, None, None, 0, 7)
+        e1.record()
+        torch.cuda.synchronize()
+        t5 = e0.elapsed_time(e1) / 1e3 / reps
+        b4, b5 = 8 * n_el * 4, (8 + 1 + 2) * n_el * 4
+        res["B%d" % nB] = {"plane_mb": n_el * 4 / 1e6,
+                           "K4_errnorm_ctrl": {"us": t4 * 1e6, "bytes": b4, "GBps": b4 / t4 / 1e9, "frac": b4 / t4 / 1e9 / hbm},
+                           "K5_dense_advance": {"us": t5 * 1e6, "bytes": b5, "GBps": b5 / t5 / 1e9, "frac": b5 / t5 / 1e9 / hbm,
+                                                "outputs_in_step": 1}}
+        del planes, sol
+    torch.cuda.empty_cache()
+    return res
+
+
 # ------------------------------------------------------------------------------------------- GPU arm
 def main():
     args = parse()
@@ -347,7 +546,7 @@ def main():
     if args.impl == "reference" and args.workload == "vidode":
         if rank != 0:
             return
-        cb = min(args.cpu_batch, 4)
+        cb = min(args.cpu_batch or 4, 4)
         val, dt = vidode_cpu(cb, max(1, args.steps))
         cores = os.cpu_count() or 1
         print(json.dumps({
@@ -363,14 +562,20 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return
-        val, dt = time_cpu(args.method, args.cpu_batch, max(1, args.steps), max(1, min(args.warmup, 1)))
+        cpu_batch = args.cpu_batch or args.batch
+        # bounded: at batch 128 one CPU training step is seconds; at most 4 timed steps + 1 warm-up (the GPU arm's K / W are sized
+        # for a 20 ms step)
+        k_cpu = max(1, min(args.steps, 4))
+        val, dt = time_cpu(args.method, cpu_batch, k_cpu, 1)
+        args.cpu_batch = cpu_batch
         cores = os.cpu_count() or 1
         line = {"impl": "reference", "metric": "ODEConvGRU training-step predicted frames/s", "value": val,
                 "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic",
-                "config": {"workload": "ODEConvGRU fwd+bwd+Adam, %s fixed-step, 10 in / 10 out 64x64x1" % args.method,
-                           "batch_per_step": args.cpu_batch},
+                "config": {"workload": workload_name(args.method, False, args.cpu_batch), "global_batch": args.cpu_batch,
+                           "batch_per_step": args.cpu_batch, "timed_steps": k_cpu,
+                           "parallelism": "one process, torch CPU with %d threads" % cores},
                 "cpu_baseline": {"value": val, "unit": "frames/s", "cores": cores, "kind": "port",
                                  "sample": "batch %d training steps of the configs[1] workload (reference wiring restated in "
                                            "oracle/refmodel.py + restated torchdiffeq 0.2.1; torch CPU, %d threads, anomaly "
@@ -520,7 +725,9 @@ def main():
         # (forward + data-gradient chains).  Launched back to back from Python: at ~66 us per launch the enqueue keeps ahead.
         L_net = 5
         xs = torch.randn(B, 16, 16, 64, device=dev)
-        wts = [be.pack_weights(torch.randn(64, 64, 3, 3, device=dev) * 0.05, False, True) for _ in range(L_net)]
+        from ode_rl_b200 import ops as _ops
+        split = 1 if _ops.CONV_SPLIT == "f16" else 0
+        wts = [be.pack_weights(torch.randn(64, 64, 3, 3, device=dev) * 0.05, False, 1 + split) for _ in range(L_net)]
         bss = [torch.randn(64, device=dev) for _ in range(L_net)]
         outs_ = [torch.empty(B, 16, 16, 64, device=dev) for _ in range(L_net)]
         acts_ = [K.ACT_RELU] * (L_net - 1) + [K.ACT_NONE]
@@ -530,7 +737,7 @@ def main():
 
         def net_pass(n):
             for _ in range(n):
-                be.convnet(xs, wts, bss, acts_, aux_, kinds_, outs_, alpha=0.05)
+                be.convnet(xs, wts, bss, acts_, aux_, kinds_, outs_, alpha=0.05, split=split)
 
         net_pass(10)
         torch.cuda.synchronize()
@@ -593,23 +800,54 @@ def main():
               "note": "algorithmic bytes: every distinct operand plane read once, every result written once (SURVEY.md 8d)"}
         del planes, outp
 
+    # ---- strong scaling: the global batch fixed at 512, 512 / N sequences per GPU
+    strong = None
+    if args.method != "dopri5" and not args.forward_only and not args.no_extras and 512 % world == 0:
+        try:
+            Bs = 512 // world
+            xs_, ys_ = synth(Bs, 777 + rank, dev)
+            from ode_rl_b200.harness import GraphedTrainStep
+            torch.manual_seed(0)
+            m2 = ODEConvGRUHarness(args.method, rtol=1e-3, atol=1e-4, device=dev).to(dev)
+            p2 = [p_ for p_ in m2.parameters()]
+            o2 = torch.optim.Adam(p2, lr=1e-3, capturable=True, fused=True)
+            b2 = parallel.GradBucket(p2)
+            g2 = GraphedTrainStep(m2, o2, torch.nn.functional.mse_loss, xs_, ys_, obs, tp,
+                                  grad_hook=(b2.allreduce if world > 1 else None), warmup=3)
+            for _ in range(3):
+                g2()
+            sec_s, _, _ = timed(lambda: g2(), max(4, args.steps // 2))
+            k_s = max(4, args.steps // 2)
+            strong = {"global_batch": 512, "batch_per_gpu": Bs, "ms_per_step": sec_s / k_s * 1e3,
+                      "value": 512 * T_OUT * k_s / sec_s, "unit": "frames/s", "scaling": "strong"}
+            del g2, m2, o2, b2
+            torch.cuda.empty_cache()
+        except Exception as e:                       # a sub-record must never cost the line
+            strong = {"error": repr(e)[:200]}
+
+    extras = {}
+    if rank == 0 and not args.no_extras and args.method != "dopri5" and not args.forward_only:
+        for name, fn in (("dopri5", lambda: sub_dopri5(dev)),
+                         ("small_batch", lambda: sub_small_batch(dev, with_cpu=not args.no_cpu_baseline and world == 1)),
+                         ("rk_kernels", lambda: sub_rk_kernels(dev, be, float(peaks.get("hbm_gbs", 6650.0))))):
+            try:
+                extras[name] = fn()
+            except Exception as e:
+                extras[name] = {"error": repr(e)[:300]}
+
     if rank == 0:
         cpu = None
         if not args.no_cpu_baseline and world == 1:
-            v, dt = time_cpu(args.method, args.cpu_batch, 2, 1)
+            cb = args.cpu_batch or 16
+            v, dt = time_cpu(args.method, cb, 2, 1)
             cpu = {"value": v, "unit": "frames/s", "cores": os.cpu_count() or 1, "kind": "port",
                    "sample": "2 timed training steps at batch %d (of the batch-%d workload) on the host cores; oracle/refmodel.py + "
-                             "restated torchdiffeq, torch CPU fp32, anomaly mode off" % (args.cpu_batch, B)}
+                             "restated torchdiffeq, torch CPU fp32, anomaly mode off" % (cb, B)}
         line = {"metric": "ODEConvGRU %s predicted frames/s" % ("forward" if args.forward_only else "training-step"), "value": value,
                 "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": sec / args.steps * 1e3,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32 (3xTF32 tensor-core convs, fp32 accumulate)",
                 "data": "synthetic",
-                "config": {"workload": "BASELINE configs[%s]: ODEConvGRU %s, %%s, batch %%d per GPU, "
-                                       "10 in / 10 out 64x64x1" % (("1" if args.method != "dopri5" else "2 (as a training step)") if not args.forward_only else
-                                                                   ("2" if args.method == "dopri5" else "1 (forward only)"),
-                                                                   "forward (no_grad)" if args.forward_only else "forward+backward+Adam") % (
-                                                                   args.method + (" fixed-step" if args.method != "dopri5" else
-                                                                                  " adaptive rtol=1e-3 atol=1e-4, device-resident controller"), B),
+                "config": {"workload": workload_name(args.method, args.forward_only, B),
                            "global_batch": B * world, "parallelism": "batch-sharded dp%d, NCCL flat-bucket gradient allreduce" % world,
                            "l2": "no explicit flush: the per-step working set (saved activations ~2 GB) is >> the 126 MB L2",
                            "cuda_graph": graphed is not None, "optimizer": "torch.optim.Adam(fused=%s)" % fused_adam},
@@ -617,7 +855,11 @@ def main():
                         "d2h_bytes_per_step": 4, "ms_per_step": sec_e / args.steps * 1e3,
                         "pipeline": "pinned host -> staging buffer on a copy stream, overlapping the previous step; staging -> step "
                                     "inputs device-to-device at the start of the step; loss read back (synchronising) every step"},
-                "gpu_launches": int(launches), "clocks": clk, "roofline": roof, "rk_stage": rk, "cpu_baseline": cpu}
+                "gpu_launches": int(launches), "clocks": clk, "roofline": roof, "rk_stage": rk, "cpu_baseline": cpu,
+                "strong_scaling": strong}
+        if rk is not None and "rk_kernels" in extras:
+            rk["K4_K5"] = extras.pop("rk_kernels")
+        line.update(extras)
         print_line(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -55,6 +55,9 @@ long long odex_launch_count(void);
  * SIMT layout: [tap][c_in][n_out] fp32.
  * TC layout  : per k-block (64-channel group, tap, 32-channel half): 2*n_out rows of 32 floats =
  *              [tf32 hi rows ; tf32 lo rows] (3xTF32 split), ready for SWIZZLE_128B TMA boxes.
+ * F16 layout (tc == 2): per k-block (64-channel group, tap): 2*n_out rows of 64 halves = [fp16 hi rows ; fp16 lo rows] of
+ *              w * s (lo scaled by 2^11; s = the power of two that puts max |w| in [2^12, 2^13)), followed by a 4-float
+ *              tail {1/s, max_n sum_k |w[n,k]|, max |w|, 0} the kernels use to scale / bound their fp16 operands.
  * Sizes are in floats.  Replaces: nothing in the reference (cuDNN/oneDNN do their own packing). */
 size_t odex_packed_weight_floats(int n_out, int c_in, int R, int tc);
 int odex_pack_weights(const float* w_oihw, int N, int C, int R, int dgrad, int tc, float* out, odex_stream_t s);
@@ -129,6 +132,9 @@ typedef struct odex_convnet_desc {
     float* out[ODEX_NET_MAX_LAYERS]; int ld_out[ODEX_NET_MAX_LAYERS];
     float alpha; const double* alpha_dev;
     const int* skip;
+    int split;                                  /* 0: w_tc are odex_pack_weights(tc = 1) blobs, 3xTF32 on tcgen05 kind::tf32;
+                                                   1: w_tc are odex_pack_weights(tc = 2) blobs, two-term fp16 split on kind::f16
+                                                      (same 22 significant bits per operand, twice the MMA rate) */
 } odex_convnet_desc;
 int odex_convnet(const odex_convnet_desc* d, odex_stream_t s);
 int odex_convnet_supported(const odex_convnet_desc* d);

@@ -5,7 +5,7 @@ modules/ConvGRUCell.py, helpers/utils.py:create_convnet); all compute runs in li
 include/odex.h).  There is no CPU or eager-PyTorch fallback.
 """
 from .modules import ConvGRUCell, DiffEqSolver, ODEConvGRUCell, ODEFunc, create_convnet  # noqa: F401
-from .ops import set_conv_impl  # noqa: F401
+from .ops import set_conv_impl, set_conv_split  # noqa: F401
 from ._lib import OdexError  # noqa: F401
 
-__all__ = ["DiffEqSolver", "ODEFunc", "ODEConvGRUCell", "ConvGRUCell", "create_convnet", "set_conv_impl", "OdexError"]
+__all__ = ["DiffEqSolver", "ODEFunc", "ODEConvGRUCell", "ConvGRUCell", "create_convnet", "set_conv_impl", "set_conv_split", "OdexError"]

@@ -59,6 +59,7 @@ class ConvNetDesc(C.Structure):
         ("out", C.c_void_p * NET_MAX_LAYERS), ("ld_out", C.c_int * NET_MAX_LAYERS),
         ("alpha", C.c_float), ("alpha_dev", C.c_void_p),
         ("skip", C.c_void_p),
+        ("split", C.c_int),
     ]
 
 

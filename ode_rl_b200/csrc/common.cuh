@@ -90,6 +90,9 @@ __device__ __forceinline__ T block_sum(T v, T* sh) {
     return sh[32];
 }
 
+// ReLU that propagates NaN like torch.relu / clamp_min (fmaxf(NaN, 0) would return 0 and swallow it)
+__device__ __forceinline__ float relu_nan(float v) { return v < 0.f ? 0.f : v; }
+
 __device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
 __device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
 // streaming variants for data touched once (bypass L1 allocation)

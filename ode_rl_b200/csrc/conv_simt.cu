@@ -5,6 +5,8 @@
 // gradient (conv_wgrad_kernel) is the reduction-over-pixels GEMM of the autograd backward.
 // Reference call sites replaced: helpers/utils.py:167-177 (3x3), modules/ConvGRUCell.py:41-43,47-49 (5x5),
 // modules/ODEConvGRUCell.py:27-30 (1x1) and their autograd backward.
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace odex {
@@ -56,6 +58,63 @@ __global__ void pack_tc_kernel(const float* __restrict__ w, int N, int C, int R,
     }
 }
 
+// F16-split layout (tc = 2): fp32 w = (hi + lo * 2^-11) / s with hi = fp16(w * s), lo = fp16((w * s - hi) * 2^11), s a power of
+// two chosen so that max |w| * s lies in [2^12, 2^13): 22 significant bits, the accuracy of the 3xTF32 split, on
+// tcgen05 kind::f16 at twice the tf32 rate.  k-block kb = grp * taps + tap covers the 64 channels [grp*64, +64) of tap:
+// 2*No rows of 64 halves (128 B): rows [0, No) = hi, [No, 2No) = lo.  A 4-float tail follows the rows:
+//   tail[0] = 1 / s,  tail[1] = G = max over output channels n of sum_{c,tap} |w[n, c, tap]|  (so |conv(x)[., n]| <= G * max|x|: the
+//   kernels size the fp16 scale of a layer's OUTPUT from it before that output exists),  tail[2] = max |w|.
+__global__ void pack_f16_stats_kernel(const float* __restrict__ w, int N, int C, int R, int dgrad, float* __restrict__ tail) {
+    const int No = dgrad ? C : N, Ci = dgrad ? N : C;
+    const int n = blockIdx.x;
+    if (n >= No) return;
+    __shared__ float sh[33];
+    float sum = 0.f, mx = 0.f;
+    const int per = Ci * R * R;
+    for (int i = threadIdx.x; i < per; i += blockDim.x) {
+        const int c = i / (R * R), t = i % (R * R);
+        const float v = fabsf(packed_src(w, N, C, R, dgrad, n, c, t / R, t % R));
+        sum += v;
+        mx = fmaxf(mx, v);
+    }
+    sum = block_sum(sum, sh);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((threadIdx.x & 31) == 0) atomicMax(reinterpret_cast<unsigned int*>(tail + 2), __float_as_uint(mx));
+    if (threadIdx.x == 0) atomicMax(reinterpret_cast<unsigned int*>(tail + 1), __float_as_uint(sum));
+}
+
+__device__ __forceinline__ float f16_pack_scale(float maxabs) {
+    // power of two s with maxabs * s in [2^12, 2^13); 1 for an all-zero (or non-finite) tensor
+    if (!(maxabs > 0.f) || !isfinite(maxabs)) return 1.f;
+    int e;
+    frexpf(maxabs, &e);                       // maxabs = m * 2^e, m in [0.5, 1)
+    return ldexpf(1.f, 13 - e);
+}
+
+__global__ void pack_f16_kernel(const float* __restrict__ w, int N, int C, int R, int dgrad, __half* __restrict__ out,
+                                float* __restrict__ tail) {
+    const int No = dgrad ? C : N, Ci = dgrad ? N : C;
+    const int taps = R * R;
+    const float s = f16_pack_scale(tail[2]);
+    const long total = static_cast<long>(Ci / 64) * taps * No * 64;
+    for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<long>(gridDim.x) * blockDim.x) {
+        const int kk = static_cast<int>(i & 63);
+        const int n = static_cast<int>((i >> 6) % No);
+        const long kb = (i >> 6) / No;
+        const int tap = static_cast<int>(kb % taps);
+        const int grp = static_cast<int>(kb / taps);
+        const float v = packed_src(w, N, C, R, dgrad, n, grp * 64 + kk, tap / R, tap % R) * s;
+        const __half hi = __float2half_rn(v);
+        const __half lo = __float2half_rn((v - __half2float(hi)) * 2048.f);
+        const long base = kb * (2L * No * 64);
+        out[base + static_cast<long>(n) * 64 + kk] = hi;
+        out[base + static_cast<long>(No + n) * 64 + kk] = lo;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) tail[0] = 1.f / s;
+}
+
 // ------------------------------------------------------------------------------------------------- forward
 struct SimtConvArgs {
     const float* x0; int ld0; int c0;
@@ -72,7 +131,7 @@ struct SimtConvArgs {
 };
 
 __device__ __forceinline__ float apply_act(float v, int act) {
-    if (act == ODEX_ACT_RELU) return fmaxf(v, 0.f);
+    if (act == ODEX_ACT_RELU) return relu_nan(v);
     if (act == ODEX_ACT_TANH) return tanhf(v);
     return v;
 }
@@ -334,6 +393,7 @@ using namespace odex;
 
 extern "C" size_t odex_packed_weight_floats(int n_out, int c_in, int R, int tc) {
     const size_t base = static_cast<size_t>(n_out) * c_in * R * R;
+    if (tc == 2) return base + 4;            // [hi ; lo] halves = base floats, + the 4-float tail
     return tc ? 2 * base : base;
 }
 
@@ -342,6 +402,18 @@ extern "C" int odex_pack_weights(const float* w, int N, int C, int R, int dgrad,
     if (!w || !out || N <= 0 || C <= 0 || R <= 0) return fail(ODEX_E_ARG, "pack_weights: bad argument");
     const long total = static_cast<long>(N) * C * R * R;
     const int blocks = static_cast<int>(std::min<long>((total + 255) / 256, 8L * kSMs));
+    if (tc == 2) {
+        const int Ci = dgrad ? N : C, No = dgrad ? C : N;
+        if (Ci % 64 != 0) return fail(ODEX_E_SHAPE, "pack_weights(f16): input channels %d not a multiple of 64", Ci);
+        if (!aligned16(out)) return fail(ODEX_E_ALIGN, "pack_weights(f16): out not 16-byte aligned");
+        float* tail = out + total;
+        cudaMemsetAsync(tail, 0, 4 * sizeof(float), s);
+        pack_f16_stats_kernel<<<No, 128, 0, s>>>(w, N, C, R, dgrad, tail);
+        int rc = launched("pack_f16_stats_kernel");
+        if (rc) return rc;
+        pack_f16_kernel<<<blocks, 256, 0, s>>>(w, N, C, R, dgrad, reinterpret_cast<__half*>(out), tail);
+        return launched("pack_f16_kernel");
+    }
     if (tc) {
         const int Ci = dgrad ? N : C;
         if (Ci % 64 != 0) return fail(ODEX_E_SHAPE, "pack_weights(tc): input channels %d not a multiple of 64", Ci);

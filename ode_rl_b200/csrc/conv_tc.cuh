@@ -292,7 +292,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                 for (int e = 0; e < 4; ++e) {
                     float t = __uint_as_float(vm[4 * j + e]) + __uint_as_float(vc[4 * j + e]);
                     if (ep.bias) t += __ldg(ep.bias + c0 + 4 * j + e);
-                    if (ep.act == 1) t = fmaxf(t, 0.f);
+                    if (ep.act == 1) t = relu_nan(t);
                     else if (ep.act == 2) t = tanhf(t);
                     v[e] = t;
                 }

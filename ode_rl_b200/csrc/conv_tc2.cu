@@ -293,7 +293,7 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
                     if (fast) {
                         if (ep.act == 1) {
 #pragma unroll
-                            for (int e = 0; e < 4; ++e) a[e] = fmaxf(a[e], 0.f);
+                            for (int e = 0; e < 4; ++e) a[e] = relu_nan(a[e]);
                         } else if (ep.act == 2) {
 #pragma unroll
                             for (int e = 0; e < 4; ++e) a[e] = tanhf(a[e]);
@@ -341,7 +341,7 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant_
                 v[0] += bv.x; v[1] += bv.y; v[2] += bv.z; v[3] += bv.w;
                 if (ep.act == 1) {
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) v[e] = fmaxf(v[e], 0.f);
+                    for (int e = 0; e < 4; ++e) v[e] = relu_nan(v[e]);
                 } else if (ep.act == 2) {
 #pragma unroll
                     for (int e = 0; e < 4; ++e) v[e] = tanhf(v[e]);

@@ -96,7 +96,7 @@ __device__ __forceinline__ void net_epilogue(uint32_t tmem_base, uint32_t lane_a
                 v[0] += bv[j].x; v[1] += bv[j].y; v[2] += bv[j].z; v[3] += bv[j].w;
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
-                    if (ACT == ODEX_ACT_RELU) v[e] = fmaxf(v[e], 0.f);
+                    if (ACT == ODEX_ACT_RELU) v[e] = relu_nan(v[e]);
                     if (ACT == ODEX_ACT_TANH) v[e] = tanhf(v[e]);
                     if (KIND == 1) v[e] = xa[j][e] > 0.f ? v[e] : 0.f;
                     if (KIND == 2) v[e] *= 1.f - xa[j][e] * xa[j][e];
@@ -405,13 +405,23 @@ static bool net_supported(const odex_convnet_desc* d) {
 
 }  // namespace odex
 
+namespace odex {
+bool convnet_f16_supported(const odex_convnet_desc* d);
+int launch_convnet_f16(const odex_convnet_desc* d, cudaStream_t s);
+}  // namespace odex
+
 using namespace odex;
 
-extern "C" int odex_convnet_supported(const odex_convnet_desc* d) { return net_supported(d) ? 1 : 0; }
+extern "C" int odex_convnet_supported(const odex_convnet_desc* d) {
+    if (d && d->split == 1) return convnet_f16_supported(d) ? 1 : 0;
+    return net_supported(d) ? 1 : 0;
+}
 
 extern "C" int odex_convnet(const odex_convnet_desc* d, odex_stream_t s_) {
     cudaStream_t s = static_cast<cudaStream_t>(s_);
     if (!d) return fail(ODEX_E_ARG, "convnet: null descriptor");
+    if (d->split == 1) return launch_convnet_f16(d, s);
+    if (d->split != 0) return fail(ODEX_E_ARG, "convnet: unknown operand split %d", d->split);
     if (!net_supported(d))
         return fail(ODEX_E_UNSUPPORTED, "convnet: shape not supported (B=%d HxW=%dx%d C=%d L=%d; needs 16x16, C=64, L<=%d, packed tc weights)",
                     d->B, d->H, d->W, d->C, d->L, kNetMaxL);

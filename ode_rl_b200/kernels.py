@@ -50,11 +50,12 @@ def _flat(t: torch.Tensor) -> int:
 class PackedConv:
     """Kernel-ready copies of one Conv2d weight: forward and data-gradient operators."""
 
-    __slots__ = ("N", "C", "R", "fwd_simt", "fwd_tc", "dgrad_simt", "dgrad_tc")
+    __slots__ = ("N", "C", "R", "fwd_simt", "fwd_tc", "dgrad_simt", "dgrad_tc", "fwd_f16", "dgrad_f16")
 
     def __init__(self, N, Cin, R):
         self.N, self.C, self.R = N, Cin, R
         self.fwd_simt = self.fwd_tc = self.dgrad_simt = self.dgrad_tc = None
+        self.fwd_f16 = self.dgrad_f16 = None         # two-term fp16 split (odex_pack_weights tc = 2)
 
 
 def tc_shape_ok(N: int, c0: int, c1: int, H: int, W: int, R: int) -> bool:
@@ -84,16 +85,18 @@ class Backend:
             raise _lib.OdexError("ode_rl_b200 runs on CUDA tensors only (got %s); there is no CPU fallback" % t.device)
 
     # ------------------------------------------------------------------ weights
-    def pack_weights(self, w: torch.Tensor, dgrad: bool, tc: bool) -> torch.Tensor:
-        """odex_pack_weights: OIHW fp32 -> SIMT [tap][c][n] or TC (3xTF32 hi/lo k-blocks) layout."""
+    def pack_weights(self, w: torch.Tensor, dgrad: bool, tc) -> torch.Tensor:
+        """odex_pack_weights: OIHW fp32 -> SIMT [tap][c][n] (tc = 0 / False), TC 3xTF32 hi/lo k-blocks (1 / True) or the
+        two-term fp16 split with its scale tail (2)."""
         self.require(w)
         w = w.detach()
         assert w.dtype == torch.float32 and w.is_contiguous() and w.dim() == 4 and w.shape[2] == w.shape[3]
         N, Cc, R, _ = w.shape
         n_out, c_in = (Cc, N) if dgrad else (N, Cc)
-        nfl = self.lib.odex_packed_weight_floats(n_out, c_in, R, 1 if tc else 0)
+        mode = int(tc)
+        nfl = self.lib.odex_packed_weight_floats(n_out, c_in, R, mode)
         out = torch.empty(nfl, dtype=torch.float32, device=w.device)
-        _lib.check(self.lib.odex_pack_weights(w.data_ptr(), N, Cc, R, 1 if dgrad else 0, 1 if tc else 0,
+        _lib.check(self.lib.odex_pack_weights(w.data_ptr(), N, Cc, R, 1 if dgrad else 0, mode,
                                               out.data_ptr(), _stream()), "odex_pack_weights")
         return out
 
@@ -134,8 +137,9 @@ class Backend:
             _lib.check(self.lib.odex_conv2d(C.byref(d), _stream()), "odex_conv2d")
         return out
 
-    def _convnet_desc(self, x, w_tc, bias, act, aux, aux_kind, out, alpha, alpha_dev, skip):
+    def _convnet_desc(self, x, w_tc, bias, act, aux, aux_kind, out, alpha, alpha_dev, skip, split=0):
         d = _lib.ConvNetDesc()
+        d.split = int(split)
         B, H, W, Cc = x.shape
         d.x, d.ldx = _rows(x)
         d.B, d.H, d.W, d.C, d.L = B, H, W, Cc, len(w_tc)
@@ -164,11 +168,12 @@ class Backend:
     def convnet(self, x: torch.Tensor, w_tc: Sequence[torch.Tensor], bias: Sequence[Optional[torch.Tensor]],
                 act: Sequence[int], aux: Sequence[Optional[torch.Tensor]], aux_kind: Sequence[int],
                 out: Sequence[Optional[torch.Tensor]], alpha: float = 1.0, alpha_dev: Optional[torch.Tensor] = None,
-                skip: Optional[torch.Tensor] = None) -> None:
+                skip: Optional[torch.Tensor] = None, split: int = 0) -> None:
         """odex_convnet: the whole conv chain in one launch; layer l: v = act(conv(a_l) + bias), v *= act'(aux) (kind 1/2)
-        or v = aux + alpha * v (kind 3), stored to out[l] when given (out[-1] required)."""
+        or v = aux + alpha * v (kind 3), stored to out[l] when given (out[-1] required).  split: 0 = w_tc packed with tc = 1
+        (3xTF32), 1 = packed with tc = 2 (two-term fp16 split on kind::f16)."""
         self.require(x)
-        d = self._convnet_desc(x, w_tc, bias, act, aux, aux_kind, out, alpha, alpha_dev, skip)
+        d = self._convnet_desc(x, w_tc, bias, act, aux, aux_kind, out, alpha, alpha_dev, skip, split)
         _lib.check(self.lib.odex_convnet(C.byref(d), _stream()), "odex_convnet")
 
     # ------------------------------------------------------------------ decoder tail (LeakyReLU + ConvTranspose2d(C,1,4,2,1))

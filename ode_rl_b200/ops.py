@@ -25,6 +25,18 @@ from .kernels import ACT_NONE, ACT_RELU, ACT_TANH, CONV_AUTO, CONV_SIMT, CONV_TC
 CONV_IMPL = os.environ.get("ODEX_CONV_IMPL", "auto").lower()
 
 
+# Operand split of the fused conv chain (odex_convnet): "f16" = two-term fp16 split on tcgen05 kind::f16 (22 significant bits
+# per operand at twice the tf32 MMA rate), "tf32" = 3xTF32 on kind::tf32.
+CONV_SPLIT = os.environ.get("ODEX_SPLIT", "f16").lower()
+
+
+def set_conv_split(name: str) -> str:
+    global CONV_SPLIT
+    assert name in ("f16", "tf32")
+    prev, CONV_SPLIT = CONV_SPLIT, name
+    return prev
+
+
 def set_conv_impl(name: str) -> str:
     global CONV_IMPL
     assert name in ("auto", "simt", "tc")
@@ -179,6 +191,23 @@ class _PackCache:
         self.key = None
         self.pk: Optional[PackedConv] = None
         self.shape_key = None
+        self.key16 = None
+        self.pk16: Optional[PackedConv] = None
+
+    def get_f16(self, need_dgrad: bool) -> PackedConv:
+        """The two-term fp16 split copies (odex_pack_weights tc = 2) the fused chain reads when CONV_SPLIT == 'f16'."""
+        w = self.conv.weight
+        key = (w.data_ptr(), w._version, w.device)
+        if self.pk16 is None or key != self.key16:
+            self.pk16 = PackedConv(w.shape[0], w.shape[1], w.shape[2])
+            self.key16 = key
+        pk = self.pk16
+        be = K.backend()
+        if pk.fwd_f16 is None:
+            pk.fwd_f16 = be.pack_weights(w, dgrad=False, tc=2)
+        if need_dgrad and pk.dgrad_f16 is None:
+            pk.dgrad_f16 = be.pack_weights(w, dgrad=True, tc=2)
+        return pk
 
     def get(self, H: int, W: int, c0: int, c1: int, need_dgrad: bool) -> PackedConv:
         w = self.conv.weight
@@ -207,6 +236,8 @@ class _PackCache:
     def invalidate(self):
         self.key = None
         self.pk = None
+        self.key16 = None
+        self.pk16 = None
 
 
 def _check_conv(conv: nn.Conv2d, what: str) -> int:
@@ -290,7 +321,11 @@ class ConvNetOp:
         saved = [x] if save else None
         a = x
         if self._fused(be, x):
-            pks = [self.caches[l].get(H, W, 64, 0, need_dgrad or save) for l in range(L)]
+            f16 = CONV_SPLIT == "f16"
+            if f16:
+                wts = [self.caches[l].get_f16(False).fwd_f16 for l in range(L)]
+            else:
+                wts = [self.caches[l].get(H, W, 64, 0, need_dgrad or save).fwd_tc for l in range(L)]
             last_act = self.layers[-1][1]
             fuse = res is not None and last_act == ACT_NONE
             outs: List[Optional[torch.Tensor]] = [None] * L
@@ -305,8 +340,9 @@ class ConvNetOp:
             kinds = [0] * L
             if fuse:
                 aux[L - 1], kinds[L - 1] = res, 3
-            be.convnet(x, [pk.fwd_tc for pk in pks], [c.bias for c, _ in self.layers], [act for _, act in self.layers],
-                       aux, kinds, outs, alpha=alpha if fuse else 1.0, alpha_dev=alpha_dev if fuse else None, skip=skip)
+            be.convnet(x, wts, [c.bias for c, _ in self.layers], [act for _, act in self.layers],
+                       aux, kinds, outs, alpha=alpha if fuse else 1.0, alpha_dev=alpha_dev if fuse else None, skip=skip,
+                       split=1 if f16 else 0)
             if save:
                 saved.extend(outs[:L - 1])
                 if last_act != ACT_NONE:
@@ -364,7 +400,11 @@ class ConvNetOp:
             # the data-gradient chain d_{l-1} = conv_l^T(d_l) * act'(a_l) in one launch, then the weight gradients
             lo = 0 if need_dx else 1                 # lowest layer whose input gradient is needed
             ls = list(range(L - 1, lo - 1, -1))      # chain position k handles layer ls[k]
-            pks = [self.caches[l].get(H, W, 64, 0, True) for l in ls]
+            f16 = CONV_SPLIT == "f16"
+            if f16:
+                wts = [self.caches[l].get_f16(True).dgrad_f16 for l in ls]
+            else:
+                wts = [self.caches[l].get(H, W, 64, 0, True).dgrad_tc for l in ls]
             aux: List[Optional[torch.Tensor]] = []
             kinds = []
             outs: List[Optional[torch.Tensor]] = []
@@ -376,7 +416,7 @@ class ConvNetOp:
                 else:
                     aux.append(res); kinds.append(3 if res is not None else 0)
                     outs.append(out if out is not None else torch.empty((B, H, W, 64), dtype=torch.float32, device=x.device))
-            be.convnet(d, [pk.dgrad_tc for pk in pks], [None] * len(ls), [ACT_NONE] * len(ls), aux, kinds, outs, alpha=1.0)
+            be.convnet(d, wts, [None] * len(ls), [ACT_NONE] * len(ls), aux, kinds, outs, alpha=1.0, split=1 if f16 else 0)
             grads = {L - 1: d}
             for k, l in enumerate(ls):
                 grads[l - 1] = outs[k]               # outs[k] = gradient w.r.t. the input of layer l = d_{l-1}

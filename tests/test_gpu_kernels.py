@@ -243,9 +243,10 @@ def test_lincomb_actbwd_layout(be, fb):
     assert torch.equal(back.cpu(), x)
 
 
+@pytest.mark.parametrize("split", [0, 1], ids=["tf32", "f16"])
 @pytest.mark.parametrize("act", [ACT_RELU, ACT_TANH])
 @pytest.mark.parametrize("L,B", [(5, 3), (1, 2), (6, 150)])
-def test_convnet_fused_chain_matches_layerwise(be, L, B, act):
+def test_convnet_fused_chain_matches_layerwise(be, L, B, act, split):
     """odex_convnet (the whole 64->64 3x3 chain on a shared-memory-resident image) against the exact-fp32 FFMA convolution
     called layer by layer: forward mode (bias, act, saved activations, fused residual with a device-side alpha) and
     data-gradient mode (dgrad-packed weights, act' masks from saved activations, residual on the last link)."""
@@ -266,8 +267,8 @@ def test_convnet_fused_chain_matches_layerwise(be, L, B, act):
         ref.append(o)
         a = o
     outs = [torch.empty(B, 16, 16, 64, device="cuda") if (l % 2 == 1 or l == L - 1) else None for l in range(L)]
-    be.convnet(x, [be.pack_weights(w, False, True) for w in ws], bs, acts, [None] * (L - 1) + [res], [0] * (L - 1) + [3], outs,
-               alpha=2.0, alpha_dev=alpha_dev)
+    be.convnet(x, [be.pack_weights(w, False, 1 + split) for w in ws], bs, acts, [None] * (L - 1) + [res], [0] * (L - 1) + [3], outs,
+               alpha=2.0, alpha_dev=alpha_dev, split=split)
     torch.cuda.synchronize()
     for l in range(L):
         if outs[l] is not None:
@@ -284,20 +285,56 @@ def test_convnet_fused_chain_matches_layerwise(be, L, B, act):
         ref.append(o)
         d = o
     outs = [torch.empty(B, 16, 16, 64, device="cuda") for _ in range(L)]
-    be.convnet(dy, [be.pack_weights(w, True, True) for w in ws], [None] * L, [ACT_NONE] * L,
-               masks[:L - 1] + [res], [act] * (L - 1) + [3], outs)
+    be.convnet(dy, [be.pack_weights(w, True, 1 + split) for w in ws], [None] * L, [ACT_NONE] * L,
+               masks[:L - 1] + [res], [act] * (L - 1) + [3], outs, split=split)
     torch.cuda.synchronize()
     for k in range(L):
         assert rel_err(outs[k], ref[k]) < 1e-5, "dgrad link %d" % k
     # ---- skip flag: nothing is written
     skip = torch.ones(1, dtype=torch.int32, device="cuda")
     o2 = [None] * (L - 1) + [torch.full((B, 16, 16, 64), 7.0, device="cuda")]
-    be.convnet(x, [be.pack_weights(w, False, True) for w in ws], bs, acts, [None] * L, [0] * L, o2, skip=skip)
+    be.convnet(x, [be.pack_weights(w, False, 1 + split) for w in ws], bs, acts, [None] * L, [0] * L, o2, skip=skip, split=split)
     torch.cuda.synchronize()
     assert float((o2[-1] - 7.0).abs().max()) == 0.0
 
 
-def test_convnet_fused_chain_is_deterministic(be):
+@pytest.mark.parametrize("scale", [1e-12, 1e-6, 1.0, 1e4, 1e12])
+def test_convnet_f16_split_holds_fp32_accuracy_at_any_magnitude(be, scale):
+    """The fp16 operands of the kind::f16 chain carry per-image / per-layer power-of-two scales sized from measured maxima and
+    a rigorous bound (csrc/convnet_f16.cu): the result must hold the 1e-5 bar whatever the magnitude of the data -- tiny
+    gradients (1e-12: everything would be an fp16 zero unscaled), huge states (1e12: everything would overflow), images of
+    very different magnitude in one batch, an all-zero image, heavy-tailed values and large weights."""
+    torch.manual_seed(3)
+    B, L = 6, 4
+    x = torch.randn(B, 16, 16, 64, device="cuda") * scale
+    x[1] *= 1e-5                                    # per-image scales: a faint image next to a bright one
+    x[2] = 0.0                                      # h_0 = 0 of the encoder recurrence
+    x[3, 5, 5, 7] = 3e3 * scale                     # one outlier sets the scale; the rest sits 2^-11 below it
+    ws = [torch.randn(64, 64, 3, 3, device="cuda") / 24.0 * (30.0 if l == 1 else 1.0) for l in range(L)]
+    bs = [torch.randn(64, device="cuda") * 0.1 * scale for l in range(L)]
+    acts = [ACT_RELU] * (L - 1) + [ACT_NONE]
+    ref, a = [], x
+    for l in range(L):
+        o = torch.empty_like(x)
+        be.conv2d(a, None, be.pack_weights(ws[l], False, False), None, 64, 3, bs[l], acts[l], o, impl=CONV_SIMT)
+        ref.append(o)
+        a = o
+    outs = [torch.empty_like(x) for _ in range(L)]
+    be.convnet(x, [be.pack_weights(w, False, 2) for w in ws], bs, acts, [None] * L, [0] * L, outs, split=1)
+    torch.cuda.synchronize()
+    for l in range(L):
+        assert bool(torch.isfinite(outs[l]).all()), l
+        for b in range(B):                          # per image: the faint one must be as accurate as the bright one
+            assert rel_err(outs[l][b], ref[l][b]) < 1e-5, (l, b, rel_err(outs[l][b], ref[l][b]))
+    # non-finite inputs propagate instead of being scaled away
+    x[0, 0, 0, 0] = float("nan")
+    be.convnet(x, [be.pack_weights(w, False, 2) for w in ws], bs, acts, [None] * L, [0] * L, outs, split=1)
+    torch.cuda.synchronize()
+    assert bool(torch.isnan(outs[-1][0]).any()) and bool(torch.isfinite(outs[-1][4]).all())
+
+
+@pytest.mark.parametrize("split", [0, 1], ids=["tf32", "f16"])
+def test_convnet_fused_chain_is_deterministic(be, split):
     """The fused chain recycles its shared-memory planes between layers (operands overwritten in place, TMA loads into
     retired planes, TMA stores reading planes the next layer is already using).  A missing fence or barrier would show up
     as run-to-run differences: 40 launches on the same input, forward and data-gradient form, must agree bit for bit, with
@@ -305,8 +342,8 @@ def test_convnet_fused_chain_is_deterministic(be):
     torch.manual_seed(21)
     B, L = 148 * 2 + 5, 5
     x = torch.randn(B, 16, 16, 64, device="cuda")
-    ws_f = [be.pack_weights(torch.randn(64, 64, 3, 3, device="cuda") / 24.0, False, True) for _ in range(L)]
-    ws_d = [be.pack_weights(torch.randn(64, 64, 3, 3, device="cuda") / 24.0, True, True) for _ in range(L)]
+    ws_f = [be.pack_weights(torch.randn(64, 64, 3, 3, device="cuda") / 24.0, False, 1 + split) for _ in range(L)]
+    ws_d = [be.pack_weights(torch.randn(64, 64, 3, 3, device="cuda") / 24.0, True, 1 + split) for _ in range(L)]
     bs = [torch.randn(64, device="cuda") * 0.1 for _ in range(L)]
     masks = [torch.randn(B, 16, 16, 64, device="cuda") for _ in range(L)]
     junk = torch.randn(B, 16, 16, 64, device="cuda")
@@ -314,8 +351,8 @@ def test_convnet_fused_chain_is_deterministic(be):
     for it in range(40):
         outs_f = [torch.empty_like(x) for _ in range(L)]
         outs_d = [torch.empty_like(x) for _ in range(L)]
-        be.convnet(x, ws_f, bs, [ACT_RELU] * (L - 1) + [ACT_NONE], [None] * (L - 1) + [x], [0] * (L - 1) + [3], outs_f, alpha=0.1)
-        be.convnet(outs_f[-1], ws_d, [None] * L, [ACT_NONE] * L, masks[:L - 1] + [x], [1] * (L - 1) + [3], outs_d)
+        be.convnet(x, ws_f, bs, [ACT_RELU] * (L - 1) + [ACT_NONE], [None] * (L - 1) + [x], [0] * (L - 1) + [3], outs_f, alpha=0.1, split=split)
+        be.convnet(outs_f[-1], ws_d, [None] * L, [ACT_NONE] * L, masks[:L - 1] + [x], [1] * (L - 1) + [3], outs_d, split=split)
         be.lincomb(junk, [junk, outs_d[-1]], [0.5, 0.5])
         torch.cuda.synchronize()
         cur = [o.clone() for o in outs_f + outs_d]

@@ -367,15 +367,15 @@ def test_encode_stem_autograd_wiring(fake_backend):
 
 
 # ---- round-2 robustness items (VERDICT r1 weak #12 / missing #7) ------------------------------------------
-def _robustness_cases(odex, device):
-    """Runs on the fake backend here and on the CUDA kernels in tests/test_gpu_parity.py."""
+def _robustness_cases(odex, device, C=32, hw=(8, 16)):
+    """Runs on the fake backend here and on the CUDA kernels in tests/test_gpu_parity.py (C = 64, 16 x 16: kernel shapes)."""
     import gc
     import numpy as np
 
-    f = make_ode_func(odex, C=32, n_units=32, scale=2.0).to(device)
-    cell = odex.ODEConvGRUCell(f, None, (8, 16), 32).to(device)
+    f = make_ode_func(odex, C=C, n_units=C, scale=2.0).to(device)
+    cell = odex.ODEConvGRUCell(f, None, hw, C).to(device)
     torch.manual_seed(5)
-    x = torch.randn(4, 2, 32, 8, 16, device=device)
+    x = torch.randn(4, 2, C, *hw, device=device)
     sd = {k: v.detach().cpu().clone() for k, v in cell.state_dict().items()}
 
     # (1) the encoder step sizes follow the VALUES of `timesteps`: a second tensor of the same shape (allocated where the
@@ -403,7 +403,7 @@ def _robustness_cases(odex, device):
 
     # (3) a second backward through the same graph fails loudly instead of with an AttributeError deep inside
     solver = odex.DiffEqSolver(f, "rk4")
-    z0 = torch.randn(2, 32, 8, 16, device=device, requires_grad=True)
+    z0 = torch.randn(2, C, *hw, device=device, requires_grad=True)
     _, tp = timesteps(3, 3)
     for make in (lambda: solver(z0, tp.to(device)), lambda: cell(x.clone().requires_grad_(True), irregular.to(device))[0],
                  lambda: odex.DiffEqSolver(f, "dopri5", odeint_rtol=1e-3, odeint_atol=1e-4)(z0, tp.to(device))):
