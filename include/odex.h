@@ -139,6 +139,39 @@ typedef struct odex_convnet_desc {
 int odex_convnet(const odex_convnet_desc* d, odex_stream_t s);
 int odex_convnet_supported(const odex_convnet_desc* d);
 
+/* ------------------------------------------------------------------------------------------------ image-resident conv + ConvGRU gates
+ * Stride-1 "same" convolution (R = 3 or 5) over 16x16 images with one or two 64-channel sources (torch.cat((x, h), 1) folded in
+ * as two K ranges) and N output channels (multiple of 64), on tcgen05 kind::f16 with the two-term fp16 operand split of
+ * odex_convnet(split = 1); one CTA = one image x 64 output channels, which at 16x16 holds whole GroupNorm groups, so the
+ * ConvGRU gate math rides in the epilogue (north_star (c)):
+ *   ODEX_C16_PLAIN      v = act(acc + bias); aux_kind 1 / 2: v *= relu' / tanh'(aux); 3: v = aux + alpha * v; out[p*ldo + n] = v.
+ *                       Replaces odex_conv2d at these shapes (the ConvGRU data-gradient convolutions among them).
+ *   ODEX_C16_GRU_GATES  N = 2C: g = acc + bias; a = sigmoid(GroupNorm(g; 32-channel groups, gamma, beta, eps)); channels [0, C):
+ *                       z[p*C + c] = a; channels [C, 2C): rh[p*C + c - C] = a * h[p*ldh + c - C].  g_raw (nullable) receives g
+ *                       [B,256,2C] for the backward; stats[b][group] = (mean, rstd).
+ *                       Replaces conv_gates of modules/ConvGRUCell.py:40-44 + split / sigmoid / r*h of :72-79.
+ *   ODEX_C16_GRU_OUT    N = C: c = tanh(GroupNorm(acc + bias)); hnew[p*ld_hnew + n] = (1 - z_in) * h + z_in * c; cand / g_raw
+ *                       (nullable) receive c and the pre-norm convolution for the backward.
+ *                       Replaces conv_can of modules/ConvGRUCell.py:46-50 + tanh / blend of :80-82.
+ * w_f16 = odex_pack_weights(tc = 2) of the [N][64 * nsrc][R][R] operator. */
+enum { ODEX_C16_PLAIN = 0, ODEX_C16_GRU_GATES = 1, ODEX_C16_GRU_OUT = 2 };
+typedef struct odex_conv16_desc {
+    const float* x0; int ld0;
+    const float* x1; int ld1;               /* NULL: one source */
+    int B, R, N;
+    const float* w_f16;
+    const float* bias;                      /* [N] or NULL */
+    int mode;
+    int act; const float* aux; int ld_aux; int aux_kind; float alpha; const double* alpha_dev;
+    float* out; int ldo;
+    const float* gamma; const float* beta; float eps;
+    const float* h; int ldh; const float* z_in;
+    float* z; float* rh; float* hnew; int ld_hnew; float* cand; float* g_raw; float* stats;
+    const int* skip;
+} odex_conv16_desc;
+int odex_conv16(const odex_conv16_desc* d, odex_stream_t s);
+int odex_conv16_supported(const odex_conv16_desc* d);
+
 /* ------------------------------------------------------------------------------------------------ decoder tail
  * LeakyReLU(slope) -> ConvTranspose2d(C, 1, 4, 2, 1) of ConvDecode (models/ODEConvGRU.py:122-140, the activation and the
  * last layer), reading the PHASE-BLOCKED pre-activation output of the first transposed convolution as the tensor-core

@@ -63,6 +63,30 @@ class ConvNetDesc(C.Structure):
     ]
 
 
+C16_PLAIN, C16_GRU_GATES, C16_GRU_OUT = 0, 1, 2
+
+
+class Conv16Desc(C.Structure):
+    """struct odex_conv16_desc (include/odex.h)."""
+
+    _fields_ = [
+        ("x0", C.c_void_p), ("ld0", C.c_int),
+        ("x1", C.c_void_p), ("ld1", C.c_int),
+        ("B", C.c_int), ("R", C.c_int), ("N", C.c_int),
+        ("w_f16", C.c_void_p),
+        ("bias", C.c_void_p),
+        ("mode", C.c_int),
+        ("act", C.c_int), ("aux", C.c_void_p), ("ld_aux", C.c_int), ("aux_kind", C.c_int), ("alpha", C.c_float),
+        ("alpha_dev", C.c_void_p),
+        ("out", C.c_void_p), ("ldo", C.c_int),
+        ("gamma", C.c_void_p), ("beta", C.c_void_p), ("eps", C.c_float),
+        ("h", C.c_void_p), ("ldh", C.c_int), ("z_in", C.c_void_p),
+        ("z", C.c_void_p), ("rh", C.c_void_p), ("hnew", C.c_void_p), ("ld_hnew", C.c_int), ("cand", C.c_void_p),
+        ("g_raw", C.c_void_p), ("stats", C.c_void_p),
+        ("skip", C.c_void_p),
+    ]
+
+
 class DopriState(C.Structure):
     """struct odex_dopri_state (include/odex.h) -- the host reads a copy of it back once per forward."""
 
@@ -99,6 +123,8 @@ SIGNATURES = {
     "odex_conv2d_repeat": (_i, [C.POINTER(ConvDesc), _i, _vp]),
     "odex_convnet": (_i, [C.POINTER(ConvNetDesc), _vp]),
     "odex_convnet_supported": (_i, [C.POINTER(ConvNetDesc)]),
+    "odex_conv16": (_i, [C.POINTER(Conv16Desc), _vp]),
+    "odex_conv16_supported": (_i, [C.POINTER(Conv16Desc)]),
     "odex_decode_tail_fwd": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _f, _vp, _vp]),
     "odex_decode_tail_bwd": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _f, _vp, _vp, _vp, _vp]),
     "odex_encode_stem_fwd": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _f, _vp, _vp]),

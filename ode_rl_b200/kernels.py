@@ -176,6 +176,74 @@ class Backend:
         d = self._convnet_desc(x, w_tc, bias, act, aux, aux_kind, out, alpha, alpha_dev, skip, split)
         _lib.check(self.lib.odex_convnet(C.byref(d), _stream()), "odex_convnet")
 
+    # ------------------------------------------------------------------ image-resident conv (+ fused ConvGRU gates), kind::f16
+    @staticmethod
+    def conv16_shape_ok(x0: torch.Tensor, x1: Optional[torch.Tensor], N: int, R: int) -> bool:
+        """Shape test of odex_conv16: 16x16 images, one or two 64-channel sources, N % 64 == 0, R in {3, 5}."""
+        if x0.dim() != 4 or tuple(x0.shape[1:]) != (16, 16, 64) or x0.shape[0] == 0 or R not in (3, 5) or N % 64 != 0:
+            return False
+        if x1 is not None and tuple(x1.shape) != tuple(x0.shape):
+            return False
+        return os.environ.get("ODEX_NO_CONV16") is None
+
+    def _conv16_desc(self, x0, x1, w_f16, N, R, bias, skip):
+        d = _lib.Conv16Desc()
+        d.x0, d.ld0 = _rows(x0)
+        if x1 is not None:
+            d.x1, d.ld1 = _rows(x1)
+        d.B, d.R, d.N = x0.shape[0], R, N
+        d.w_f16 = _ptr(w_f16)
+        d.bias = _ptr(bias.detach()) if bias is not None else None
+        d.skip = _ptr(skip)
+        return d
+
+    def conv16(self, x0: torch.Tensor, x1: Optional[torch.Tensor], w_f16: torch.Tensor, N: int, R: int,
+               bias: Optional[torch.Tensor], act: int, out: torch.Tensor, aux: Optional[torch.Tensor] = None, aux_kind: int = 0,
+               alpha: float = 1.0, alpha_dev: Optional[torch.Tensor] = None, skip: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """odex_conv16(PLAIN): out = act(conv(cat(x0, x1)) + bias), then * act'(aux) (aux_kind 1 / 2) or aux + alpha * v (3)."""
+        self.require(x0)
+        d = self._conv16_desc(x0, x1, w_f16, N, R, bias, skip)
+        d.mode = _lib.C16_PLAIN
+        d.act = act
+        if aux is not None and aux_kind:
+            d.aux, d.ld_aux = _rows(aux)
+            d.aux_kind = aux_kind
+        d.alpha = float(alpha)
+        d.alpha_dev = _ptr(alpha_dev)
+        assert tuple(out.shape) == (x0.shape[0], 16, 16, N)
+        d.out, d.ldo = _rows(out)
+        _lib.check(self.lib.odex_conv16(C.byref(d), _stream()), "odex_conv16")
+        return out
+
+    def conv16_gru_gates(self, x: torch.Tensor, h: torch.Tensor, w_f16: torch.Tensor, R: int, bias, gamma, beta, eps: float,
+                         z: torch.Tensor, rh: torch.Tensor, stats: torch.Tensor, g_raw: Optional[torch.Tensor] = None) -> None:
+        """odex_conv16(GRU_GATES): z, r = sigmoid(GroupNorm(conv(cat(x, h)) + bias)); rh = r * h; g_raw <- the pre-norm conv."""
+        self.require(x)
+        Cc = h.shape[3]
+        d = self._conv16_desc(x, h, w_f16, 2 * Cc, R, bias, None)
+        d.mode = _lib.C16_GRU_GATES
+        d.gamma, d.beta, d.eps = gamma.detach().data_ptr(), beta.detach().data_ptr(), float(eps)
+        d.h, d.ldh = _rows(h)
+        assert z.is_contiguous() and rh.is_contiguous() and (g_raw is None or g_raw.is_contiguous())
+        d.z, d.rh, d.stats, d.g_raw = z.data_ptr(), rh.data_ptr(), stats.data_ptr(), _ptr(g_raw)
+        _lib.check(self.lib.odex_conv16(C.byref(d), _stream()), "odex_conv16")
+
+    def conv16_gru_out(self, x: torch.Tensor, rh: torch.Tensor, w_f16: torch.Tensor, R: int, bias, gamma, beta, eps: float,
+                       z: torch.Tensor, h: torch.Tensor, hnew: torch.Tensor, stats: torch.Tensor,
+                       cand: Optional[torch.Tensor] = None, cpre: Optional[torch.Tensor] = None) -> None:
+        """odex_conv16(GRU_OUT): c = tanh(GroupNorm(conv(cat(x, rh)) + bias)); hnew = (1 - z) * h + z * c."""
+        self.require(x)
+        Cc = h.shape[3]
+        d = self._conv16_desc(x, rh, w_f16, Cc, R, bias, None)
+        d.mode = _lib.C16_GRU_OUT
+        d.gamma, d.beta, d.eps = gamma.detach().data_ptr(), beta.detach().data_ptr(), float(eps)
+        d.h, d.ldh = _rows(h)
+        assert z.is_contiguous() and (cand is None or cand.is_contiguous()) and (cpre is None or cpre.is_contiguous())
+        d.z_in = z.data_ptr()
+        d.hnew, d.ld_hnew = _rows(hnew)
+        d.cand, d.g_raw, d.stats = _ptr(cand), _ptr(cpre), stats.data_ptr()
+        _lib.check(self.lib.odex_conv16(C.byref(d), _stream()), "odex_conv16")
+
     # ------------------------------------------------------------------ decoder tail (LeakyReLU + ConvTranspose2d(C,1,4,2,1))
     @staticmethod
     def decode_tail_supported(p: torch.Tensor) -> bool:

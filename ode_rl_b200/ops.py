@@ -468,12 +468,36 @@ class GruOp:
     def flops(self, B: int, H: int, W: int) -> int:
         return 2 * B * H * W * (self.Cx + self.C) * self.R * self.R * 3 * self.C
 
+    def _fused16(self, be, x: torch.Tensor, h: torch.Tensor) -> bool:
+        """True when the step runs on odex_conv16 (16x16 latents, 64-channel input and hidden state, 3x3 / 5x5, f16 split)."""
+        return (CONV_SPLIT == "f16" and CONV_IMPL != "simt" and hasattr(be, "conv16") and self.C == 64 and self.Cx == 64
+                and be.conv16_shape_ok(x, h, 2 * self.C, self.R))
+
     def fwd(self, x: torch.Tensor, h: torch.Tensor, save: bool = False, out: Optional[torch.Tensor] = None):
         be = K.backend()
         B, H, W, Cx = x.shape
         C, R = self.C, self.R
         dev = x.device
         f32 = torch.float32
+        if self._fused16(be, x, h):
+            # K2 fused (north_star (c)): each convolution and the gate math behind it in ONE launch -- GroupNorm statistics,
+            # sigmoid / r*h and tanh / blend ride in the epilogue of the kind::f16 image-resident convolution
+            wg = self.pc_g.get_f16(save).fwd_f16
+            wc = self.pc_c.get_f16(save).fwd_f16
+            z = torch.empty((B, H, W, C), dtype=f32, device=dev)
+            rh = torch.empty((B, H, W, C), dtype=f32, device=dev)
+            st_g = torch.empty((B * (2 * C // 32) * 2,), dtype=f32, device=dev)
+            st_c = torch.empty((B * (C // 32) * 2,), dtype=f32, device=dev)
+            g = torch.empty((B, H, W, 2 * C), dtype=f32, device=dev) if save else None
+            be.conv16_gru_gates(x, h, wg, R, self.cg.bias, self.gn_g.weight, self.gn_g.bias, self.gn_g.eps, z, rh, st_g, g_raw=g)
+            hnew = out if out is not None else torch.empty((B, H, W, C), dtype=f32, device=dev)
+            cpre = torch.empty((B, H, W, C), dtype=f32, device=dev) if save else None
+            cand = torch.empty((B, H, W, C), dtype=f32, device=dev) if save else None
+            be.conv16_gru_out(x, rh, wc, R, self.cc.bias, self.gn_c.weight, self.gn_c.bias, self.gn_c.eps, z, h, hnew, st_c,
+                              cand=cand, cpre=cpre)
+            if save:
+                return hnew, (x, h, g, z, rh, st_g, cpre, cand, st_c)
+            return hnew
         pg = self.pc_g.get(H, W, Cx, C, save)
         g = torch.empty((B, H, W, 2 * C), dtype=f32, device=dev)
         be.conv2d(x, h, pg.fwd_simt, pg.fwd_tc, 2 * C, R, self.cg.bias, ACT_NONE, g)
@@ -512,9 +536,13 @@ class GruOp:
         gw, gb = sink.get_packed(self.cc.weight), sink.get(self.cc.bias)
         if gw is not None or gb is not None:
             be.conv2d_wgrad_packed(x, rh, dcpre, R, gw if gw is not None else _scratch_packed(self.cc.weight), gb)
-        pc = self.pc_c.get(H, W, Cx, C, True)
+        f16 = self._fused16(be, x, h)
         D1 = torch.empty((B, H, W, Cx + C), dtype=f32, device=dev)            # [dx_can | drh]
-        be.conv2d(dcpre, None, pc.dgrad_simt, pc.dgrad_tc, Cx + C, R, None, ACT_NONE, D1)
+        if f16:
+            be.conv16(dcpre, None, self.pc_c.get_f16(True).dgrad_f16, Cx + C, R, None, ACT_NONE, D1)
+        else:
+            pc = self.pc_c.get(H, W, Cx, C, True)
+            be.conv2d(dcpre, None, pc.dgrad_simt, pc.dgrad_tc, Cx + C, R, None, ACT_NONE, D1)
         dg = torch.empty((B, H, W, 2 * C), dtype=f32, device=dev)
         drh = D1[..., Cx:]
         be.gru_gates_bwd(dz, drh, dh_a, g, h, self.gn_g.weight, self.gn_g.bias, st_g, dg, drh,
@@ -522,7 +550,11 @@ class GruOp:
         gw, gb = sink.get_packed(self.cg.weight), sink.get(self.cg.bias)
         if gw is not None or gb is not None:
             be.conv2d_wgrad_packed(x, h, dg, R, gw if gw is not None else _scratch_packed(self.cg.weight), gb)
-        pg = self.pc_g.get(H, W, Cx, C, True)
         D2 = out if out is not None else torch.empty((B, H, W, Cx + C), dtype=f32, device=dev)
-        be.conv2d(dg, None, pg.dgrad_simt, pg.dgrad_tc, Cx + C, R, None, ACT_NONE, D2, res=D1, alpha=1.0)
+        if f16:
+            pgf = self.pc_g.get_f16(True).dgrad_f16
+            be.conv16(dg[..., :C], dg[..., C:], pgf, Cx + C, R, None, ACT_NONE, D2, aux=D1, aux_kind=3, alpha=1.0)
+        else:
+            pg = self.pc_g.get(H, W, Cx, C, True)
+            be.conv2d(dg, None, pg.dgrad_simt, pg.dgrad_tc, Cx + C, R, None, ACT_NONE, D2, res=D1, alpha=1.0)
         return D2

@@ -530,3 +530,108 @@ def test_encode_stem_matches_torch():
     exp = torch.autograd.grad((torch.tanh(ref) * w).sum(), ps)
     for g_, r_ in zip(got, exp):
         assert g_.shape == r_.shape and rel_err(g_, r_) < 1e-5
+
+
+# ---- odex_conv16: image-resident kind::f16 convolution with the ConvGRU gate math in its epilogue (csrc/conv16_f16.cu) ----------
+@pytest.mark.parametrize("R,nsrc,N", [(3, 1, 64), (3, 1, 128), (5, 1, 128), (5, 2, 128), (5, 2, 64)])
+def test_conv16_plain_matches_exact_fp32_conv(be, R, nsrc, N):
+    """PLAIN mode against the exact-fp32 FFMA convolution: bias + ReLU, a tanh' mask, a residual with a device-side alpha;
+    channel-slice views as sources (the ConvGRU data-gradient passes dg[..., :C], dg[..., C:]) and as the output."""
+    torch.manual_seed(R * 10 + nsrc)
+    B = 5
+    wide = torch.randn(B, 16, 16, 128, device="cuda")
+    x0, x1 = wide[..., :64], (wide[..., 64:] if nsrc == 2 else None)
+    w = torch.randn(N, 64 * nsrc, R, R, device="cuda") / (8.0 * R)
+    bias = torch.randn(N, device="cuda") * 0.1
+    wf, ws = be.pack_weights(w, False, 2), be.pack_weights(w, False, False)
+    aux = torch.randn(B, 16, 16, N, device="cuda").tanh()
+    alpha_dev = torch.tensor(-0.3, dtype=torch.float64, device="cuda")
+    cases = [dict(bias=bias, act=ACT_RELU), dict(bias=None, act=ACT_NONE, aux=aux, aux_kind=ACT_TANH),
+             dict(bias=bias, act=ACT_NONE, aux=aux, aux_kind=3, alpha=2.0, alpha_dev=alpha_dev)]
+    for c in cases:
+        ref = torch.empty(B, 16, 16, N, device="cuda")
+        kind = c.get("aux_kind", 0)
+        be.conv2d(x0, x1, ws, None, N, R, c["bias"], c["act"], ref, dact=c["aux"] if kind in (1, 2) else None, dact_kind=kind if kind in (1, 2) else 0,
+                  res=c["aux"] if kind == 3 else None, alpha=c.get("alpha", 1.0), alpha_dev=c.get("alpha_dev"), impl=CONV_SIMT)
+        outw = torch.full((B, 16, 16, N + 64), 7.0, device="cuda")
+        out = outw[..., :N]
+        be.conv16(x0, x1, wf, N, R, c["bias"], c["act"], out, aux=c.get("aux"), aux_kind=kind, alpha=c.get("alpha", 1.0),
+                  alpha_dev=c.get("alpha_dev"))
+        torch.cuda.synchronize()
+        assert rel_err(out, ref) < 1e-5, (c.get("aux_kind"), rel_err(out, ref))
+        assert float((outw[..., N:] - 7.0).abs().max()) == 0.0           # nothing written beyond the N channels
+    skip = torch.ones(1, dtype=torch.int32, device="cuda")
+    o2 = torch.full((B, 16, 16, N), 7.0, device="cuda")
+    be.conv16(x0, x1, wf, N, R, bias, ACT_NONE, o2, skip=skip)
+    torch.cuda.synchronize()
+    assert float((o2 - 7.0).abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("R", [3, 5])
+@pytest.mark.parametrize("scale", [1.0, 1e-6, 1e5])
+def test_conv16_fused_gru_step_matches_unfused_kernels(be, R, scale):
+    """GRU_GATES + GRU_OUT (two launches) against conv (exact fp32) -> gru_gates_fwd_kernel -> conv -> gru_out_fwd_kernel:
+    z, r*h, h', the saved pre-norm convolutions, candidate and GroupNorm statistics -- at several data magnitudes (GroupNorm
+    makes the result scale-free; the fp16 operand scales must make the convolution so)."""
+    torch.manual_seed(5)
+    B, Cn = 6, 64
+    x = torch.randn(B, 16, 16, Cn, device="cuda") * scale
+    hw = torch.randn(B, 16, 16, 2 * Cn, device="cuda") * scale
+    h = hw[..., Cn:]                                                    # a channel-slice view, as the encoder hands it over
+    x[1] *= 1e-3
+    wg = torch.randn(2 * Cn, 2 * Cn, R, R, device="cuda") / (11.0 * R)
+    wc = torch.randn(Cn, 2 * Cn, R, R, device="cuda") / (11.0 * R)
+    bg, bc = torch.randn(2 * Cn, device="cuda") * 0.1 * scale, torch.randn(Cn, device="cuda") * 0.1 * scale
+    gam_g, bet_g = torch.rand(2 * Cn, device="cuda") + 0.5, torch.randn(2 * Cn, device="cuda") * 0.1
+    gam_c, bet_c = torch.rand(Cn, device="cuda") + 0.5, torch.randn(Cn, device="cuda") * 0.1
+    # reference: the unfused path
+    g = torch.empty(B, 16, 16, 2 * Cn, device="cuda")
+    be.conv2d(x, h, be.pack_weights(wg, False, False), None, 2 * Cn, R, bg, ACT_NONE, g, impl=CONV_SIMT)
+    z, rh, stg = torch.empty(B, 16, 16, Cn, device="cuda"), torch.empty(B, 16, 16, Cn, device="cuda"), torch.empty(B * 8, device="cuda")
+    be.gru_gates_fwd(g, h, gam_g, bet_g, 1e-5, z, rh, stg)
+    cpre = torch.empty(B, 16, 16, Cn, device="cuda")
+    be.conv2d(x, rh, be.pack_weights(wc, False, False), None, Cn, R, bc, ACT_NONE, cpre, impl=CONV_SIMT)
+    hn, cand, stc = torch.empty(B, 16, 16, Cn, device="cuda"), torch.empty(B, 16, 16, Cn, device="cuda"), torch.empty(B * 4, device="cuda")
+    be.gru_out_fwd(cpre, z, h, gam_c, bet_c, 1e-5, hn, cand, stc)
+    # fused
+    fz, frh, fstg = torch.empty_like(z), torch.empty_like(rh), torch.empty_like(stg)
+    fg = torch.empty_like(g)
+    be.conv16_gru_gates(x, h, be.pack_weights(wg, False, 2), R, bg, gam_g, bet_g, 1e-5, fz, frh, fstg, g_raw=fg)
+    hwide = torch.full((B, 16, 16, 2 * Cn), 3.0, device="cuda")
+    fhn = hwide[..., :Cn]
+    fcand, fcpre, fstc = torch.empty_like(cand), torch.empty_like(cpre), torch.empty_like(stc)
+    be.conv16_gru_out(x, frh, be.pack_weights(wc, False, 2), R, bc, gam_c, bet_c, 1e-5, fz, h, fhn, fstc, cand=fcand, cpre=fcpre)
+    torch.cuda.synchronize()
+    # the candidate / new state sit behind TWO convolutions and two GroupNorms (each divides by a standard deviation): 3e-5
+    for a, b, n, tol in ((fg, g, "g", 1e-5), (fz, z, "z", 1e-5), (frh, rh, "rh", 1e-5), (fcpre, cpre, "cpre", 1e-5),
+                         (fcand, cand, "cand", 3e-5), (fhn, hn, "hnew", 3e-5)):
+        for i in range(B):
+            assert rel_err(a[i], b[i]) < tol, (n, i, rel_err(a[i], b[i]))
+    sg, sc = fstg.view(B, 4, 2), stg.view(B, 4, 2)
+    assert rel_err(sg[..., 0], sc[..., 0]) < 1e-5 and rel_err(sg[..., 1], sc[..., 1]) < 1e-5
+    assert rel_err(fstc.view(B, 2, 2)[..., 1], stc.view(B, 2, 2)[..., 1]) < 1e-5
+    assert float((hwide[..., Cn:] - 3.0).abs().max()) == 0.0
+    # inference form: nothing saved
+    fz2, frh2, fhn2 = torch.empty_like(z), torch.empty_like(rh), torch.empty_like(hn)
+    be.conv16_gru_gates(x, h, be.pack_weights(wg, False, 2), R, bg, gam_g, bet_g, 1e-5, fz2, frh2, fstg)
+    be.conv16_gru_out(x, frh2, be.pack_weights(wc, False, 2), R, bc, gam_c, bet_c, 1e-5, fz2, h, fhn2, fstc)
+    torch.cuda.synchronize()
+    assert torch.equal(fhn2, fhn.contiguous())
+
+
+def test_conv16_is_deterministic(be):
+    torch.manual_seed(9)
+    B = 148 + 9
+    x, h = torch.randn(B, 16, 16, 64, device="cuda"), torch.randn(B, 16, 16, 64, device="cuda")
+    wg = be.pack_weights(torch.randn(128, 128, 5, 5, device="cuda") / 55.0, False, 2)
+    bg, gam, bet = torch.randn(128, device="cuda") * 0.1, torch.rand(128, device="cuda") + 0.5, torch.randn(128, device="cuda") * 0.1
+    first = None
+    for it in range(10):
+        z, rh, st = torch.empty_like(x), torch.empty_like(x), torch.empty(B * 8, device="cuda")
+        be.conv16_gru_gates(x, h, wg, 5, bg, gam, bet, 1e-5, z, rh, st)
+        torch.cuda.synchronize()
+        cur = (z.clone(), rh.clone(), st.clone())
+        if first is None:
+            first = cur
+        else:
+            assert all(torch.equal(a, b) for a, b in zip(cur, first)), it

@@ -56,7 +56,7 @@ def test_golden_rollout(name, impl):
             assert abs(a[1] - b[1]) <= 1e-4 * abs(b[1]), (a, b)
 
 
-def _check_grads(grads, oracle_run, rec, nonlinear, index_map=None, tol=1e-4):
+def _check_grads(grads, oracle_run, rec, nonlinear, index_map=None, tol=1e-4, flip_rel=1e-5, flip_frac=1e-5):
     """tanh: the hand-written backward must match autograd through the oracle at `tol`.  relu: the same bar, with the one
     ambiguity ReLU has taken out -- the oracle backward is re-run with the sub-gradient masks the product used
     (tests/test_relu_replay.py explains), and the elements where the two sides chose differently must be a handful of
@@ -70,7 +70,7 @@ def _check_grads(grads, oracle_run, rec, nonlinear, index_map=None, tol=1e-4):
     plain, replay, hook = relu_replay_gradients(grads, oracle_run, rec, index_map)
     print("relu: plain max %.2e  replayed max %.2e  flips %d of %d (max |pre|/range %.1e)" % (
         max(plain.values()), max(replay.values()), hook.n_flips, hook.n_elems, hook.max_flip_rel), replay)
-    assert hook.n_elems > 0 and hook.n_flips <= max(8, hook.n_elems // 100000) and hook.max_flip_rel < 1e-5, \
+    assert hook.n_elems > 0 and hook.n_flips <= max(8, int(hook.n_elems * flip_frac)) and hook.max_flip_rel < flip_rel, \
         (hook.n_flips, hook.n_elems, hook.max_flip_rel)
     assert max(replay.values()) < tol, replay
     assert max(plain.values()) < 2e-2, plain
@@ -166,7 +166,10 @@ def test_dopri5_relu_gradients_with_rejected_steps():
         return dict({n: ps[n].grad for n in grads if n != "z0"}, z0=z1.grad)
 
     accepted = [bool(a[3]) for a in st.attempts]
-    _check_grads(grads, oracle_run, rec, "relu", index_map=dopri5_backward_index_map(accepted), tol=1e-3)
+    # the adaptive forward itself agrees with the oracle to rtol, not to fp32 rounding (the two sides' step sizes differ in the
+    # last digits), so pre-activations up to ~rtol of the layer range may sit on different sides of 0
+    _check_grads(grads, oracle_run, rec, "relu", index_map=dopri5_backward_index_map(accepted), tol=1e-3, flip_rel=1e-3,
+                 flip_frac=1e-4)
     print(st)
     assert st.n_attempt >= 5 and accepted == [a[3] for a in logs[0].attempts] and st.n_feval == logs[0].n_feval
 
