@@ -30,6 +30,7 @@ FEVAL_FLOPS = 94371840            # per sample, 5 x conv3x3 64->64 at 16x16 (SUR
 CONV3_FLOPS = 2 * 256 * 64 * 576  # one 3x3 64->64 conv, per sample
 
 
+NET_TRAFFIC_F16_B128 = 9804416  # bytes per launch at batch 128: dram read 9.22 MB + written 0.28-0.89 MB (mean of the two launches captured; ncu --set full, profiles/r02_ncu.md)
 NET_TRAFFIC_B128 = 10654848  # bytes per launch at batch 128: dram read 9.95 MB + written 0.42-0.98 MB (mean of the two launches captured; ncu --set full, profiles/r01_final_ncu.md)
 
 
@@ -336,7 +337,7 @@ def vidode_main(args, world, rank, local):
                 "gpu_launches": int(launches), "clocks": clk, "roofline": roof, "cpu_baseline": cpu}
         print_line(json.dumps(line))
     if world > 1:
-        dist.destroy_process_group()
+        _teardown(dist, [])
 
 
 
@@ -749,16 +750,21 @@ def main():
         avg = e0.elapsed_time(e1) / 1e3 / reps
         ach = L_net * CONV3_FLOPS * B / avg / 1e12
         peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
-        roof = {"bound": "tensor", "kernel": "convnet_tc_kernel (5 x conv3x3 64->64 fused, 3xTF32, tcgen05 kind::tf32)", "achieved": ach,
+        kname = ("convnet_f16_kernel (5 x conv3x3 64->64 fused, two-term fp16 operand split, tcgen05 kind::f16)" if split else
+                 "convnet_tc_kernel (5 x conv3x3 64->64 fused, 3xTF32, tcgen05 kind::tf32)")
+        roof = {"bound": "tensor", "kernel": kname, "achieved": ach,
                 "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
                 # dram__bytes_read.sum + dram__bytes_write.sum of one launch at batch 128 (ncu --set full,
                 # profiles/r01_final_ncu.md), scaled with the batch; None until that capture exists
-                "traffic": NET_TRAFFIC_B128 and int(NET_TRAFFIC_B128 * B / 128),
-                "traffic_source": "profiles/r01_final_ncu.md (ncu --set full, per launch)",
+                "traffic": (NET_TRAFFIC_F16_B128 if split else NET_TRAFFIC_B128) and int((NET_TRAFFIC_F16_B128 if split else NET_TRAFFIC_B128) * B / 128),
+                "traffic_source": "profiles/r02_ncu.md (ncu --set full, per launch)" if split else "profiles/r01_final_ncu.md (ncu --set full, per launch)",
                 "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (of measured)" if peaks else "fallback 1.4 PF (of fallback)",
-                "note": "achieved counts algorithmic FLOPs once (2*M*N*K per layer, 5 layers per launch); the kernel issues 3 TF32 "
-                        "MMAs per useful one and TF32 runs at half the bf16 rate, so frac*6 is the share of tensor issue slots "
-                        "used; %d launches back to back, batch %d" % (reps, B),
+                "note": ("achieved counts algorithmic FLOPs once (2*M*N*K per layer, 5 layers per launch); fp32-level accuracy costs 3 fp16 "
+                         "MMAs per useful one (hi.hi, hi.lo, lo.hi) at the bf16 / fp16 rate, so the ceiling of useful FLOPs is 1/3 of "
+                         "the peak and frac*3 is the share of tensor issue slots used; " if split else
+                         "achieved counts algorithmic FLOPs once (2*M*N*K per layer, 5 layers per launch); the kernel issues 3 TF32 "
+                         "MMAs per useful one and TF32 runs at half the bf16 rate, so frac*6 is the share of tensor issue slots used; ")
+                        + "%d launches back to back, batch %d" % (reps, B),
                 "launches_timed": reps, "avg_launch_us": avg * 1e6}
 
         # ---- RK-stage GB/s (the second half of BASELINE's metric): the fused stage-combination / error-norm / dense-output
@@ -820,6 +826,8 @@ def main():
             k_s = max(4, args.steps // 2)
             strong = {"global_batch": 512, "batch_per_gpu": Bs, "ms_per_step": sec_s / k_s * 1e3,
                       "value": 512 * T_OUT * k_s / sec_s, "unit": "frames/s", "scaling": "strong"}
+            torch.cuda.synchronize()
+            g2.graph.reset()
             del g2, m2, o2, b2
             torch.cuda.empty_cache()
         except Exception as e:                       # a sub-record must never cost the line
@@ -845,12 +853,14 @@ def main():
                              "restated torchdiffeq, torch CPU fp32, anomaly mode off" % (cb, B)}
         line = {"metric": "ODEConvGRU %s predicted frames/s" % ("forward" if args.forward_only else "training-step"), "value": value,
                 "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": sec / args.steps * 1e3,
-                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32 (3xTF32 tensor-core convs, fp32 accumulate)",
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32 (tensor-core convs from split operands: two-term fp16 on kind::f16 / 3xTF32 on kind::tf32; fp32 accumulate)",
                 "data": "synthetic",
                 "config": {"workload": workload_name(args.method, args.forward_only, B),
                            "global_batch": B * world, "parallelism": "batch-sharded dp%d, NCCL flat-bucket gradient allreduce" % world,
                            "l2": "no explicit flush: the per-step working set (saved activations ~2 GB) is >> the 126 MB L2",
-                           "cuda_graph": graphed is not None, "optimizer": "torch.optim.Adam(fused=%s)" % fused_adam},
+                           "cuda_graph": graphed is not None,
+                           "allreduce_in_graph": bool(graphed is not None and world > 1 and graphed.hook_in_graph),
+                           "optimizer": "torch.optim.Adam(fused=%s)" % fused_adam},
                 "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": int(xh.numel() * 4 + yh.numel() * 4),
                         "d2h_bytes_per_step": 4, "ms_per_step": sec_e / args.steps * 1e3,
                         "pipeline": "pinned host -> staging buffer on a copy stream, overlapping the previous step; staging -> step "
@@ -862,7 +872,33 @@ def main():
         line.update(extras)
         print_line(json.dumps(line))
     if world > 1:
+        _teardown(dist, [graphed])
+
+
+def _teardown(dist, graphs):
+    """Leave a multi-rank run without hanging: a CUDA graph that holds captured NCCL work must be released before the process
+    group is destroyed, and a stuck communicator teardown (seen once with the all-reduce captured in the step graph: every rank
+    had printed / finished, destroy_process_group never returned) must not keep the launcher alive -- the line is already out,
+    so a watchdog ends the process with status 0 if teardown takes longer than 20 s."""
+    import gc
+    import threading
+
+    sys.stdout.flush()
+    sys.stderr.flush()
+    t = threading.Timer(20.0, lambda: os._exit(0))
+    t.daemon = True
+    t.start()
+    try:
+        torch.cuda.synchronize()
+        for g in graphs:
+            if g is not None and getattr(g, "graph", None) is not None:
+                g.graph.reset()
+        gc.collect()
+        torch.cuda.synchronize()
+        dist.barrier()
         dist.destroy_process_group()
+    finally:
+        t.cancel()
 
 
 if __name__ == "__main__":

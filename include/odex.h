@@ -109,6 +109,12 @@ int odex_conv2d_wgrad_packed(const float* x0, int ld0, int c0, const float* x1, 
                              int ldy, int B, int H, int W, int R, int N, float* dwp, float* db, int impl,
                              odex_stream_t s);
 int odex_wgrad_unpack(const float* dwp, int N, int C, int R, float* dw, odex_stream_t s);
+/* odex_conv2d_wgrad_packed on tcgen05 kind::f16 with the two-term fp16 operand split (x * s = fp16 hi + fp16 lo, s per tensor):
+ * same result to fp32 rounding at twice the MMA rate.  The per-tensor scales come from a max-|.| pass over X and dy that this
+ * entry enqueues first; scratch2 = 2 device floats it may use (contents irrelevant on entry, overwritten).  Same shapes as the TC
+ * kernel (c0, c1, N % 64 == 0, W % 16 == 0, H % 4 == 0, R in {1,3,5}). */
+int odex_conv2d_wgrad_f16(const float* x0, int ld0, int c0, const float* x1, int ld1, int c1, const float* dy, int ldy,
+                          int B, int H, int W, int R, int N, float* dwp, float* db, float* scratch2, odex_stream_t s);
 
 /* ------------------------------------------------------------------------------------------------ fused conv chain
  * A chain of L 3x3 C->C convolutions (C = 64) over 16x16 images in ONE launch, the image resident in shared memory
@@ -200,6 +206,25 @@ int odex_encode_stem_bwd(const float* x, const float* cells, const float* dcells
  * C must be a multiple of 4, pointers 16-byte aligned. */
 int odex_upsample2x_fwd(const float* x, int n, int H, int W, int C, float* out, odex_stream_t s);
 int odex_upsample2x_bwd(const float* dout, int n, int H, int W, int C, float* dx, odex_stream_t s);
+
+/* ------------------------------------------------------------------------------------------------ VidODE torch-side remainder
+ * BatchNorm2d (training mode: batch statistics over all M = N*H*W rows, biased variance, eps) fused with ReLU (relu != 0), NHWC
+ * rows x[M][C] (C % 4 == 0, C <= 256): the `nn.Conv2d, nn.BatchNorm2d, nn.ReLU` triples of models/VidODE.py:16-19,36.
+ * stats[3][C] <- (mean, rstd, biased variance) (the caller updates the module's running statistics from it);
+ * scratch: odex_bn_scratch_floats(M, C) floats.  _bwd: dx, and dgamma_dbeta[2][C] <- (dbeta = sum g, dgamma = sum g * xhat),
+ * g = dy * (y > 0).  Statistics are centred two-level sums merged in a fixed order (deterministic, no atomics). */
+long long odex_bn_scratch_floats(long long M, int C);
+int odex_bn_relu_fwd(const float* x, long long M, int C, const float* gamma, const float* beta, float eps, int relu, float* y,
+                     float* stats, float* scratch, long long scratch_floats, odex_stream_t s);
+int odex_bn_relu_bwd(const float* x, const float* y, const float* dy, long long M, int C, const float* gamma, const float* stats,
+                     int relu, float* dx, float* dgamma_dbeta, float* scratch, long long scratch_floats, odex_stream_t s);
+/* One step of the recursive flow warp + mask composition of models/VidODE.py:121-131,162-186:
+ *   warped = grid_sample(prev, grid + flow / ((size - 1) / 2), bilinear, padding_mode = 'border', align_corners = False)
+ *   pred   = sigmoid(mask) * warped + (1 - sigmoid(mask)) * intermediate
+ * prev / warped / pred: NCHW frames [B][C][H][W], C <= 3; head: the decoder head's NHWC output, row stride ldh floats, channels
+ * (flow_x, flow_y, intermediate[C], mask logit); lin_x[W], lin_y[H]: the reference's torch.linspace(-1, 1, .) base grid. */
+int odex_warp_compose_fwd(const float* prev, const float* head, int ldh, const float* lin_x, const float* lin_y, int B, int C,
+                          int H, int W, float* warped, float* pred, odex_stream_t s);
 
 /* ------------------------------------------------------------------------------------------------ ConvGRU gates
  * GroupNorm (groups of 32 channels, biased variance, eps, affine) fused with the gate non-linearities.

@@ -129,11 +129,16 @@ SIGNATURES = {
     "odex_decode_tail_bwd": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _f, _vp, _vp, _vp, _vp]),
     "odex_encode_stem_fwd": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _f, _vp, _vp]),
     "odex_encode_stem_bwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _f, _vp, _vp, _vp]),
+    "odex_bn_scratch_floats": (_ll, [_ll, _i]),
+    "odex_bn_relu_fwd": (_i, [_vp, _ll, _i, _vp, _vp, _f, _i, _vp, _vp, _vp, _ll, _vp]),
+    "odex_bn_relu_bwd": (_i, [_vp, _vp, _vp, _ll, _i, _vp, _vp, _i, _vp, _vp, _vp, _ll, _vp]),
+    "odex_warp_compose_fwd": (_i, [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp]),
     "odex_upsample2x_fwd": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "odex_upsample2x_bwd": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "odex_conv2d_wgrad": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
     "odex_conv2d_wgrad_packed": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
     "odex_wgrad_unpack": (_i, [_vp, _i, _i, _i, _vp, _vp]),
+    "odex_conv2d_wgrad_f16": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "odex_gru_gates_fwd": (_i, [_vp, _vp, _i, _vp, _vp, _f, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "odex_gru_out_fwd": (_i, [_vp, _vp, _vp, _i, _vp, _vp, _f, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "odex_gru_out_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),

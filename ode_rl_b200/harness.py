@@ -12,7 +12,7 @@ import os
 import torch
 import torch.nn as nn
 
-from .modules import encode_stem_supported, encode_stem_then_conv, conv_same_padded, conv_same_padded_supported, DiffEqSolver, ODEConvGRUCell, ODEFunc, conv3x3s2, conv3x3s2_supported, conv_transpose4x4s2_phases, conv_transpose4x4s2_supported, conv_same, conv_same_supported, decode_tail, decode_tail_supported, phases_to_nchw, upsample2x, upsample2x_supported
+from .modules import bn_relu, bn_relu_supported, warp_compose, warp_compose_supported, encode_stem_supported, encode_stem_then_conv, conv_same_padded, conv_same_padded_supported, DiffEqSolver, ODEConvGRUCell, ODEFunc, conv3x3s2, conv3x3s2_supported, conv_transpose4x4s2_phases, conv_transpose4x4s2_supported, conv_same, conv_same_supported, decode_tail, decode_tail_supported, phases_to_nchw, upsample2x, upsample2x_supported
 
 
 class _Encoder(nn.Module):          # models/ODEConvGRU.py:101-119 with n_downs == 2
@@ -107,8 +107,16 @@ class _VidEncoder(nn.Module):        # models/VidODE.py:11-26 (BatchNorm conv en
         # channels-last frames: cuDNN's NHWC stem + BatchNorm kernels (the NCHW BatchNorm kernel alone was 3.2 ms of the
         # forward at 320 x 32 x 128 x 128; measured 38.9 -> 36.0 ms per forward)
         x = x.contiguous(memory_format=torch.channels_last)
-        for m in self.cnn_encoder:
+        mods = list(self.cnn_encoder)
+        i = 0
+        while i < len(mods):
+            m = mods[i]
+            if i + 1 < len(mods) and isinstance(mods[i + 1], nn.ReLU) and bn_relu_supported(x, m):
+                x = bn_relu(x, m)               # BatchNorm (batch statistics) + ReLU: one statistics pass + one apply pass
+                i += 2
+                continue
             x = conv3x3s2(x, m) if conv3x3s2_supported(x, m) else m(x)
+            i += 1
         return x
 
 
@@ -130,7 +138,14 @@ class _VidDecoder(nn.Module):        # models/VidODE.py:28-44 (bilinear 2x upsam
         # the wide 3x3 convolutions (256 -> 128 on 64x64, 128 -> 64 on 128x128) on the tensor-core
         # convolution of the path; upsample / BatchNorm / ReLU and the 6-channel head stay torch, in channels-last memory
         x = x.contiguous(memory_format=torch.channels_last)
-        for m in self.cnn_decoder:
+        mods = list(self.cnn_decoder)
+        i = 0
+        while i < len(mods):
+            m = mods[i]
+            if i + 1 < len(mods) and isinstance(mods[i + 1], nn.ReLU) and bn_relu_supported(x, m):
+                x = bn_relu(x, m)
+                i += 2
+                continue
             if upsample2x_supported(x, m):
                 x = upsample2x(x)
             elif conv_same_supported(x, m):
@@ -139,6 +154,7 @@ class _VidDecoder(nn.Module):        # models/VidODE.py:28-44 (bilinear 2x upsam
                 x = conv_same_padded(x, m)          # the 64 -> in_channels + 3 head, output channels padded to 64
             else:
                 x = m(x)
+            i += 1
         return x
 
 
@@ -169,6 +185,7 @@ class VidODEHarness(nn.Module):
                                         downsize=False, nonlinear='relu', final_act=False, device=device)
         self.diffeq_solver = DiffEqSolver(self.ode_decoder_func, method, odeint_rtol=rtol, odeint_atol=atol, device=device)
         self.conv_decoder = _VidDecoder(out_dim * 2, in_channels + 3, n_downs, device=device)
+        self.fast_warp = os.environ.get("ODEX_TORCH_WARP") is None
 
     def latents(self, inputs, batch_dict):
         """The hot path alone: frames -> (mean_z0, sol_y [B,T,C,H',W'])."""
@@ -190,6 +207,7 @@ class VidODEHarness(nn.Module):
             cur = sol_y[:, k, ...]
             outs.append(self.conv_decoder(torch.cat([cur, prev], dim=1)))
             prev = cur
+        heads = outs
         outs = torch.stack(outs, dim=1)                                       # [B,T,2+c+1(+...),h,w]
         flows, inter = outs[:, :, :2, ...], outs[:, :, 2:2 + c, ...]
         masks = torch.sigmoid(outs[:, :, 2 + c:, ...])
@@ -198,6 +216,19 @@ class VidODEHarness(nn.Module):
         gy = torch.linspace(-1.0, 1.0, h, device=inputs.device).view(1, h, 1, 1).expand(b, -1, w, -1)
         grid = torch.cat([gx, gy], 3).float()
         frame, warped = inputs[:, -1, ...], []
+        if self.fast_warp and warp_compose_supported(frame, heads[0]):
+            # the recursive warp + the composition, one kernel per predicted frame, read straight from the head's NHWC output
+            lin_x, lin_y = torch.linspace(-1.0, 1.0, w, device=inputs.device), torch.linspace(-1.0, 1.0, h, device=inputs.device)
+            preds = []
+            for k in range(n_pred):
+                frame, pk = warp_compose(frame, heads[k], lin_x, lin_y)
+                warped.append(frame)
+                preds.append(pk)
+            warped = torch.stack(warped, dim=1)
+            pred_x = torch.stack(preds, dim=1).view(b, -1, c, h, w)
+            extra = {"optical_flow": flows, "warped_pred_x": warped, "pred_intermediates": inter, "pred_masks": masks,
+                     "mean_z0": mean_z0, "sol_y": sol_y}
+            return pred_x, extra
         for k in range(n_pred):
             fl = torch.cat([flows[:, k, 0:1] / ((w - 1.0) / 2.0), flows[:, k, 1:2] / ((h - 1.0) / 2.0)], dim=1)
             frame = nn.functional.grid_sample(frame, grid + fl.permute(0, 2, 3, 1), padding_mode="border", align_corners=False)   # the default the reference runs with
@@ -210,11 +241,14 @@ class VidODEHarness(nn.Module):
 
 
 class GraphedTrainStep:
-    """One training step (zero_grad -> forward -> loss -> backward [-> optimizer.step]) captured once as a CUDA graph and
-    replayed: the step is ~1200 kernel launches enqueued from Python through ctypes, i.e. ~20 ms of host time per step,
-    which a graph replay removes.  Fixed-step solvers only (the adaptive solver reads its controller state back on the
-    host once per forward, which cannot be captured).  `grad_hook`, when given, runs EAGERLY between the captured
-    backward and the (eager) optimizer step -- the NCCL gradient all-reduce of the multi-GPU run."""
+    """One training step (zero_grad -> forward -> loss -> backward -> [gradient all-reduce] -> optimizer.step) captured once as
+    a CUDA graph and replayed: the step is ~700 kernel launches enqueued from Python through ctypes, i.e. ~17 ms of host time
+    per step, which a graph replay removes.  Fixed-step solvers only (the adaptive solver reads its controller state back on
+    the host once per forward, which cannot be captured).
+    `grad_hook` (the NCCL flat-bucket all-reduce of the multi-GPU run) is captured INSIDE the graph together with the optimizer
+    step, so that nothing between the last weight-gradient kernel and Adam passes through the host (round 1 replayed the graph,
+    then ran the all-reduce and the optimizer eagerly: a graph split and ~0.24 ms per step at 8 GPUs).  If the collective cannot
+    be captured on this build (`ODEX_GRAPH_NCCL=0`, or the capture raises), it falls back to that eager tail."""
 
     def __init__(self, model, optimizer, loss_fn, x, y, obs, tp, grad_hook=None, warmup=3):
         self.model, self.opt, self.loss_fn, self.grad_hook = model, optimizer, loss_fn, grad_hook
@@ -223,18 +257,30 @@ class GraphedTrainStep:
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
-            for _ in range(warmup):                            # allocator / cuDNN autotune / weight-pack warm-up
+            for _ in range(warmup):                            # allocator / cuDNN autotune / weight-pack / NCCL warm-up
                 self._eager()
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         from . import _lib
-        n0 = _lib.launch_count()
-        self.graph = torch.cuda.CUDAGraph()
-        self.opt.zero_grad(set_to_none=True)
-        with torch.cuda.graph(self.graph):
-            self.loss = self._fwd_bwd()
-            if self.grad_hook is None:
-                self.opt.step()
+        self.hook_in_graph = grad_hook is not None and os.environ.get("ODEX_GRAPH_NCCL", "1") != "0"
+        for attempt in range(2):
+            n0 = _lib.launch_count()
+            self.graph = torch.cuda.CUDAGraph()
+            self.opt.zero_grad(set_to_none=True)
+            try:
+                with torch.cuda.graph(self.graph):
+                    self.loss = self._fwd_bwd()
+                    if self.grad_hook is None:
+                        self.opt.step()
+                    elif self.hook_in_graph:
+                        self.grad_hook()
+                        self.opt.step()
+                break
+            except Exception:                                  # a collective that cannot be captured: eager tail instead
+                if not self.hook_in_graph or attempt == 1:
+                    raise
+                self.hook_in_graph = False
+                torch.cuda.synchronize()
         self.launches_per_step = _lib.launch_count() - n0      # libodex kernels inside the graph
 
     def _fwd_bwd(self):
@@ -257,7 +303,7 @@ class GraphedTrainStep:
         if y is not None:
             self.y.copy_(y, non_blocking=True)
         self.graph.replay()
-        if self.grad_hook is not None:
+        if self.grad_hook is not None and not self.hook_in_graph:
             self.grad_hook()
             self.opt.step()
         return self.loss.detach()

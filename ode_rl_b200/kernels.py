@@ -292,6 +292,41 @@ class Backend:
         _lib.check(self.lib.odex_encode_stem_bwd(x.data_ptr(), cells.data_ptr(), dcells.data_ptr(), n, 64, 64, 16, float(slope),
                                                  _ptr(dw), _ptr(db), _stream()), "odex_encode_stem_bwd")
 
+    # ------------------------------------------------------------------ BatchNorm(batch statistics) + ReLU, flow warp (VidODE)
+    def bn_relu_fwd(self, x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float, relu: bool, y: torch.Tensor,
+                    stats: torch.Tensor) -> None:
+        """odex_bn_relu_fwd on dense NHWC x [..., C]: y = relu(batchnorm(x)); stats [3, C] <- (mean, rstd, biased var)."""
+        self.require(x)
+        Cc = x.shape[-1]
+        M = x.numel() // Cc
+        assert x.is_contiguous() and y.is_contiguous() and stats.is_contiguous() and stats.numel() == 3 * Cc
+        n = int(self.lib.odex_bn_scratch_floats(M, Cc))
+        scratch = torch.empty(n, dtype=torch.float32, device=x.device)
+        _lib.check(self.lib.odex_bn_relu_fwd(x.data_ptr(), M, Cc, gamma.detach().data_ptr(), beta.detach().data_ptr(), float(eps),
+                                             1 if relu else 0, y.data_ptr(), stats.data_ptr(), scratch.data_ptr(), n, _stream()),
+                   "odex_bn_relu_fwd")
+
+    def bn_relu_bwd(self, x, y, dy, gamma, stats, relu: bool, dx, dgb) -> None:
+        """odex_bn_relu_bwd: dx and dgb [2, C] <- (dbeta, dgamma)."""
+        Cc = x.shape[-1]
+        M = x.numel() // Cc
+        assert x.is_contiguous() and dy.is_contiguous() and dx.is_contiguous() and dgb.numel() == 2 * Cc
+        n = int(self.lib.odex_bn_scratch_floats(M, Cc))
+        scratch = torch.empty(n, dtype=torch.float32, device=x.device)
+        _lib.check(self.lib.odex_bn_relu_bwd(x.data_ptr(), _ptr(y), dy.data_ptr(), M, Cc, gamma.detach().data_ptr(), stats.data_ptr(),
+                                             1 if relu else 0, dx.data_ptr(), dgb.data_ptr(), scratch.data_ptr(), n, _stream()),
+                   "odex_bn_relu_bwd")
+
+    def warp_compose_fwd(self, prev: torch.Tensor, head: torch.Tensor, lin_x: torch.Tensor, lin_y: torch.Tensor,
+                         warped: torch.Tensor, pred: torch.Tensor) -> None:
+        """odex_warp_compose_fwd: prev [B,C,H,W] NCHW, head [B,H,W,>=C+3] NHWC view -> warped, pred [B,C,H,W]."""
+        self.require(prev)
+        B, Cc, H, W = prev.shape
+        ph, ldh = _rows(head)
+        assert prev.is_contiguous() and warped.is_contiguous() and pred.is_contiguous() and tuple(head.shape[:3]) == (B, H, W)
+        _lib.check(self.lib.odex_warp_compose_fwd(prev.data_ptr(), ph, ldh, lin_x.data_ptr(), lin_y.data_ptr(), B, Cc, H, W,
+                                                  warped.data_ptr(), pred.data_ptr(), _stream()), "odex_warp_compose_fwd")
+
     # ------------------------------------------------------------------ bilinear 2x upsample (NHWC)
     def upsample2x_fwd(self, x: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
         """odex_upsample2x_fwd: x [n,H,W,C] -> out [n,2H,2W,C] (align_corners=False)."""
@@ -324,11 +359,31 @@ class Backend:
         _lib.check(self.lib.odex_conv2d_wgrad(p0, ld0, c0, p1, ld1, c1, pdy, ldy, B, H, W, R, N, dw.data_ptr(),
                                               _ptr(db), _stream()), "odex_conv2d_wgrad")
 
+    @staticmethod
+    def wgrad_f16_shape_ok(c0: int, c1: int, N: int, H: int, W: int, R: int) -> bool:
+        """Mirror of wgrad_f16_supported() in csrc/wgrad_f16.cu."""
+        return R in (1, 3, 5) and c0 % 64 == 0 and c1 % 64 == 0 and N % 64 == 0 and W % 16 == 0 and H % 4 == 0 \
+            and os.environ.get("ODEX_NO_WGRAD16") is None
+
     def conv2d_wgrad_packed(self, x0: torch.Tensor, x1: Optional[torch.Tensor], dy: torch.Tensor, R: int,
-                            dwp: torch.Tensor, db: Optional[torch.Tensor], impl: int = CONV_AUTO) -> None:
+                            dwp: torch.Tensor, db: Optional[torch.Tensor], impl: int = CONV_AUTO, f16: bool = False) -> None:
         """odex_conv2d_wgrad_packed: dwp [R*R, N, c0+c1] += dy^T X (tensor-core kernel where the shape allows),
-        db += colsum(dy)."""
+        db += colsum(dy).  f16: the kind::f16 kernel with the two-term fp16 split (odex_conv2d_wgrad_f16) where its shape test
+        passes."""
         B, H, W, c0 = x0.shape
+        if f16 and impl == CONV_AUTO and self.wgrad_f16_shape_ok(c0, 0 if x1 is None else x1.shape[3], dy.shape[3], H, W, R):
+            p0, ld0 = _rows(x0)
+            p1, ld1, c1 = None, 0, 0
+            if x1 is not None:
+                p1, ld1 = _rows(x1)
+                c1 = x1.shape[3]
+            pdy, ldy = _rows(dy)
+            N = dy.shape[3]
+            assert dwp.is_contiguous() and tuple(dwp.shape) == (R * R, N, c0 + c1), (tuple(dwp.shape), (R * R, N, c0 + c1))
+            scratch = torch.empty(2, dtype=torch.float32, device=x0.device)
+            _lib.check(self.lib.odex_conv2d_wgrad_f16(p0, ld0, c0, p1, ld1, c1, pdy, ldy, B, H, W, R, N, dwp.data_ptr(),
+                                                      _ptr(db), scratch.data_ptr(), _stream()), "odex_conv2d_wgrad_f16")
+            return
         p0, ld0 = _rows(x0)
         p1, ld1, c1 = None, 0, 0
         if x1 is not None:

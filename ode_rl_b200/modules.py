@@ -23,7 +23,7 @@ import torch.nn as nn
 
 from . import kernels as K
 from .kernels import ACT_NONE, CONV_TC
-from .ops import ConvNetOp, GradSink, GruOp, from_nhwc, live, live_input, to_nhwc
+from .ops import ConvNetOp, GradSink, GruOp, _wgrad_f16, from_nhwc, live, live_input, to_nhwc
 from .solver import FIXED, odeint_dopri5, odeint_fixed
 
 
@@ -166,7 +166,7 @@ class _ConvT4x4s2Fn(torch.autograd.Function):
         if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
             dwp = torch.zeros((9, 4 * cout, cin), dtype=torch.float32, device=xn.device)
             db3 = torch.zeros((4 * cout,), dtype=torch.float32, device=xn.device)
-            be.conv2d_wgrad_packed(xn, None, dP, 3, dwp, db3)
+            be.conv2d_wgrad_packed(xn, None, dP, 3, dwp, db3, f16=_wgrad_f16())
             dw3 = torch.zeros((4 * cout, cin, 3, 3), dtype=torch.float32, device=xn.device)
             be.wgrad_unpack(dwp, dw3)
             dw = _ct_dwt(dw3, cin, cout)
@@ -260,7 +260,7 @@ class _Conv3x3s2Fn(torch.autograd.Function):
         if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
             dwp = torch.zeros((9, cout, c4), dtype=torch.float32, device=xs.device)
             dbv = torch.zeros((cout,), dtype=torch.float32, device=xs.device)
-            be.conv2d_wgrad_packed(xs, None, dy, 3, dwp, dbv)
+            be.conv2d_wgrad_packed(xs, None, dy, 3, dwp, dbv, f16=_wgrad_f16())
             dw3 = torch.zeros((cout, c4, 3, 3), dtype=torch.float32, device=xs.device)
             be.wgrad_unpack(dwp, dw3)
             dw = _cs_dw(dw3, cout, cin, ctx.k)
@@ -305,7 +305,7 @@ class _ConvCellsFn(torch.autograd.Function):
         if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
             dwp = torch.zeros((9, cout, c4), dtype=torch.float32, device=xs.device)
             dbv = torch.zeros((cout,), dtype=torch.float32, device=xs.device)
-            be.conv2d_wgrad_packed(xs, None, dy, 3, dwp, dbv)
+            be.conv2d_wgrad_packed(xs, None, dy, 3, dwp, dbv, f16=_wgrad_f16())
             dw3 = torch.zeros((cout, c4, 3, 3), dtype=torch.float32, device=xs.device)
             be.wgrad_unpack(dwp, dw3)
             dw = _cs_dw(dw3, cout, cin, ctx.k)
@@ -521,7 +521,7 @@ class _ConvSameWFn(torch.autograd.Function):
         if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
             dwp = torch.zeros((R * R, cout, cin), dtype=torch.float32, device=xn.device)
             dbv = torch.zeros((cout,), dtype=torch.float32, device=xn.device)
-            be.conv2d_wgrad_packed(xn, None, dy, R, dwp, dbv)
+            be.conv2d_wgrad_packed(xn, None, dy, R, dwp, dbv, f16=_wgrad_f16())
             dw = torch.zeros((cout, cin, R, R), dtype=torch.float32, device=xn.device)
             be.wgrad_unpack(dwp, dw)
             if ctx.has_bias:
@@ -588,6 +588,104 @@ def upsample2x(x: torch.Tensor) -> torch.Tensor:
     """The VidODE decoder's bilinear 2x upsample (models/VidODE.py:34) as one HBM-bound NHWC kernel (odex_upsample2x_fwd;
     adjoint odex_upsample2x_bwd); the result is a channels-last view, what conv_same reads without a repack."""
     return _Upsample2xFn.apply(x)
+
+
+class _BnReluFn(torch.autograd.Function):
+    """relu(BatchNorm2d(x)) with batch statistics (training mode), logical NCHW in / out on NHWC memory (odex_bn_relu_fwd / _bwd).
+    Returns (y, mean, biased var); the caller updates the module's running statistics."""
+
+    @staticmethod
+    def forward(ctx, x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float, relu: bool):
+        be = K.backend()
+        be.require(x)
+        xn = to_nhwc(x.detach().float())
+        if not xn.is_contiguous():
+            xn = xn.contiguous()
+        Cc = xn.shape[-1]
+        y = torch.empty_like(xn)
+        stats = torch.empty((3, Cc), dtype=torch.float32, device=xn.device)
+        be.bn_relu_fwd(xn, gamma, beta, eps, relu, y, stats)
+        ctx.save_for_backward(xn, y, gamma.detach(), stats)
+        ctx.relu = relu
+        ctx.mark_non_differentiable(stats)
+        return from_nhwc(y), stats
+
+    @staticmethod
+    def backward(ctx, dy, _dstats):
+        be = K.backend()
+        xn, y, gamma, stats = ctx.saved_tensors
+        d = to_nhwc(dy.float())
+        if not d.is_contiguous():
+            d = d.contiguous()
+        dx = torch.empty_like(xn)
+        dgb = torch.empty((2, xn.shape[-1]), dtype=torch.float32, device=xn.device)
+        be.bn_relu_bwd(xn, y, d, gamma, stats, ctx.relu, dx, dgb)
+        return from_nhwc(dx), dgb[1], dgb[0], None, None
+
+
+def bn_relu_supported(x: torch.Tensor, bn: nn.Module) -> bool:
+    """BatchNorm2d in training mode (batch statistics, what the reference's VidODE runs) with affine parameters on a CUDA
+    fp32 tensor whose channel count the kernel takes."""
+    return (isinstance(bn, nn.BatchNorm2d) and bn.training and bn.affine and x.is_cuda and x.dim() == 4 and x.dtype == torch.float32
+            and x.shape[0] > 0 and x.shape[1] % 4 == 0 and x.shape[1] <= 256 and hasattr(K.backend(), "bn_relu_fwd"))
+
+
+def bn_relu(x: torch.Tensor, bn: nn.BatchNorm2d, relu: bool = True) -> torch.Tensor:
+    """relu(bn(x)) (models/VidODE.py:16-19,36) as one statistics pass + one apply pass; the running statistics are updated as
+    nn.BatchNorm2d does (momentum, unbiased variance)."""
+    y, stats = _BnReluFn.apply(x, bn.weight, bn.bias, float(bn.eps), relu)
+    if bn.track_running_stats and bn.running_mean is not None:
+        with torch.no_grad():
+            n = x.numel() // x.shape[1]
+            bn.num_batches_tracked.add_(1)
+            mom = bn.momentum if bn.momentum is not None else 1.0 / float(bn.num_batches_tracked)
+            bn.running_mean.mul_(1.0 - mom).add_(stats[0], alpha=mom)
+            bn.running_var.mul_(1.0 - mom).add_(stats[2], alpha=mom * n / max(n - 1, 1))
+    return y
+
+
+class _WarpComposeFn(torch.autograd.Function):
+    """One step of the recursive flow warp + mask composition (models/VidODE.py:121-131,162-186): forward on
+    odex_warp_compose_fwd; the backward re-derives the step with torch's own grid_sample on the saved operands (the warp is
+    0.6 % of the forward and off every benchmarked path)."""
+
+    @staticmethod
+    def forward(ctx, prev: torch.Tensor, head: torch.Tensor, lin_x: torch.Tensor, lin_y: torch.Tensor):
+        be = K.backend()
+        be.require(prev)
+        p = prev.detach().float().contiguous()
+        hn = head.detach().movedim(1, -1)                       # [B, H, W, 3 + C] view of the head's NHWC memory
+        if hn.stride(3) != 1 or hn.stride(2) % 4 != 0 or hn.stride(2) < 8 or hn.data_ptr() % 16 != 0:
+            hn = torch.nn.functional.pad(hn, (0, 8 - hn.shape[3] % 8 if hn.shape[3] % 8 else 0)).contiguous()
+        warped, pred = torch.empty_like(p), torch.empty_like(p)
+        be.warp_compose_fwd(p, hn, lin_x, lin_y, warped, pred)
+        ctx.save_for_backward(p, head.detach(), lin_x, lin_y)
+        return warped, pred
+
+    @staticmethod
+    def backward(ctx, dwarped, dpred):
+        p, head, lin_x, lin_y = ctx.saved_tensors
+        b, c, h, w = p.shape
+        with torch.enable_grad():
+            p_ = p.requires_grad_(True)
+            hd = head.requires_grad_(True)
+            grid = torch.stack(torch.broadcast_tensors(lin_x.view(1, 1, w), lin_y.view(1, h, 1)), dim=-1).expand(b, h, w, 2)
+            fl = torch.cat([hd[:, 0:1] / ((w - 1.0) / 2.0), hd[:, 1:2] / ((h - 1.0) / 2.0)], dim=1)
+            warped = nn.functional.grid_sample(p_, grid + fl.permute(0, 2, 3, 1), padding_mode="border", align_corners=False)
+            m = torch.sigmoid(hd[:, 2 + c:3 + c])
+            pred = m * warped + (1 - m) * hd[:, 2:2 + c]
+            gp, gh = torch.autograd.grad([warped, pred], [p_, hd], [dwarped, dpred], allow_unused=True)
+        return gp, gh, None, None
+
+
+def warp_compose_supported(prev: torch.Tensor, head: torch.Tensor) -> bool:
+    return (prev.is_cuda and prev.dim() == 4 and 1 <= prev.shape[1] <= 3 and head.dim() == 4 and head.shape[1] == prev.shape[1] + 3
+            and prev.dtype == torch.float32 and head.dtype == torch.float32 and prev.shape[0] > 0 and hasattr(K.backend(), "warp_compose_fwd"))
+
+
+def warp_compose(prev: torch.Tensor, head: torch.Tensor, lin_x: torch.Tensor, lin_y: torch.Tensor):
+    """(warped, pred) for one predicted frame: prev [B,C,H,W], head [B,3+C,H,W] = (flow_x, flow_y, intermediate, mask logit)."""
+    return _WarpComposeFn.apply(prev, head, lin_x, lin_y)
 
 
 class ODEFunc(nn.Module):

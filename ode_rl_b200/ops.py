@@ -37,6 +37,14 @@ def set_conv_split(name: str) -> str:
     return prev
 
 
+def _wgrad_f16() -> bool:
+    """The kind::f16 weight-gradient kernel (csrc/wgrad_f16.cu) is opt-in (ODEX_WGRAD_SPLIT=f16): it is parity-green, but its
+    per-tensor scales need a max pass over both operands (21 us per batched launch at B = 128) and its fp32 -> fp16 operand
+    transform, not the halved MMA time, bounds a tile -- measured 17.4 ms per step against 16.6 ms with the 3xTF32 kernel
+    (profiles/r02_step_breakdown_wgrad_f16.log)."""
+    return os.environ.get("ODEX_WGRAD_SPLIT", "tf32").lower() == "f16" and CONV_IMPL != "simt"
+
+
 def set_conv_impl(name: str) -> str:
     global CONV_IMPL
     assert name in ("auto", "simt", "tc")
@@ -111,7 +119,7 @@ class GradSink:
         gw, gb = self.get_packed(conv.weight), self.get(conv.bias)
         if gw is None:          # bias-only gradient: the kernel still needs a dw target
             gw = _scratch_packed(conv.weight)
-        K.backend().conv2d_wgrad_packed(x, None, dy, conv.kernel_size[0], gw, gb)
+        K.backend().conv2d_wgrad_packed(x, None, dy, conv.kernel_size[0], gw, gb, f16=_wgrad_f16())
 
     def flush(self) -> None:
         for conv, items in self._pending.values():
@@ -535,7 +543,7 @@ class GruOp:
                        grad_or_scratch(self.gn_c.weight), grad_or_scratch(self.gn_c.bias))
         gw, gb = sink.get_packed(self.cc.weight), sink.get(self.cc.bias)
         if gw is not None or gb is not None:
-            be.conv2d_wgrad_packed(x, rh, dcpre, R, gw if gw is not None else _scratch_packed(self.cc.weight), gb)
+            be.conv2d_wgrad_packed(x, rh, dcpre, R, gw if gw is not None else _scratch_packed(self.cc.weight), gb, f16=_wgrad_f16())
         f16 = self._fused16(be, x, h)
         D1 = torch.empty((B, H, W, Cx + C), dtype=f32, device=dev)            # [dx_can | drh]
         if f16:
@@ -549,7 +557,7 @@ class GruOp:
                          grad_or_scratch(self.gn_g.weight), grad_or_scratch(self.gn_g.bias))   # D1[..., Cx:] <- dh_a + drh*r
         gw, gb = sink.get_packed(self.cg.weight), sink.get(self.cg.bias)
         if gw is not None or gb is not None:
-            be.conv2d_wgrad_packed(x, h, dg, R, gw if gw is not None else _scratch_packed(self.cg.weight), gb)
+            be.conv2d_wgrad_packed(x, h, dg, R, gw if gw is not None else _scratch_packed(self.cg.weight), gb, f16=_wgrad_f16())
         D2 = out if out is not None else torch.empty((B, H, W, Cx + C), dtype=f32, device=dev)
         if f16:
             pgf = self.pc_g.get_f16(True).dgrad_f16

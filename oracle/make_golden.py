@@ -99,6 +99,24 @@ def param_checksums(model):
     return {k: float(v.double().sum()) for k, v in model.state_dict().items() if v.dtype.is_floating_point}
 
 
+def main_vidode_128():
+    """BASELINE configs[4]'s own frame size: 128x128x3 frames -> 128 latent channels on 32x32 (the shapes at which the kernels take
+    their 32x32 / 256-gate paths), dopri5 at the DiffEqSolver defaults, B=1, 2 in / 2 out (the CPU reference needs seconds)."""
+    ref = refload.load()
+    B, T, C, S = 1, 2, 3, 128
+    frames, batch = vidode_batch(B, T, C, S, seed=4321)
+    torch.manual_seed(0)
+    model = ref.VidODE(refload.vidode_opt("dopri5", S, C), torch.device("cpu"))
+    sums = param_checksums(model)
+    with torch.no_grad():
+        mu, sol_y, pred, log = vidode_forward(model, frames, batch)
+    rec = {"method": "dopri5", "scale": 1.0, "rtol": model.diffeq_solver.odeint_rtol, "atol": model.diffeq_solver.odeint_atol,
+           "frames_seed": 4321, "B": B, "T": T, "C": C, "S": S, "weights_seed": 0, "checksums": sums,
+           "mean_z0": mu.contiguous(), "sol_y": sol_y, "pred": pred.contiguous(), "attempts": list(log.attempts), "n_feval": log.n_feval}
+    torch.save(rec, os.path.join(OUT, "vidode_dopri5_128.pt"))
+    print("vidode_dopri5_128.pt pred", tuple(pred.shape), "attempts", len(rec["attempts"]))
+
+
 def main_vidode():
     """BASELINE configs[4] wiring at a fixture-sized shape: 64x64x3 frames (16x16 latent, 128 channels), B=2, 3 in / 3 out.
     Weights are NOT stored (13 MB): the fixture keeps per-tensor checksums of the seeded default init and the product
@@ -129,7 +147,9 @@ def main_vidode():
 
 
 if __name__ == "__main__":
-    if "vidode" in sys.argv[1:]:
+    if "vidode128" in sys.argv[1:]:
+        main_vidode_128()
+    elif "vidode" in sys.argv[1:]:
         main_vidode()
     else:
         main()

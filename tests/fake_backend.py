@@ -178,7 +178,7 @@ class FakeBackend:
         if db is not None:
             db += dy.sum((0, 1, 2))
 
-    def conv2d_wgrad_packed(self, x0, x1, dy, R, dwp, db, impl=0):
+    def conv2d_wgrad_packed(self, x0, x1, dy, R, dwp, db, impl=0, f16=False):
         self.launches += 1
         x = x0 if x1 is None else torch.cat((x0, x1), 3)
         N, Cc = dy.shape[3], x.shape[3]
@@ -456,6 +456,37 @@ class FakeBackend:
                 sol[j].copy_((((y0 + x * cd) + x * x * cc) + x * x * x * cb) + x * x * x * x * ca)
         y0.copy_(y1)
         k7[0].copy_(f1)
+
+    def bn_relu_fwd(self, x, gamma, beta, eps, relu, y, stats):
+        self.launches += 3
+        Cc = x.shape[-1]
+        r = x.reshape(-1, Cc).double()
+        mean, var = r.mean(0), r.var(0, unbiased=False)
+        rstd = 1.0 / torch.sqrt(var + eps)
+        stats[0], stats[1], stats[2] = mean.float(), rstd.float(), var.float()
+        o = (x - stats[0]) * stats[1] * gamma.detach() + beta.detach()
+        y.copy_(torch.relu(o) if relu else o)
+
+    def bn_relu_bwd(self, x, y, dy, gamma, stats, relu, dx, dgb):
+        self.launches += 3
+        Cc = x.shape[-1]
+        g = dy * (y > 0) if relu else dy
+        xh = (x - stats[0]) * stats[1]
+        M = x.numel() // Cc
+        dgb[0] = g.reshape(-1, Cc).sum(0)
+        dgb[1] = (g * xh).reshape(-1, Cc).sum(0)
+        dx.copy_(gamma.detach() * stats[1] * (g - dgb[0] / M - xh * (dgb[1] / M)))
+
+    def warp_compose_fwd(self, prev, head, lin_x, lin_y, warped, pred):
+        self.launches += 1
+        b, c, h, w = prev.shape
+        hd = head.movedim(-1, 1)
+        grid = torch.stack(torch.broadcast_tensors(lin_x.view(1, 1, w), lin_y.view(1, h, 1)), dim=-1).expand(b, h, w, 2)
+        fl = torch.cat([hd[:, 0:1] / ((w - 1.0) / 2.0), hd[:, 1:2] / ((h - 1.0) / 2.0)], dim=1)
+        wv = F.grid_sample(prev, grid + fl.permute(0, 2, 3, 1), padding_mode="border", align_corners=False)
+        m = torch.sigmoid(hd[:, 2 + c:3 + c])
+        warped.copy_(wv)
+        pred.copy_(m * wv + (1 - m) * hd[:, 2:2 + c])
 
     def nan_flag(self, x, flag, bit):
         self.launches += 1

@@ -139,7 +139,7 @@ def test_conv2d_wgrad(be, fb, case):
     assert rel_err(gw, rw) < 5e-6 and rel_err(gb, rb) < 5e-6
 
 
-@pytest.mark.parametrize("impl", ["tc", "simt"])
+@pytest.mark.parametrize("impl", ["tc", "simt", "f16"])
 @pytest.mark.parametrize("case", [(2, 16, 16, 64, 0, 64, 3), (3, 16, 16, 64, 64, 128, 5), (2, 16, 16, 64, 64, 64, 5),
                                   (2, 16, 16, 64, 0, 128, 1), (1, 32, 32, 128, 0, 64, 3), (5, 8, 32, 64, 0, 64, 3)],
                          ids=lambda c: "B%d_%dx%d_c%d+%d_N%d_R%d" % c if isinstance(c, tuple) else c)
@@ -156,7 +156,10 @@ def test_conv2d_wgrad_packed(be, fb, case, impl):
     rw, rb = dwp0.clone(), db0.clone()
     fb.conv2d_wgrad_packed(x0, x1, dy, R, rw, rb)
     gw, gb = g(dwp0), g(db0)
-    be.conv2d_wgrad_packed(g(x0), g(x1), g(dy), R, gw, gb, impl=CONV_TC if impl == "tc" else CONV_SIMT)
+    if impl == "f16":
+        be.conv2d_wgrad_packed(g(x0), g(x1), g(dy), R, gw, gb, f16=True)
+    else:
+        be.conv2d_wgrad_packed(g(x0), g(x1), g(dy), R, gw, gb, impl=CONV_TC if impl == "tc" else CONV_SIMT)
     torch.cuda.synchronize()
     assert rel_err(gw, rw) < 5e-6 and rel_err(gb, rb) < 5e-6
     dw0 = torch.randn(N, c0 + c1, R, R)
@@ -635,3 +638,86 @@ def test_conv16_is_deterministic(be):
             first = cur
         else:
             assert all(torch.equal(a, b) for a, b in zip(cur, first)), it
+
+
+@pytest.mark.parametrize("sx,sdy", [(1.0, 1e-9), (1e-4, 1e6), (1e5, 1e-3)])
+def test_wgrad_f16_holds_accuracy_at_any_magnitude(be, fb, sx, sdy):
+    """kind::f16 weight gradient: per-tensor power-of-two scales from a device-side max pass keep the fp16 split at fp32-level
+    accuracy for tiny gradients / large activations (and vice versa), with a heavy tail in both operands and an all-zero
+    image in the batch; channel-slice views as operands."""
+    torch.manual_seed(8)
+    B, R, N = 6, 3, 64
+    xw = torch.randn(B, 16, 16, 128) * sx
+    x0 = xw[..., 64:]
+    dy = torch.randn(B, 16, 16, N) * sdy
+    x0[2] = 0.0
+    x0[3, 4, 4, 5] = 500.0 * sx
+    dy[1, 7, 7, 9] = 800.0 * sdy
+    rw, rb = torch.zeros(R * R, N, 64), torch.zeros(N)
+    fb.conv2d_wgrad_packed(x0.double(), None, dy.double(), R, rw, rb)
+    gw, gb = torch.zeros(R * R, N, 64, device="cuda"), torch.zeros(N, device="cuda")
+    be.conv2d_wgrad_packed(g(xw)[..., 64:], None, g(dy), R, gw, gb, f16=True)
+    torch.cuda.synchronize()
+    assert bool(torch.isfinite(gw).all())
+    assert rel_err(gw, rw) < 5e-6 and rel_err(gb, rb) < 5e-6
+
+
+# ---- VidODE torch-side remainder (csrc/vid.cu): BatchNorm(batch statistics) + ReLU, flow warp + composition ---------------------
+@pytest.mark.parametrize("shape", [(4, 32, 32, 32), (6, 64, 16, 24), (2, 128, 32, 32), (3, 24, 7, 9)], ids=str)
+def test_bn_relu_matches_torch(shape):
+    import torch.nn as nn
+    import torch.nn.functional as F
+    from ode_rl_b200 import modules
+
+    torch.manual_seed(1)
+    n, c, h, w = shape
+    bn_a, bn_b = nn.BatchNorm2d(c).cuda(), nn.BatchNorm2d(c).cuda()
+    with torch.no_grad():
+        bn_a.weight.uniform_(0.5, 1.5); bn_a.bias.normal_(0, 0.2)
+    bn_b.load_state_dict(bn_a.state_dict())
+    x = (torch.randn(n, c, h, w, device="cuda") * 3 + 10.0).contiguous(memory_format=torch.channels_last)   # |mean| >> std: the centred sums matter
+    xa, xb = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+    assert modules.bn_relu_supported(xa, bn_a)
+    ya = modules.bn_relu(xa, bn_a)
+    yb = F.relu(bn_b(xb))
+    assert rel_err(ya, yb) < 2e-6
+    wt = torch.randn_like(yb)
+    (ya * wt).sum().backward()
+    (yb * wt).sum().backward()
+    assert rel_err(xa.grad, xb.grad) < 1e-5
+    assert rel_err(bn_a.weight.grad, bn_b.weight.grad) < 1e-5 and rel_err(bn_a.bias.grad, bn_b.bias.grad) < 1e-5
+    assert rel_err(bn_a.running_mean, bn_b.running_mean) < 1e-6 and rel_err(bn_a.running_var, bn_b.running_var) < 1e-5
+    y2 = modules.bn_relu(x, bn_a)                               # deterministic: same input, same bits
+    assert torch.equal(y2, ya.detach())
+
+
+@pytest.mark.parametrize("c,h,w", [(3, 128, 128), (1, 64, 64), (3, 24, 40)])
+def test_warp_compose_matches_torch_grid_sample(c, h, w):
+    import torch.nn.functional as F
+    from ode_rl_b200 import modules
+
+    torch.manual_seed(2)
+    b = 3
+    prev = torch.rand(b, c, h, w, device="cuda")
+    wide = torch.randn(b, h, w, 64, device="cuda")
+    wide[..., :2] *= 6.0                                         # flows of several pixels, some pointing outside (border clamp)
+    head = wide.movedim(-1, 1)[:, :c + 3]                         # the padded decoder head, as the harness passes it
+    lin_x, lin_y = torch.linspace(-1.0, 1.0, w, device="cuda"), torch.linspace(-1.0, 1.0, h, device="cuda")
+    assert modules.warp_compose_supported(prev, head)
+    pa, ha = prev.clone().requires_grad_(True), head.detach().clone().requires_grad_(True)
+    warped, pred = modules.warp_compose(prev, head, lin_x, lin_y)
+    gx = lin_x.view(1, 1, w, 1).expand(b, h, -1, -1)
+    gy = lin_y.view(1, h, 1, 1).expand(b, -1, w, -1)
+    fl = torch.cat([ha[:, 0:1] / ((w - 1.0) / 2.0), ha[:, 1:2] / ((h - 1.0) / 2.0)], dim=1)
+    rw = F.grid_sample(pa, torch.cat([gx, gy], 3) + fl.permute(0, 2, 3, 1), padding_mode="border", align_corners=False)
+    m = torch.sigmoid(ha[:, 2 + c:])
+    rp = m * rw + (1 - m) * ha[:, 2:2 + c]
+    # a rounding difference of 1 ulp in the sampling coordinate (64 px x 2^-23) times the image gradient: 1e-5 of the frame range
+    assert rel_err(warped, rw) < 1e-5 and rel_err(pred, rp) < 1e-5
+    # gradients through the custom node (backward re-derived with torch on the saved operands)
+    p2, h2 = prev.clone().requires_grad_(True), head.detach().clone().requires_grad_(True)
+    w2, q2 = modules.warp_compose(p2, h2, lin_x, lin_y)
+    w1, wq = torch.randn_like(rw), torch.randn_like(rp)
+    ((w2 * w1).sum() + (q2 * wq).sum()).backward()
+    ((rw * w1).sum() + (rp * wq).sum()).backward()
+    assert rel_err(p2.grad, pa.grad) < 1e-5 and rel_err(h2.grad, ha.grad) < 1e-5

@@ -297,7 +297,7 @@ def test_vidode_shapes_encoder_and_solver():
     assert max(errs.values()) < 1e-4, errs
 
 
-@pytest.mark.parametrize("name", ["rk4", "dopri5", "dopri5_x4"])
+@pytest.mark.parametrize("name", ["rk4", "dopri5", "dopri5_x4", "dopri5_128"])
 def test_vidode_golden(name):
     """BASELINE configs[4] wiring (models/VidODE.py) against the fixtures made from the reference's own VidODE submodules:
     128-channel ODEConvGRUCell + DiffEqSolver on the C-ABI path, BN encoder / decoder / grid_sample warp in torch."""
@@ -451,3 +451,25 @@ def test_robustness_cases_on_device():
     from tests.test_host_logic import _robustness_cases
 
     _robustness_cases(odex, DEV, C=64, hw=(16, 16))
+
+
+@pytest.mark.parametrize("method", ["euler", "rk4"])
+def test_long_rollout_stays_within_the_error_growth_bound(method):
+    """The reference evaluates on rollouts of 90-190 predicted frames (configs.yaml:628-630).  100 output times through the
+    fused kind::f16 chain against the CPU oracle: rounding differences of 1e-6 per f-eval may compound over 400 evaluations,
+    and the per-latent error must stay <= 1e-5 x the number of steps taken (linear growth), in fact far below it."""
+    f = make_ode_func(odex, C=64, n_units=64).to(DEV)
+    solver = odex.DiffEqSolver(f, method)
+    import numpy as np
+    tp = torch.tensor(np.arange(10, 110) / 110.0)
+    torch.manual_seed(6)
+    z0 = torch.randn(2, 64, 16, 16)
+    with torch.no_grad():
+        sol = solver(z0.to(DEV), tp.to(DEV))
+        ref = refmodel.diffeq_solver(_sd_cpu(solver), z0, tp, method)
+    errs = [latent_rel(sol[i], ref[i]) for i in range(len(tp))]
+    print(method, "per-latent error at frames 1 / 10 / 50 / 99: %.2e %.2e %.2e %.2e" % (errs[1], errs[10], errs[50], errs[99]))
+    assert errs[0] == 0.0
+    for i, e in enumerate(errs):
+        assert e <= 1e-5 * max(i, 1), (i, e)
+    assert max(errs) < 1e-4

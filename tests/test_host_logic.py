@@ -493,3 +493,51 @@ def test_dt0_detach_deviation_is_of_the_order_of_rtol(rtol, atol):
     gap = float((grads[0] - grads[1]).norm() / grads[1].norm())
     print("dt0 gradient path at rtol %g: relative gap %.2e" % (rtol, gap))
     assert gap < 5 * rtol
+
+
+def test_bn_relu_and_warp_compose_autograd_wiring(fake_backend):
+    """modules.bn_relu (BatchNorm2d batch statistics + ReLU, running-statistics update) and modules.warp_compose (one step of the
+    VidODE flow warp + mask composition) against torch's own modules: values, gradients, module buffers."""
+    import torch.nn as nn
+    import torch.nn.functional as F
+    from ode_rl_b200 import modules
+
+    fake_backend.require = lambda t: None
+    torch.manual_seed(0)
+    bn_a, bn_b = nn.BatchNorm2d(8), nn.BatchNorm2d(8)
+    with torch.no_grad():
+        bn_a.weight.uniform_(0.5, 1.5); bn_a.bias.normal_(0, 0.2)
+    bn_b.load_state_dict(bn_a.state_dict())
+    x = torch.randn(3, 8, 6, 5).contiguous(memory_format=torch.channels_last)
+    xa, xb = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+    ya = modules.bn_relu(xa, bn_a)
+    yb = F.relu(bn_b(xb))
+    assert rel_err(ya, yb) < 1e-6
+    w = torch.randn_like(yb)
+    (ya * w).sum().backward()
+    (yb * w).sum().backward()
+    assert rel_err(xa.grad, xb.grad) < 1e-5
+    assert rel_err(bn_a.weight.grad, bn_b.weight.grad) < 1e-5 and rel_err(bn_a.bias.grad, bn_b.bias.grad) < 1e-5
+    assert rel_err(bn_a.running_mean, bn_b.running_mean) < 1e-6 and rel_err(bn_a.running_var, bn_b.running_var) < 1e-6
+    assert int(bn_a.num_batches_tracked) == 1
+    # warp + compose
+    b, c, h, wd = 2, 3, 8, 10
+    prev = torch.rand(b, c, h, wd)
+    head = torch.randn(b, 8, h, wd)[:, :c + 3]                 # a channel slice of a wider tensor, like the padded decoder head
+    head = head * torch.tensor([3.0, 3.0, 1, 1, 1, 1]).view(1, 6, 1, 1)
+    lin_x, lin_y = torch.linspace(-1.0, 1.0, wd), torch.linspace(-1.0, 1.0, h)
+    pa, ha = prev.clone().requires_grad_(True), head.clone().requires_grad_(True)
+    warped, pred = modules.warp_compose(pa, ha, lin_x, lin_y)
+    pb, hb = prev.clone().requires_grad_(True), head.clone().requires_grad_(True)
+    gx = lin_x.view(1, 1, wd, 1).expand(b, h, -1, -1)
+    gy = lin_y.view(1, h, 1, 1).expand(b, -1, wd, -1)
+    grid = torch.cat([gx, gy], 3)
+    fl = torch.cat([hb[:, 0:1] / ((wd - 1.0) / 2.0), hb[:, 1:2] / ((h - 1.0) / 2.0)], dim=1)
+    rw = F.grid_sample(pb, grid + fl.permute(0, 2, 3, 1), padding_mode="border", align_corners=False)
+    m = torch.sigmoid(hb[:, 2 + c:])
+    rp = m * rw + (1 - m) * hb[:, 2:2 + c]
+    assert rel_err(warped, rw) < 1e-6 and rel_err(pred, rp) < 1e-6
+    w1, w2 = torch.randn_like(rw), torch.randn_like(rp)
+    ((warped * w1).sum() + (pred * w2).sum()).backward()
+    ((rw * w1).sum() + (rp * w2).sum()).backward()
+    assert rel_err(pa.grad, pb.grad) < 1e-5 and rel_err(ha.grad, hb.grad) < 1e-5
