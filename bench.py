@@ -465,6 +465,34 @@ def sub_small_batch(dev, with_cpu=True):
     return out
 
 
+def sub_vidode(dev, B=32):
+    """BASELINE configs[4] inside the default line: VidODE forward (128x128x3, dopri5 at the reference's rtol 1e-4 / atol 1e-5)
+    at the per-GPU batch of the 8-GPU configuration (256 / 8 = 32), device-resident frames.  The full record (e2e, hot-path share,
+    roofline of its top kernel, CPU arm) is `bench.py --workload vidode`."""
+    from ode_rl_b200.harness import VidODEHarness
+    torch.manual_seed(0)
+    model = VidODEHarness("dopri5", device=dev).to(dev)
+    model.device = dev
+    x = torch.rand(B, T_IN, 3, 128, 128, generator=torch.Generator().manual_seed(1234)).to(dev)
+    obs, tp = times(dev)
+    batch = {"observed_tp": obs, "tp_to_predict": tp, "observed_mask": torch.ones(B, T_IN, 1, device=dev),
+             "mask_predicted_data": torch.ones(B, T_OUT, 1, device=dev)}
+
+    def fwd():
+        with torch.no_grad():
+            return model(x, batch)[0]
+
+    sec = _ev_time(fwd, 5, warm=3)
+    st = model.diffeq_solver.last_stats
+    out = {"workload": "cfg5 VidODE dopri5 forward, 128x128x3, batch %d (per-GPU share of batch 256 on 8 GPUs)" % B,
+           "value": B * T_OUT / sec, "unit": "frames/s", "ms_per_forward": sec * 1e3}
+    if st is not None:
+        out.update(n_accept=int(st.n_accept), n_reject=int(st.n_reject), n_feval=int(st.n_feval))
+    del model, x
+    torch.cuda.empty_cache()
+    return out
+
+
 def sub_rk_kernels(dev, be, hbm, batches=(512, 2048)):
     """Achieved GB/s (algorithmic bytes of SURVEY.md 8d / kernel time) of the dopri5 kernels north_star names: K4 =
     dopri_errnorm_kernel (error estimate + RMS norm + accept/reject + controller in one launch: 8 planes read = 32 B/elem) and
@@ -837,7 +865,8 @@ def main():
     if rank == 0 and not args.no_extras and args.method != "dopri5" and not args.forward_only:
         for name, fn in (("dopri5", lambda: sub_dopri5(dev)),
                          ("small_batch", lambda: sub_small_batch(dev, with_cpu=not args.no_cpu_baseline and world == 1)),
-                         ("rk_kernels", lambda: sub_rk_kernels(dev, be, float(peaks.get("hbm_gbs", 6650.0))))):
+                         ("rk_kernels", lambda: sub_rk_kernels(dev, be, float(peaks.get("hbm_gbs", 6650.0)))),
+                         ("vidode", lambda: sub_vidode(dev))):
             try:
                 extras[name] = fn()
             except Exception as e:

@@ -163,7 +163,7 @@ wgrad_f16_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
     if (threadIdx.x == 0) {
         for (int i = 0; i < S; ++i) {
             mbar_init(bar_raw_full + 8 * i, 1);
-            mbar_init(bar_split_full + 8 * i, 256);
+            mbar_init(bar_split_full + 8 * i, 128);
             mbar_init(bar_stage_empty + 8 * i, 1);
         }
         mbar_init(bar_acc, 1);
@@ -249,12 +249,12 @@ wgrad_f16_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
         __syncwarp();
     } else {
         // ===================== operand preparation (8 warps), then epilogue (the first 4 of them) =====================
-        // thread <-> TMEM lane L = 32 * (warp % 4) + lane: dy channel n = L % 64, part = L / 64 (0: hi rows, 1: lo rows); the two
-        // warps of a lane quadrant take 32 of the tile's 64 pixels each.  With one warp per scheduler the fp32 -> fp16 transform,
-        // not the halved MMA time, bounded a tile (2.0 k cycles against 0.77 k of math): two warps per scheduler.
-        const int tid = threadIdx.x - 64;                 // 0..255
+        // thread <-> TMEM lane L = 32 * (warp % 4) + lane: dy channel n = L % 64, part = L / 64 (0: hi rows, 1: lo rows).  The
+        // preparation of a tile is a latency chain that did not overlap the MMAs of the previous one (tools/wgrad_probe.py);
+        // two groups of four warps take alternate tiles, so each chain spans two tile periods.
+        const int grp = (warp - 2) >> 2;                  // two groups of four warps take alternate tiles (see wgrad_tc.cu)
+        const int tid = (threadIdx.x - 64) & 127;         // 0..127 within the group
         const int q = warp & 3;
-        const int khalf = (warp - 2) >> 2;                // which 32 pixels of the tile
         const int L = q * 32 + lane;
         const int n = L & 63;
         const int part = L >> 6;
@@ -269,6 +269,7 @@ wgrad_f16_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
         const int xhalf = tid & 1;                        // X: a lane pair owns a pixel slot, one 32-channel raw plane each
         int it = 0;
         for (int t = ps; t < g.ntiles; t += g.PS, ++it) {
+            if ((it & 1) != grp) continue;
             const int st = it % S;
             const uint32_t use = static_cast<uint32_t>(it / S);
             mbar_wait(bar_raw_full + 8 * st, use & 1u);
@@ -277,7 +278,7 @@ wgrad_f16_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
             // ---- X: slot i holds 32 + 32 fp32 channels in the two raw planes; it becomes 64 fp16 hi (plane 0) + 64 fp16 lo
             // (plane 1), in place: both lanes of the pair read their raw plane, then (after __syncwarp) write their half rows
 #pragma unroll 1
-            for (int i0_ = 0; i0_ < hrows; i0_ += 128) {
+            for (int i0_ = 0; i0_ < hrows; i0_ += 64) {
                 const int i = i0_ + (tid >> 1);
                 const bool ok = i < hrows;
                 const uint32_t row = xs + static_cast<uint32_t>(ok ? i : 0) * 128u;
@@ -311,13 +312,13 @@ wgrad_f16_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
             }
             // ---- dy: this lane's channel at 32 of the tile's pixels -> A operand row in TMEM (K-major, two pixels per column)
             tc_fence_after_sync();
-            uint32_t a[16];
+            uint32_t a[32];
 #pragma unroll
-            for (int k0 = 0; k0 < 32; k0 += 16) {
+            for (int k0 = 0; k0 < 64; k0 += 16) {
                 uint32_t v[16];
 #pragma unroll
                 for (int b = 0; b < 16; ++b) {
-                    const uint32_t k = static_cast<uint32_t>(32 * khalf + k0 + b);
+                    const uint32_t k = static_cast<uint32_t>(k0 + b);
                     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v[b]) : "r"(ds + k * 128u + ((dy_chunk ^ (k & 7u)) << 4)));
                 }
 #pragma unroll
@@ -333,14 +334,14 @@ wgrad_f16_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
                     a[(k0 + b) >> 1] = *reinterpret_cast<const uint32_t*>(&outv);        // low half = the even pixel
                 }
             }
-            tmem_st16(tmem_base + lane_addr + a_col0 + static_cast<uint32_t>(st) * 32u + static_cast<uint32_t>(khalf) * 16u, a);
+            tmem_st32(tmem_base + lane_addr + a_col0 + static_cast<uint32_t>(st) * 32u, a);
             tmem_st_wait();
             tc_fence_before_sync();
             fence_proxy_async_smem();
             mbar_arrive(bar_split_full + 8 * st);
         }
         if (do_db) atomicAdd(g.db + nb * 64 + n, dbsum);
-        if (khalf == 0) {
+        if (grp == 0) {
         mbar_wait(bar_acc, 0u);             // every MMA has completed: the stage buffers are free as well
         tc_fence_after_sync();
 
