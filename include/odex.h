@@ -115,6 +115,11 @@ int odex_wgrad_unpack(const float* dwp, int N, int C, int R, float* dw, odex_str
  * kernel (c0, c1, N % 64 == 0, W % 16 == 0, H % 4 == 0, R in {1,3,5}). */
 int odex_conv2d_wgrad_f16(const float* x0, int ld0, int c0, const float* x1, int ld1, int c1, const float* dy, int ldy,
                           int B, int H, int W, int R, int N, float* dwp, float* db, float* scratch2, odex_stream_t s);
+/* The same kernel when the caller already holds upper bounds of the two maxima: amax2 = {>= max |X|, >= max |dy|} in device
+ * memory (e.g. accumulated by odex_convnet through odex_convnet_desc.amax_out while it produced the operands).  No max pass.
+ * A bound up to ~2^9 above the true maximum costs no accuracy (the lo term resolves 2^-24 absolute against 2^13). */
+int odex_conv2d_wgrad_f16_scaled(const float* x0, int ld0, int c0, const float* x1, int ld1, int c1, const float* dy, int ldy,
+                                 int B, int H, int W, int R, int N, float* dwp, float* db, const float* amax2, odex_stream_t s);
 
 /* ------------------------------------------------------------------------------------------------ fused conv chain
  * A chain of L 3x3 C->C convolutions (C = 64) over 16x16 images in ONE launch, the image resident in shared memory

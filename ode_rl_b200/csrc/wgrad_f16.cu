@@ -428,12 +428,12 @@ bool wgrad_f16_supported(int c0, int c1, int N, int H, int W, int R) {
 }
 
 int launch_wgrad_f16(const float* x0, int ld0, int c0, const float* x1, int ld1, int c1, const float* dy, int ldy, int B,
-                     int H, int W, int R, int N, float* dwp, float* db, float* scratch2, cudaStream_t s) {
+                     int H, int W, int R, int N, float* dwp, float* db, float* scratch2, const float* amax_ready, cudaStream_t s) {
     if (!w16_encode_fn()) return fail(ODEX_E_DRIVER, "cuTensorMapEncodeTiled not available from the driver");
-    // ---- per-tensor maxima -> scratch2
+    // ---- per-tensor maxima -> scratch2 (unless the caller has upper bounds of them already)
     const long P = static_cast<long>(B) * H * W;
-    cudaMemsetAsync(scratch2, 0, 2 * sizeof(float), s);
-    {
+    if (!amax_ready) {
+        cudaMemsetAsync(scratch2, 0, 2 * sizeof(float), s);
         const long work = P * ((c0 + c1 + N) / 4);
         const int blocks = static_cast<int>(std::min<long>((work + 1023) / 1024, 8L * kSMs));
         launch_pdl(absmax2_kernel, blocks, 256, 0, s, x0, ld0, c0, x1, ld1, c1, dy, ldy, N, P, scratch2);
@@ -447,14 +447,17 @@ int launch_wgrad_f16(const float* x0, int ld0, int c0, const float* x1, int ld1,
     const int hrows = (kW16TH + 2 * pad) * Pp;
     g.xplane = (hrows * 128 + 1023) / 1024 * 1024;
     const int taps = R * R;
-    g.taps_per_group = R;                       // 1, 3 or 5 taps x 64 TMEM columns
-    g.TG = taps / g.taps_per_group;
+    // taps x 64 accumulator columns + stages x 32 operand columns <= 512: up to 6 taps per CTA.  3x3: 5 + 4 instead of 3 + 3 + 3
+    // -- a tile's load and fp16 conversion then feed 40 / 32 MMAs instead of 24 and are repeated by 2 CTAs instead of 3
+    static const int taps3 = getenv("ODEX_W16_TAPS3") ? atoi(getenv("ODEX_W16_TAPS3")) : 5;
+    g.taps_per_group = R == 3 ? std::max(1, std::min(6, taps3)) : R;
+    g.TG = (taps + g.taps_per_group - 1) / g.taps_per_group;
     g.CG = g.Ctot / 64;
     g.NB = N / 64;
     g.ntiles = B * (H / kW16TH) * (W / kW16TW);
     const int units = g.TG * g.CG * g.NB;
     g.PS = std::max(1, std::min(g.ntiles, kSMs / units));
-    g.dwp = dwp; g.db = db; g.amax = scratch2;
+    g.dwp = dwp; g.db = db; g.amax = amax_ready ? amax_ready : scratch2;
     const int stages = R <= 3 ? 4 : 3;
     const int smem = 1024 + std::max(stages * (2 * g.xplane + 2 * kW16DyPlane), 32768) + 128;
     if (smem > 232448) return fail(ODEX_E_UNSUPPORTED, "wgrad(f16): needs %d bytes of shared memory", smem);
@@ -494,5 +497,18 @@ extern "C" int odex_conv2d_wgrad_f16(const float* x0, int ld0, int c0, const flo
     if (B <= 0 || (x1 == nullptr) != (c1 == 0)) return fail(ODEX_E_ARG, "wgrad_f16: bad batch / second source");
     if (!wgrad_f16_supported(c0, c1, N, H, W, R))
         return fail(ODEX_E_UNSUPPORTED, "wgrad_f16: shape not supported (c0=%d c1=%d N=%d HxW=%dx%d R=%d)", c0, c1, N, H, W, R);
-    return launch_wgrad_f16(x0, ld0, c0, x1, ld1, c1, dy, ldy, B, H, W, R, N, dwp, db, scratch2, s);
+    return launch_wgrad_f16(x0, ld0, c0, x1, ld1, c1, dy, ldy, B, H, W, R, N, dwp, db, scratch2, nullptr, s);
+}
+
+extern "C" int odex_conv2d_wgrad_f16_scaled(const float* x0, int ld0, int c0, const float* x1, int ld1, int c1, const float* dy,
+                                            int ldy, int B, int H, int W, int R, int N, float* dwp, float* db,
+                                            const float* amax2, odex_stream_t s_) {
+    cudaStream_t s = static_cast<cudaStream_t>(s_);
+    if (!x0 || !dy || !dwp || !amax2) return fail(ODEX_E_ARG, "wgrad_f16_scaled: null pointer");
+    if (!aligned16(x0) || !aligned16(dy) || (x1 && !aligned16(x1)) || ld0 % 4 || ldy % 4 || (x1 && ld1 % 4))
+        return fail(ODEX_E_ALIGN, "wgrad_f16_scaled: pointers / strides must be 16-byte aligned");
+    if (B <= 0 || (x1 == nullptr) != (c1 == 0)) return fail(ODEX_E_ARG, "wgrad_f16_scaled: bad batch / second source");
+    if (!wgrad_f16_supported(c0, c1, N, H, W, R))
+        return fail(ODEX_E_UNSUPPORTED, "wgrad_f16_scaled: shape not supported (c0=%d c1=%d N=%d HxW=%dx%d R=%d)", c0, c1, N, H, W, R);
+    return launch_wgrad_f16(x0, ld0, c0, x1, ld1, c1, dy, ldy, B, H, W, R, N, dwp, db, nullptr, amax2, s);
 }

@@ -366,12 +366,14 @@ class Backend:
             and os.environ.get("ODEX_NO_WGRAD16") is None
 
     def conv2d_wgrad_packed(self, x0: torch.Tensor, x1: Optional[torch.Tensor], dy: torch.Tensor, R: int,
-                            dwp: torch.Tensor, db: Optional[torch.Tensor], impl: int = CONV_AUTO, f16: bool = False) -> None:
+                            dwp: torch.Tensor, db: Optional[torch.Tensor], impl: int = CONV_AUTO, f16: bool = False,
+                            amax: Optional[torch.Tensor] = None) -> None:
         """odex_conv2d_wgrad_packed: dwp [R*R, N, c0+c1] += dy^T X (tensor-core kernel where the shape allows),
         db += colsum(dy).  f16: the kind::f16 kernel with the two-term fp16 split (odex_conv2d_wgrad_f16) where its shape test
-        passes."""
+        passes.  amax: 2 device floats {>= max |X|, >= max |dy|} the caller already holds (odex_conv2d_wgrad_f16_scaled: the
+        same kernel without its max pass)."""
         B, H, W, c0 = x0.shape
-        if f16 and impl == CONV_AUTO and self.wgrad_f16_shape_ok(c0, 0 if x1 is None else x1.shape[3], dy.shape[3], H, W, R):
+        if (f16 or amax is not None) and impl == CONV_AUTO and self.wgrad_f16_shape_ok(c0, 0 if x1 is None else x1.shape[3], dy.shape[3], H, W, R):
             p0, ld0 = _rows(x0)
             p1, ld1, c1 = None, 0, 0
             if x1 is not None:
@@ -380,6 +382,11 @@ class Backend:
             pdy, ldy = _rows(dy)
             N = dy.shape[3]
             assert dwp.is_contiguous() and tuple(dwp.shape) == (R * R, N, c0 + c1), (tuple(dwp.shape), (R * R, N, c0 + c1))
+            if amax is not None:
+                assert amax.dtype == torch.float32 and amax.numel() == 2 and amax.is_contiguous()
+                _lib.check(self.lib.odex_conv2d_wgrad_f16_scaled(p0, ld0, c0, p1, ld1, c1, pdy, ldy, B, H, W, R, N, dwp.data_ptr(),
+                                                                 _ptr(db), amax.data_ptr(), _stream()), "odex_conv2d_wgrad_f16_scaled")
+                return
             scratch = torch.empty(2, dtype=torch.float32, device=x0.device)
             _lib.check(self.lib.odex_conv2d_wgrad_f16(p0, ld0, c0, p1, ld1, c1, pdy, ldy, B, H, W, R, N, dwp.data_ptr(),
                                                       _ptr(db), scratch.data_ptr(), _stream()), "odex_conv2d_wgrad_f16")

@@ -57,6 +57,7 @@ class FakeBackend:
 
     def __init__(self):
         self.launches = 0
+        self.wgrad_scaled = 0
 
     @staticmethod
     def require(t):
@@ -178,9 +179,13 @@ class FakeBackend:
         if db is not None:
             db += dy.sum((0, 1, 2))
 
-    def conv2d_wgrad_packed(self, x0, x1, dy, R, dwp, db, impl=0, f16=False):
+    def conv2d_wgrad_packed(self, x0, x1, dy, R, dwp, db, impl=0, f16=False, amax=None):
         self.launches += 1
         x = x0 if x1 is None else torch.cat((x0, x1), 3)
+        if amax is not None:            # the scaled kernel trusts these bounds: a too-small one would overflow its fp16 operands
+            self.wgrad_scaled += 1
+            assert float(amax[0]) >= float(x.abs().max()) and float(amax[1]) >= float(dy.abs().max()), \
+                ("wgrad maxima are not upper bounds", amax.tolist(), float(x.abs().max()), float(dy.abs().max()))
         N, Cc = dy.shape[3], x.shape[3]
         g = torch.nn.grad.conv2d_weight(x.permute(0, 3, 1, 2).contiguous(), (N, Cc, R, R),
                                         dy.permute(0, 3, 1, 2).contiguous(), padding=(R - 1) // 2)
