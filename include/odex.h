@@ -223,6 +223,18 @@ int odex_bn_relu_fwd(const float* x, long long M, int C, const float* gamma, con
                      float* stats, float* scratch, long long scratch_floats, odex_stream_t s);
 int odex_bn_relu_bwd(const float* x, const float* y, const float* dy, long long M, int C, const float* gamma, const float* stats,
                      int relu, float* dx, float* dgamma_dbeta, float* scratch, long long scratch_floats, odex_stream_t s);
+/* odex_bn_relu_fwd for callers that cannot allocate (code under CUDA-graph capture, serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.  Same arguments and results as
+ * odex_bn_relu_fwd minus the scratch buffer: the slab statistics go through a `static __device__` array inside the library
+ * (odex_bn_static_scratch_floats() = 151 552 floats = 592 KiB, held by every GPU that loads the library until the process
+ * exits), whose device address is resolved once per device with cudaGetSymbolAddress.  Calls no cudaMalloc / cudaFree or any
+ * allocating routine.  Limit: 2 * nblocks * C <= 151 552 with nblocks = ceil(M / max(64, ceil(M / 592))), i.e. every M for
+ * C <= 128 and M <= 18 944 rows (296 slabs) for C = 256; beyond it returns ODEX_E_UNSUPPORTED with a message.  All calls on a
+ * device share the one array (nothing in it has to start at zero: a call writes every slot it reads): calls that overlap on
+ * the GPU -- different streams, or graph branches -- race; serialise them on one stream. */
+long long odex_bn_static_scratch_floats(void);
+int odex_bn_relu_fwd_static(const float* x, long long M, int C, const float* gamma, const float* beta, float eps, int relu,
+                            float* y, float* stats, odex_stream_t s);
 /* One step of the recursive flow warp + mask composition of models/VidODE.py:121-131,162-186:
  *   warped = grid_sample(prev, grid + flow / ((size - 1) / 2), bilinear, padding_mode = 'border', align_corners = False)
  *   pred   = sigmoid(mask) * warped + (1 - sigmoid(mask)) * intermediate

@@ -131,6 +131,8 @@ SIGNATURES = {
     "odex_encode_stem_bwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _f, _vp, _vp, _vp]),
     "odex_bn_scratch_floats": (_ll, [_ll, _i]),
     "odex_bn_relu_fwd": (_i, [_vp, _ll, _i, _vp, _vp, _f, _i, _vp, _vp, _vp, _ll, _vp]),
+    "odex_bn_static_scratch_floats": (_ll, []),
+    "odex_bn_relu_fwd_static": (_i, [_vp, _ll, _i, _vp, _vp, _f, _i, _vp, _vp, _vp]),
     "odex_bn_relu_bwd": (_i, [_vp, _vp, _vp, _ll, _i, _vp, _vp, _i, _vp, _vp, _vp, _ll, _vp]),
     "odex_warp_compose_fwd": (_i, [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp]),
     "odex_upsample2x_fwd": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),

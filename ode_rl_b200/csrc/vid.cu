@@ -7,6 +7,8 @@
 //     pred = sigmoid(m) * warped + (1 - sigmoid(m)) * intermediate, read straight from the decoder head's NHWC output.
 // Plain CUDA: 128-bit accesses, grids a multiple of the 148 SMs, deterministic two-level reductions (no atomics on the
 // statistics), each operand plane read once.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace odex {
@@ -283,6 +285,63 @@ extern "C" int odex_bn_relu_fwd(const float* x, long long M, int C, const float*
     int nblocks;
     const long rpb = bn_rows_per_block(M, &nblocks);
     if (scratch_floats < 2LL * nblocks * C) return fail(ODEX_E_ARG, "bn_relu_fwd: scratch needs %lld floats", 2LL * nblocks * C);
+    const int smem = kBnThreads * 4 * static_cast<int>(sizeof(float));
+    bn_slab_stats_kernel<<<nblocks, kBnThreads, smem, s>>>(x, M, C, rpb, scratch);
+    if (int rc = launched("bn_slab_stats_kernel")) return rc;
+    bn_finish_stats_kernel<<<C, 128, 0, s>>>(scratch, nblocks, M, rpb, C, eps, stats);
+    if (int rc = launched("bn_finish_stats_kernel")) return rc;
+    const long n4 = M * (C / 4);
+    const int blocks = static_cast<int>(std::min<long>((n4 + 255) / 256, 8L * kSMs));
+    bn_relu_apply_kernel<<<blocks, 256, 0, s>>>(x, stats, gamma, beta, M, C, relu, y);
+    return launched("bn_relu_apply_kernel");
+}
+
+// ---- odex_bn_relu_fwd without a caller-provided scratch buffer (no counterpart in the reference; added
+// for callers that cannot allocate: CUDA-graph capture, serving loops, harnesses that forbid cudaMalloc).
+// The slab statistics go through this file-scope array instead: 2 * 592 * 128 floats = 592 KiB, resident on every GPU that
+// loads the library until the process exits.  In host code `g_bn_static_scratch` is only a stand-in for the symbol: its device
+// address is taken once per device with cudaGetSymbolAddress (that device current) and that pointer is what the kernels get.
+constexpr long long kBnStaticFloats = 2LL * 4 * kSMs * 128;
+static __device__ __align__(256) float g_bn_static_scratch[kBnStaticFloats];
+
+static int bn_static_scratch_ptr(float** out) {
+    constexpr int kMaxDev = 64;
+    static float* ptrs[kMaxDev] = {};
+    static std::mutex mu;
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return fail(-static_cast<int>(e), "bn_relu_fwd_static: cudaGetDevice: %s", cudaGetErrorString(e));
+    if (dev < 0 || dev >= kMaxDev) return fail(ODEX_E_ARG, "bn_relu_fwd_static: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptrs[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_bn_static_scratch);
+        if (e != cudaSuccess || !p)
+            return fail(-static_cast<int>(e), "bn_relu_fwd_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+        ptrs[dev] = static_cast<float*>(p);
+    }
+    *out = ptrs[dev];
+    return 0;
+}
+
+extern "C" long long odex_bn_static_scratch_floats(void) { return kBnStaticFloats; }
+
+extern "C" int odex_bn_relu_fwd_static(const float* x, long long M, int C, const float* gamma, const float* beta, float eps,
+                                       int relu, float* y, float* stats, odex_stream_t s_) {
+    cudaStream_t s = static_cast<cudaStream_t>(s_);
+    if (!x || !y || !gamma || !beta || !stats || M <= 0) return fail(ODEX_E_ARG, "bn_relu_fwd_static: bad argument");
+    if (C % 4 != 0 || C < 4 || C > 256) return fail(ODEX_E_SHAPE, "bn_relu_fwd_static: C must be a multiple of 4 in [4, 256] (got %d)", C);
+    if (!aligned16(x) || !aligned16(y) || !aligned16(gamma) || !aligned16(beta) || !aligned16(stats))
+        return fail(ODEX_E_ALIGN, "bn_relu_fwd_static: pointers must be 16-byte aligned");
+    int nblocks;
+    const long rpb = bn_rows_per_block(M, &nblocks);
+    const long long need = 2LL * nblocks * C;
+    if (need > kBnStaticFloats)
+        return fail(ODEX_E_UNSUPPORTED, "bn_relu_fwd_static: M=%lld C=%d needs %lld floats of scratch, the built-in array holds %lld "
+                    "(use odex_bn_relu_fwd with a caller-provided buffer)", M, C, need, kBnStaticFloats);
+    float* scratch = nullptr;
+    if (int rc = bn_static_scratch_ptr(&scratch)) return rc;
+    // every slot the finish kernel reads (2 * nblocks * C) is written by the slab kernel of the same call: nothing to clear
     const int smem = kBnThreads * 4 * static_cast<int>(sizeof(float));
     bn_slab_stats_kernel<<<nblocks, kBnThreads, smem, s>>>(x, M, C, rpb, scratch);
     if (int rc = launched("bn_slab_stats_kernel")) return rc;
