@@ -146,6 +146,10 @@ typedef struct odex_convnet_desc {
     int split;                                  /* 0: w_tc are odex_pack_weights(tc = 1) blobs, 3xTF32 on tcgen05 kind::tf32;
                                                    1: w_tc are odex_pack_weights(tc = 2) blobs, two-term fp16 split on kind::f16
                                                       (same 22 significant bits per operand, twice the MMA rate) */
+    float* amax_out[ODEX_NET_MAX_LAYERS];       /* split = 1 only, each nullable: *amax_out[l] = max(*amax_out[l], max |a_l|) over the
+                                                   launch's images (a_0 = x, a_l = v_{l-1}), atomically; the caller zeroes them.
+                                                   These are the operands of the layers' weight gradients: odex_conv2d_wgrad_f16_scaled
+                                                   takes them instead of running a max pass.  split = 0 rejects a non-NULL entry. */
 } odex_convnet_desc;
 int odex_convnet(const odex_convnet_desc* d, odex_stream_t s);
 int odex_convnet_supported(const odex_convnet_desc* d);

@@ -60,6 +60,7 @@ class ConvNetDesc(C.Structure):
         ("alpha", C.c_float), ("alpha_dev", C.c_void_p),
         ("skip", C.c_void_p),
         ("split", C.c_int),
+        ("amax_out", C.c_void_p * NET_MAX_LAYERS),
     ]
 
 

@@ -57,6 +57,7 @@ struct F16Args {
     float alpha;
     const double* alpha_dev;
     const int* skip;
+    float* amax_out[kF16MaxL];      // nullable: atomic max of max |input of layer l| over the launch's images (non-negative float bits)
     long long* dbg;
 };
 
@@ -308,6 +309,13 @@ convnet_f16_kernel(const __grid_constant__ F16Maps tm, const F16Args a) {
             }
         }
         if (tid == 0) tma_store_wait_read();
+        // maxima of the chain input and of the outputs of layers 0 .. L-2 (all final since the last layer's closing bar.sync): the
+        // operands of the weight gradients, whose kind::f16 kernel then needs no max pass of its own
+        if (tid < L && a.amax_out[tid]) {
+            uint32_t mb;
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(mb) : "r"(amax_s + 4u * tid));
+            atomicMax(reinterpret_cast<unsigned int*>(a.amax_out[tid]), mb);
+        }
         tc_fence_before_sync();
         if (a.dbg && blockIdx.x == 0 && tid == 0) a.dbg[0] = clock64() - t_start;
     }
@@ -380,6 +388,7 @@ int launch_convnet_f16(const odex_convnet_desc* d, cudaStream_t s) {
         a.store[l] = on && d->out[l] ? 1 : 0;
         a.bias[l] = on ? d->bias[l] : nullptr;
         a.wtail[l] = on ? d->w_tc[l] + kRowsFloats : nullptr;
+        a.amax_out[l] = on ? d->amax_out[l] : nullptr;
         tm.w[l] = tm.x; tm.aux[l] = tm.x; tm.out[l] = tm.x;
         if (!on) continue;
         {

@@ -422,6 +422,8 @@ extern "C" int odex_convnet(const odex_convnet_desc* d, odex_stream_t s_) {
     if (!d) return fail(ODEX_E_ARG, "convnet: null descriptor");
     if (d->split == 1) return launch_convnet_f16(d, s);
     if (d->split != 0) return fail(ODEX_E_ARG, "convnet: unknown operand split %d", d->split);
+    for (int l = 0; l < ODEX_NET_MAX_LAYERS; ++l)
+        if (d->amax_out[l]) return fail(ODEX_E_ARG, "convnet: amax_out needs split = 1 (the kind::f16 chain measures the maxima anyway)");
     if (!net_supported(d))
         return fail(ODEX_E_UNSUPPORTED, "convnet: shape not supported (B=%d HxW=%dx%d C=%d L=%d; needs 16x16, C=64, L<=%d, packed tc weights)",
                     d->B, d->H, d->W, d->C, d->L, kNetMaxL);

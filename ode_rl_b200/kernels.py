@@ -137,7 +137,7 @@ class Backend:
             _lib.check(self.lib.odex_conv2d(C.byref(d), _stream()), "odex_conv2d")
         return out
 
-    def _convnet_desc(self, x, w_tc, bias, act, aux, aux_kind, out, alpha, alpha_dev, skip, split=0):
+    def _convnet_desc(self, x, w_tc, bias, act, aux, aux_kind, out, alpha, alpha_dev, skip, split=0, amax_out=None):
         d = _lib.ConvNetDesc()
         d.split = int(split)
         B, H, W, Cc = x.shape
@@ -154,6 +154,12 @@ class Backend:
             if out[l] is not None:
                 assert tuple(out[l].shape) == (B, H, W, Cc)
                 d.out[l], d.ld_out[l] = _rows(out[l])
+        if amax_out is not None:
+            assert split == 1, "amax_out needs the kind::f16 chain"
+            for l, t in enumerate(amax_out):
+                if t is not None:
+                    assert t.dtype == torch.float32 and t.numel() == 1 and t.device == x.device
+                    d.amax_out[l] = t.data_ptr()
         d.alpha = float(alpha)
         d.alpha_dev = _ptr(alpha_dev)
         d.skip = _ptr(skip)
@@ -168,12 +174,14 @@ class Backend:
     def convnet(self, x: torch.Tensor, w_tc: Sequence[torch.Tensor], bias: Sequence[Optional[torch.Tensor]],
                 act: Sequence[int], aux: Sequence[Optional[torch.Tensor]], aux_kind: Sequence[int],
                 out: Sequence[Optional[torch.Tensor]], alpha: float = 1.0, alpha_dev: Optional[torch.Tensor] = None,
-                skip: Optional[torch.Tensor] = None, split: int = 0) -> None:
+                skip: Optional[torch.Tensor] = None, split: int = 0,
+                amax_out: Optional[Sequence[Optional[torch.Tensor]]] = None) -> None:
         """odex_convnet: the whole conv chain in one launch; layer l: v = act(conv(a_l) + bias), v *= act'(aux) (kind 1/2)
         or v = aux + alpha * v (kind 3), stored to out[l] when given (out[-1] required).  split: 0 = w_tc packed with tc = 1
-        (3xTF32), 1 = packed with tc = 2 (two-term fp16 split on kind::f16)."""
+        (3xTF32), 1 = packed with tc = 2 (two-term fp16 split on kind::f16).  amax_out[l] (split = 1): one-element fp32 tensor
+        that receives max(itself, max |input of layer l|), atomically."""
         self.require(x)
-        d = self._convnet_desc(x, w_tc, bias, act, aux, aux_kind, out, alpha, alpha_dev, skip, split)
+        d = self._convnet_desc(x, w_tc, bias, act, aux, aux_kind, out, alpha, alpha_dev, skip, split, amax_out)
         _lib.check(self.lib.odex_convnet(C.byref(d), _stream()), "odex_convnet")
 
     # ------------------------------------------------------------------ image-resident conv (+ fused ConvGRU gates), kind::f16

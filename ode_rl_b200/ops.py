@@ -45,6 +45,19 @@ def _wgrad_f16() -> bool:
     return os.environ.get("ODEX_WGRAD_SPLIT", "tf32").lower() == "f16" and CONV_IMPL != "simt"
 
 
+def _wgrad_scaled() -> bool:
+    """Weight gradients of the fused ODE-function chain on the kind::f16 kernel WITHOUT its max pass (odex_conv2d_wgrad_f16_scaled):
+    the chain kernels measure max |a_l| / max |d_l| of every layer's operands anyway and leave them in a maxima buffer the caller
+    of ConvNetOp.fwd provides (odex_convnet_desc.amax_out).  Default on; ODEX_WGRAD_SCALED=0 keeps the 3xTF32 kernel."""
+    return os.environ.get("ODEX_WGRAD_SCALED", "1") != "0" and CONV_IMPL != "simt"
+
+
+class SavedActs(list):
+    """The activations ConvNetOp.fwd(save=True) keeps for the backward, plus the [L, 2] maxima buffer their max |a_l| went into
+    (column 0; the backward adds max |d_l| in column 1).  None: not measured."""
+    maxima: Optional[torch.Tensor] = None
+
+
 def set_conv_impl(name: str) -> str:
     global CONV_IMPL
     assert name in ("auto", "simt", "tc")
@@ -104,27 +117,34 @@ class GradSink:
         self._pending: Dict[int, Tuple[nn.Conv2d, list]] = {}
         self.deferred = False                           # True: add_wgrad only records; flush() launches, batched
 
-    def add_wgrad(self, conv: nn.Conv2d, x: torch.Tensor, dy: torch.Tensor) -> None:
+    def add_wgrad(self, conv: nn.Conv2d, x: torch.Tensor, dy: torch.Tensor, amax=None) -> None:
         """dW(conv) += x^T dy, db += colsum(dy).  While `deferred`, the request is only recorded: weight gradients are off
         the critical path of a backward pass, and requests whose operands are consecutive slices of one buffer (the RK
-        stages of a step, allocated as [s, B, ...] arenas) run as ONE launch over s*B images."""
+        stages of a step, allocated as [s, B, ...] arenas) run as ONE launch over s*B images.
+        amax: 2 device floats {>= max |x|, >= max |dy|} (a row of a maxima buffer the chain kernels filled); such requests run on
+        the kind::f16 kernel without a max pass, and only requests that share the row merge."""
         if (conv.weight is None or not conv.weight.requires_grad) and (conv.bias is None or not conv.bias.requires_grad):
             return
         if not self.deferred:
-            self._launch(conv, x, dy)
+            self._launch(conv, x, dy, amax)
         else:
-            self._pending.setdefault(id(conv.weight), (conv, []))[1].append((x, dy))
+            self._pending.setdefault(id(conv.weight), (conv, []))[1].append((x, dy, amax))
 
-    def _launch(self, conv: nn.Conv2d, x: torch.Tensor, dy: torch.Tensor) -> None:
+    def _launch(self, conv: nn.Conv2d, x: torch.Tensor, dy: torch.Tensor, amax=None) -> None:
         gw, gb = self.get_packed(conv.weight), self.get(conv.bias)
         if gw is None:          # bias-only gradient: the kernel still needs a dw target
             gw = _scratch_packed(conv.weight)
-        K.backend().conv2d_wgrad_packed(x, None, dy, conv.kernel_size[0], gw, gb, f16=_wgrad_f16())
+        K.backend().conv2d_wgrad_packed(x, None, dy, conv.kernel_size[0], gw, gb, f16=_wgrad_f16(), amax=amax)
 
     def flush(self) -> None:
         for conv, items in self._pending.values():
-            for x, dy in _slice_runs(items):
-                self._launch(conv, x, dy)
+            # requests measured into the same maxima row merge among themselves (one kind::f16 launch per run), the rest likewise
+            groups: Dict[object, list] = {}
+            for x, dy, amax in items:
+                groups.setdefault(None if amax is None else amax.data_ptr(), []).append((x, dy, amax))
+            for group in groups.values():
+                for x, dy in _slice_runs([(x, dy) for x, dy, _ in group]):
+                    self._launch(conv, x, dy, group[0][2])
         self._pending.clear()
 
     def get_packed(self, w: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
@@ -296,6 +316,17 @@ class ConvNetOp:
         self.c_in = self.layers[0][0].in_channels
         self.c_out = self.layers[-1][0].out_channels
 
+    def new_maxima(self, x: torch.Tensor) -> Optional[torch.Tensor]:
+        """A zeroed [L, 2] maxima buffer for fwd(save=True, maxima=...) when the weight gradients of this chain can use it
+        (fused kind::f16 chain + odex_conv2d_wgrad_f16_scaled), else None.  Row l = {max |a_l|, max |d_l|} over every launch
+        that is given the buffer, so share one only between launches whose operands have the same order of magnitude (the
+        stages of one RK step): a bound far above a launch's own maximum pushes its fp16 operands towards underflow."""
+        if CONV_SPLIT != "f16" or not _wgrad_scaled() or not self._fused(K.backend(), x):
+            return None
+        if not K.backend().wgrad_f16_shape_ok(64, 0, 64, x.shape[1], x.shape[2], 3):
+            return None
+        return torch.zeros((len(self.layers), 2), dtype=torch.float32, device=x.device)
+
     def params(self) -> List[torch.Tensor]:
         ps = []
         for conv, _ in self.layers:
@@ -321,15 +352,20 @@ class ConvNetOp:
     def fwd(self, x: torch.Tensor, save: bool = False, out: Optional[torch.Tensor] = None,
             res: Optional[torch.Tensor] = None, alpha: float = 1.0, alpha_dev: Optional[torch.Tensor] = None,
             skip: Optional[torch.Tensor] = None, need_dgrad: bool = False,
-            bufs: Optional[List[torch.Tensor]] = None):
-        """bufs: optional caller-owned buffers for the outputs of layers 0 .. L-2 (the saved activations)."""
+            bufs: Optional[List[torch.Tensor]] = None, maxima: Optional[torch.Tensor] = None):
+        """bufs: optional caller-owned buffers for the outputs of layers 0 .. L-2 (the saved activations).  maxima: a buffer from
+        new_maxima(); the chain adds max |a_l| of this launch to column 0 and the saved activations carry it to bwd()."""
         be = K.backend()
         B, H, W, _ = x.shape
         L = len(self.layers)
-        saved = [x] if save else None
+        saved = SavedActs([x]) if save else None
         a = x
         if self._fused(be, x):
             f16 = CONV_SPLIT == "f16"
+            amax_out = None
+            if f16 and save and maxima is not None:
+                amax_out = [maxima[l, 0:1] for l in range(L)]
+                saved.maxima = maxima
             if f16:
                 wts = [self.caches[l].get_f16(False).fwd_f16 for l in range(L)]
             else:
@@ -350,7 +386,7 @@ class ConvNetOp:
                 aux[L - 1], kinds[L - 1] = res, 3
             be.convnet(x, wts, [c.bias for c, _ in self.layers], [act for _, act in self.layers],
                        aux, kinds, outs, alpha=alpha if fuse else 1.0, alpha_dev=alpha_dev if fuse else None, skip=skip,
-                       split=1 if f16 else 0)
+                       split=1 if f16 else 0, **({"amax_out": amax_out} if amax_out is not None else {}))
             if save:
                 saved.extend(outs[:L - 1])
                 if last_act != ACT_NONE:
@@ -424,12 +460,19 @@ class ConvNetOp:
                 else:
                     aux.append(res); kinds.append(3 if res is not None else 0)
                     outs.append(out if out is not None else torch.empty((B, H, W, 64), dtype=torch.float32, device=x.device))
-            be.convnet(d, wts, [None] * len(ls), [ACT_NONE] * len(ls), aux, kinds, outs, alpha=1.0, split=1 if f16 else 0)
+            # chain position k reads d_{ls[k]}: its measured max is the dy bound of layer ls[k]'s weight gradient (d_{lo-1}, the
+            # chain's last output, is read by no position: with need_dx False layer 0's weight gradient has no bound)
+            am = getattr(saved, "maxima", None) if f16 else None
+            extra = {}
+            if am is not None:
+                extra["amax_out"] = [am[l, 1:2] for l in ls]
+            be.convnet(d, wts, [None] * len(ls), [ACT_NONE] * len(ls), aux, kinds, outs, alpha=1.0, split=1 if f16 else 0, **extra)
             grads = {L - 1: d}
             for k, l in enumerate(ls):
                 grads[l - 1] = outs[k]               # outs[k] = gradient w.r.t. the input of layer l = d_{l-1}
             for l in range(L - 1, -1, -1):
-                sink.add_wgrad(self.layers[l][0], saved[l], grads[l])
+                sink.add_wgrad(self.layers[l][0], saved[l], grads[l],
+                               amax=am[l] if am is not None and l >= lo else None)
             return grads[-1] if need_dx else None
         for l in range(L - 1, -1, -1):
             conv, _ = self.layers[l]

@@ -80,6 +80,9 @@ def rk_step_fwd(be, op: ConvNetOp, tab: Tableau, y: torch.Tensor, y_next: torch.
         yi_arena = torch.empty((s,) + tuple(y.shape), dtype=y.dtype, device=y.device)
         if all(c.out_channels == y.shape[3] for c, _ in op.layers[:-1]):
             arenas = [torch.empty((s,) + tuple(y.shape), dtype=y.dtype, device=y.device) for _ in range(len(op.layers) - 1)]
+    # one maxima buffer for the s stages of this step (same order of magnitude): their merged weight gradients then run on the
+    # kind::f16 kernel without a max pass (ConvNetOp.new_maxima)
+    maxima = op.new_maxima(y) if save else None
     for i in range(s):
         if i == 0:
             yi = y
@@ -94,7 +97,8 @@ def rk_step_fwd(be, op: ConvNetOp, tab: Tableau, y: torch.Tensor, y_next: torch.
             saved.append(None)
             continue
         kout = k_bufs[i] if k_bufs is not None else None
-        r = op.fwd(yi, save=save, out=kout, skip=skip, bufs=[a[i] for a in arenas] if arenas is not None else None)
+        r = op.fwd(yi, save=save, out=kout, skip=skip, bufs=[a[i] for a in arenas] if arenas is not None else None,
+                   maxima=maxima)
         if save:
             ks.append(r[0])
             saved.append(r[1])
@@ -445,7 +449,7 @@ class _Dopri5Fn(torch.autograd.Function):
             for s in range(6):
                 yi = new()
                 _lin(be, yi, [y] + ks, [1.0] + DP_BETA[s], dt_dev=dt_dev, dt_from=1)
-                ki, sv = op.fwd(yi, save=True)
+                ki, sv = op.fwd(yi, save=True, maxima=op.new_maxima(yi))      # per evaluation: the weight gradients are not merged here
                 ks.append(ki)
                 saved.append(sv)
             # ---- dense-output adjoints: sol_j = P(x_j) . (y0, y1, y_mid, dt f0, dt f1)

@@ -179,13 +179,49 @@ class FakeBackend:
         if db is not None:
             db += dy.sum((0, 1, 2))
 
+    @staticmethod
+    def wgrad_f16_shape_ok(c0, c1, N, H, W, R):
+        return R in (1, 3, 5) and c0 % 64 == 0 and c1 % 64 == 0 and N % 64 == 0 and W % 16 == 0 and H % 4 == 0
+
+    # ------------------------------------------------------------------ fused conv chain (odex_convnet)
+    def convnet_supported(self, x, n_layers):
+        B, H, W, Cc = x.shape
+        return H == 16 and W == 16 and Cc == 64 and 1 <= n_layers <= 6 and B > 0
+
+    def convnet(self, x, w_tc, bias, act, aux, aux_kind, out, alpha=1.0, alpha_dev=None, skip=None, split=0, amax_out=None):
+        self.launches += 1
+        if _skipped(skip):
+            return
+        assert amax_out is None or split == 1
+        a = x
+        for l in range(len(w_tc)):
+            if amax_out is not None and amax_out[l] is not None:
+                amax_out[l].copy_(torch.maximum(amax_out[l], a.detach().abs().max().reshape(amax_out[l].shape)))
+            w = w_tc[l]
+            wt = w.transpose(0, 1).flip(2, 3) if w._odex_dgrad else w
+            v = F.conv2d(a.permute(0, 3, 1, 2), wt, None if bias[l] is None else bias[l].detach(), padding=1)
+            v = _act(v, act[l]).permute(0, 2, 3, 1)
+            kind = aux_kind[l] if aux[l] is not None else 0
+            if kind in (1, 2):
+                v = v * _dact(aux[l], kind)
+            elif kind == 3:
+                al = f32(alpha)
+                if alpha_dev is not None:
+                    al = f32(al * f32(float(alpha_dev.reshape(-1)[0])))
+                v = aux[l] + float(al) * v
+            v = v.contiguous()
+            if out[l] is not None:
+                out[l].copy_(v)
+            a = v
+
     def conv2d_wgrad_packed(self, x0, x1, dy, R, dwp, db, impl=0, f16=False, amax=None):
         self.launches += 1
         x = x0 if x1 is None else torch.cat((x0, x1), 3)
-        if amax is not None:            # the scaled kernel trusts these bounds: a too-small one would overflow its fp16 operands
-            self.wgrad_scaled += 1
-            assert float(amax[0]) >= float(x.abs().max()) and float(amax[1]) >= float(dy.abs().max()), \
-                ("wgrad maxima are not upper bounds", amax.tolist(), float(x.abs().max()), float(dy.abs().max()))
+        if amax is not None:            # the scaled kernel trusts these bounds: a too-small one would overflow its fp16 operands,
+            self.wgrad_scaled += 1      # one far too large would push them into underflow
+            mx, md = float(x.abs().max()), float(dy.abs().max())
+            assert float(amax[0]) >= mx and float(amax[1]) >= md, ("wgrad maxima are not upper bounds", amax.tolist(), mx, md)
+            assert float(amax[0]) <= 1024 * mx and float(amax[1]) <= 1024 * md, ("wgrad maxima are too loose", amax.tolist(), mx, md)
         N, Cc = dy.shape[3], x.shape[3]
         g = torch.nn.grad.conv2d_weight(x.permute(0, 3, 1, 2).contiguous(), (N, Cc, R, R),
                                         dy.permute(0, 3, 1, 2).contiguous(), padding=(R - 1) // 2)

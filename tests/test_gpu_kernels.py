@@ -336,6 +336,47 @@ def test_convnet_f16_split_holds_fp32_accuracy_at_any_magnitude(be, scale):
     assert bool(torch.isnan(outs[-1][0]).any()) and bool(torch.isfinite(outs[-1][4]).all())
 
 
+def test_convnet_amax_out_and_scaled_weight_gradient(be):
+    """odex_convnet_desc.amax_out: the kind::f16 chain leaves max |input of layer l| (over all images of the launch, accumulated
+    atomically over launches) where the caller points; odex_conv2d_wgrad_f16_scaled takes such maxima instead of a max pass and
+    must agree with the 3xTF32 weight gradient."""
+    torch.manual_seed(5)
+    B, L = 7, 4
+    x = torch.randn(B, 16, 16, 64, device="cuda") * 3.0
+    x[2] = 0.0
+    ws = [torch.randn(64, 64, 3, 3, device="cuda") / 24.0 for _ in range(L)]
+    bs = [torch.randn(64, device="cuda") * 0.1 for _ in range(L)]
+    acts = [ACT_RELU] * (L - 1) + [ACT_NONE]
+    outs = [torch.empty_like(x) for _ in range(L)]
+    am = torch.zeros(L, 2, device="cuda")
+    packs = [be.pack_weights(w, False, 2) for w in ws]
+    be.convnet(x, packs, bs, acts, [None] * L, [0] * L, outs, split=1, amax_out=[am[l, 0:1] for l in range(L)])
+    torch.cuda.synchronize()
+    ins = [x] + outs[:-1]
+    for l in range(L):
+        assert float(am[l, 0]) == float(ins[l].abs().max()), (l, float(am[l, 0]), float(ins[l].abs().max()))
+    # a second launch on smaller data leaves the maxima where they are; on larger data it raises them
+    be.convnet(x * 0.5, packs, bs, acts, [None] * L, [0] * L, [torch.empty_like(x) for _ in range(L)], split=1,
+               amax_out=[am[l, 0:1] for l in range(L)])
+    assert float(am[0, 0]) == float(x.abs().max())
+    be.convnet(x * 4.0, packs, bs, acts, [None] * L, [0] * L, [torch.empty_like(x) for _ in range(L)], split=1,
+               amax_out=[am[l, 0:1] for l in range(L)])
+    assert float(am[0, 0]) == float((x * 4.0).abs().max())
+    # the tf32 chain refuses the request instead of ignoring it
+    with pytest.raises(Exception):
+        be.convnet(x, [be.pack_weights(w, False, 1) for w in ws], bs, acts, [None] * L, [0] * L, outs, split=0,
+                   amax_out=[am[l, 0:1] for l in range(L)])
+    # weight gradient of layer 1 from (a_1, dy) with bounds {max |a_1| * 4 (see above), a loose bound of max |dy|}
+    dy = torch.randn(B, 16, 16, 64, device="cuda") * 1e-3
+    am[1, 1] = dy.abs().max() * 37.0
+    ref, got = torch.zeros(9, 64, 64, device="cuda"), torch.zeros(9, 64, 64, device="cuda")
+    rb, gb = torch.zeros(64, device="cuda"), torch.zeros(64, device="cuda")
+    be.conv2d_wgrad_packed(ins[1], None, dy, 3, ref, rb)
+    be.conv2d_wgrad_packed(ins[1], None, dy, 3, got, gb, amax=am[1])
+    torch.cuda.synchronize()
+    assert rel_err(got, ref) < 1e-5 and rel_err(gb, rb) < 1e-5, (rel_err(got, ref), rel_err(gb, rb))
+
+
 @pytest.mark.parametrize("split", [0, 1], ids=["tf32", "f16"])
 def test_convnet_fused_chain_is_deterministic(be, split):
     """The fused chain recycles its shared-memory planes between layers (operands overwritten in place, TMA loads into
