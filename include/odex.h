@@ -183,6 +183,11 @@ typedef struct odex_conv16_desc {
     const float* h; int ldh; const float* z_in;
     float* z; float* rh; float* hnew; int ld_hnew; float* cand; float* g_raw; float* stats;
     const int* skip;
+    float* amax_out;                        /* nullable: *amax_out = max(*amax_out, max |x0|, max |x1|) over the launch's images,
+                                               atomically (the kernel measures it for its operand scale anyway); the caller zeroes
+                                               it.  A bound for odex_conv2d_wgrad_f16_scaled: the sources of a forward launch are
+                                               the X of that convolution's weight gradient, the source of its data-gradient
+                                               launch (mode PLAIN over dy) is the dy. */
 } odex_conv16_desc;
 int odex_conv16(const odex_conv16_desc* d, odex_stream_t s);
 int odex_conv16_supported(const odex_conv16_desc* d);

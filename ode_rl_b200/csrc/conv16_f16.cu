@@ -62,6 +62,7 @@ struct C16Args {
     const float* h; int ldh; const float* z_in;
     float* z; float* rh; float* hnew; int ld_hnew; float* cand; float* g_raw; float* stats;
     const int* skip;
+    float* amax_out;
     long long* dbg;
 };
 
@@ -289,6 +290,7 @@ conv16_f16_kernel(const __grid_constant__ C16Maps tm, const C16Args a) {
         asm volatile("ld.shared.u32 %0, [%1];" : "=r"(mb) : "r"(amax_s));
         float a_inv;
         const float a_scale = f16_scale_for(__uint_as_float(mb), &a_inv);
+        if (tid == 0 && a.amax_out) atomicMax(reinterpret_cast<unsigned int*>(a.amax_out), mb);
         C16_MARK(1);
 
         c16_convert<R>(s_base, base, m, a_scale);
@@ -630,6 +632,7 @@ static int c16_launch(const odex_conv16_desc* d, cudaStream_t s) {
     a.h = d->h; a.ldh = d->ldh; a.z_in = d->z_in;
     a.z = d->z; a.rh = d->rh; a.hnew = d->hnew; a.ld_hnew = d->ld_hnew; a.cand = d->cand; a.g_raw = d->g_raw; a.stats = d->stats;
     a.skip = d->skip;
+    a.amax_out = d->amax_out;
     a.dbg = nullptr;
     static const bool debug = getenv("ODEX_CONV_DEBUG") != nullptr;
     if (debug) {

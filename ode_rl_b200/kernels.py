@@ -207,10 +207,13 @@ class Backend:
 
     def conv16(self, x0: torch.Tensor, x1: Optional[torch.Tensor], w_f16: torch.Tensor, N: int, R: int,
                bias: Optional[torch.Tensor], act: int, out: torch.Tensor, aux: Optional[torch.Tensor] = None, aux_kind: int = 0,
-               alpha: float = 1.0, alpha_dev: Optional[torch.Tensor] = None, skip: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """odex_conv16(PLAIN): out = act(conv(cat(x0, x1)) + bias), then * act'(aux) (aux_kind 1 / 2) or aux + alpha * v (3)."""
+               alpha: float = 1.0, alpha_dev: Optional[torch.Tensor] = None, skip: Optional[torch.Tensor] = None,
+               amax_out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """odex_conv16(PLAIN): out = act(conv(cat(x0, x1)) + bias), then * act'(aux) (aux_kind 1 / 2) or aux + alpha * v (3).
+        amax_out (all three modes): one-element fp32 tensor <- max(itself, max |sources|), atomically."""
         self.require(x0)
         d = self._conv16_desc(x0, x1, w_f16, N, R, bias, skip)
+        d.amax_out = _ptr(amax_out)
         d.mode = _lib.C16_PLAIN
         d.act = act
         if aux is not None and aux_kind:
@@ -224,12 +227,14 @@ class Backend:
         return out
 
     def conv16_gru_gates(self, x: torch.Tensor, h: torch.Tensor, w_f16: torch.Tensor, R: int, bias, gamma, beta, eps: float,
-                         z: torch.Tensor, rh: torch.Tensor, stats: torch.Tensor, g_raw: Optional[torch.Tensor] = None) -> None:
+                         z: torch.Tensor, rh: torch.Tensor, stats: torch.Tensor, g_raw: Optional[torch.Tensor] = None,
+                         amax_out: Optional[torch.Tensor] = None) -> None:
         """odex_conv16(GRU_GATES): z, r = sigmoid(GroupNorm(conv(cat(x, h)) + bias)); rh = r * h; g_raw <- the pre-norm conv."""
         self.require(x)
         Cc = h.shape[3]
         d = self._conv16_desc(x, h, w_f16, 2 * Cc, R, bias, None)
         d.mode = _lib.C16_GRU_GATES
+        d.amax_out = _ptr(amax_out)
         d.gamma, d.beta, d.eps = gamma.detach().data_ptr(), beta.detach().data_ptr(), float(eps)
         d.h, d.ldh = _rows(h)
         assert z.is_contiguous() and rh.is_contiguous() and (g_raw is None or g_raw.is_contiguous())
@@ -238,12 +243,14 @@ class Backend:
 
     def conv16_gru_out(self, x: torch.Tensor, rh: torch.Tensor, w_f16: torch.Tensor, R: int, bias, gamma, beta, eps: float,
                        z: torch.Tensor, h: torch.Tensor, hnew: torch.Tensor, stats: torch.Tensor,
-                       cand: Optional[torch.Tensor] = None, cpre: Optional[torch.Tensor] = None) -> None:
+                       cand: Optional[torch.Tensor] = None, cpre: Optional[torch.Tensor] = None,
+                       amax_out: Optional[torch.Tensor] = None) -> None:
         """odex_conv16(GRU_OUT): c = tanh(GroupNorm(conv(cat(x, rh)) + bias)); hnew = (1 - z) * h + z * c."""
         self.require(x)
         Cc = h.shape[3]
         d = self._conv16_desc(x, rh, w_f16, Cc, R, bias, None)
         d.mode = _lib.C16_GRU_OUT
+        d.amax_out = _ptr(amax_out)
         d.gamma, d.beta, d.eps = gamma.detach().data_ptr(), beta.detach().data_ptr(), float(eps)
         d.h, d.ldh = _rows(h)
         assert z.is_contiguous() and (cand is None or cand.is_contiguous()) and (cpre is None or cpre.is_contiguous())

@@ -540,14 +540,21 @@ class GruOp:
             st_g = torch.empty((B * (2 * C // 32) * 2,), dtype=f32, device=dev)
             st_c = torch.empty((B * (C // 32) * 2,), dtype=f32, device=dev)
             g = torch.empty((B, H, W, 2 * C), dtype=f32, device=dev) if save else None
-            be.conv16_gru_gates(x, h, wg, R, self.cg.bias, self.gn_g.weight, self.gn_g.bias, self.gn_g.eps, z, rh, st_g, g_raw=g)
+            # [2, 2] maxima of this step: row 0 = conv_gates {max |(x, h)|, max |dg|}, row 1 = conv_can {max |(x, rh)|, max |dcpre|};
+            # the conv16 launches measure them for their operand scales anyway, the weight gradients of the step take them
+            mx = None
+            if save and _wgrad_scaled() and be.wgrad_f16_shape_ok(Cx, C, 2 * C, H, W, R):
+                mx = torch.zeros((2, 2), dtype=f32, device=dev)
+            mxa = (lambda i, j: {"amax_out": mx[i, j:j + 1]}) if mx is not None else (lambda i, j: {})
+            be.conv16_gru_gates(x, h, wg, R, self.cg.bias, self.gn_g.weight, self.gn_g.bias, self.gn_g.eps, z, rh, st_g, g_raw=g,
+                                **mxa(0, 0))
             hnew = out if out is not None else torch.empty((B, H, W, C), dtype=f32, device=dev)
             cpre = torch.empty((B, H, W, C), dtype=f32, device=dev) if save else None
             cand = torch.empty((B, H, W, C), dtype=f32, device=dev) if save else None
             be.conv16_gru_out(x, rh, wc, R, self.cc.bias, self.gn_c.weight, self.gn_c.bias, self.gn_c.eps, z, h, hnew, st_c,
-                              cand=cand, cpre=cpre)
+                              cand=cand, cpre=cpre, **mxa(1, 0))
             if save:
-                return hnew, (x, h, g, z, rh, st_g, cpre, cand, st_c)
+                return hnew, (x, h, g, z, rh, st_g, cpre, cand, st_c, mx)
             return hnew
         pg = self.pc_g.get(H, W, Cx, C, save)
         g = torch.empty((B, H, W, 2 * C), dtype=f32, device=dev)
@@ -570,7 +577,8 @@ class GruOp:
     def bwd(self, saved, dhnew: torch.Tensor, sink: GradSink, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """Returns D = [dx | dh] as one [B,H,W,Cx+C] buffer (channel slices are the two gradients)."""
         be = K.backend()
-        x, h, g, z, rh, st_g, cpre, cand, st_c = saved
+        x, h, g, z, rh, st_g, cpre, cand, st_c = saved[:9]
+        mx = saved[9] if len(saved) > 9 else None       # the step's maxima (fused forward only)
         B, H, W, Cx = x.shape
         C, R = self.C, self.R
         dev, f32 = x.device, torch.float32
@@ -584,28 +592,34 @@ class GruOp:
         dh_a = torch.empty((B, H, W, C), dtype=f32, device=dev)
         be.gru_out_bwd(dhnew, cpre, cand, z, h, self.gn_c.weight, st_c, dcpre, dz, dh_a,
                        grad_or_scratch(self.gn_c.weight), grad_or_scratch(self.gn_c.bias))
-        gw, gb = sink.get_packed(self.cc.weight), sink.get(self.cc.bias)
-        if gw is not None or gb is not None:
-            be.conv2d_wgrad_packed(x, rh, dcpre, R, gw if gw is not None else _scratch_packed(self.cc.weight), gb, f16=_wgrad_f16())
         f16 = self._fused16(be, x, h)
+        mx = mx if f16 else None
         D1 = torch.empty((B, H, W, Cx + C), dtype=f32, device=dev)            # [dx_can | drh]
         if f16:
-            be.conv16(dcpre, None, self.pc_c.get_f16(True).dgrad_f16, Cx + C, R, None, ACT_NONE, D1)
+            # the data-gradient launch reads dcpre: its max |dcpre| completes row 1 of the maxima before the weight gradient runs
+            be.conv16(dcpre, None, self.pc_c.get_f16(True).dgrad_f16, Cx + C, R, None, ACT_NONE, D1,
+                      **({"amax_out": mx[1, 1:2]} if mx is not None else {}))
         else:
             pc = self.pc_c.get(H, W, Cx, C, True)
             be.conv2d(dcpre, None, pc.dgrad_simt, pc.dgrad_tc, Cx + C, R, None, ACT_NONE, D1)
+        gw, gb = sink.get_packed(self.cc.weight), sink.get(self.cc.bias)
+        if gw is not None or gb is not None:
+            be.conv2d_wgrad_packed(x, rh, dcpre, R, gw if gw is not None else _scratch_packed(self.cc.weight), gb, f16=_wgrad_f16(),
+                                   amax=mx[1] if mx is not None else None)
         dg = torch.empty((B, H, W, 2 * C), dtype=f32, device=dev)
         drh = D1[..., Cx:]
         be.gru_gates_bwd(dz, drh, dh_a, g, h, self.gn_g.weight, self.gn_g.bias, st_g, dg, drh,
                          grad_or_scratch(self.gn_g.weight), grad_or_scratch(self.gn_g.bias))   # D1[..., Cx:] <- dh_a + drh*r
-        gw, gb = sink.get_packed(self.cg.weight), sink.get(self.cg.bias)
-        if gw is not None or gb is not None:
-            be.conv2d_wgrad_packed(x, h, dg, R, gw if gw is not None else _scratch_packed(self.cg.weight), gb, f16=_wgrad_f16())
         D2 = out if out is not None else torch.empty((B, H, W, Cx + C), dtype=f32, device=dev)
         if f16:
             pgf = self.pc_g.get_f16(True).dgrad_f16
-            be.conv16(dg[..., :C], dg[..., C:], pgf, Cx + C, R, None, ACT_NONE, D2, aux=D1, aux_kind=3, alpha=1.0)
+            be.conv16(dg[..., :C], dg[..., C:], pgf, Cx + C, R, None, ACT_NONE, D2, aux=D1, aux_kind=3, alpha=1.0,
+                      **({"amax_out": mx[0, 1:2]} if mx is not None else {}))
         else:
             pg = self.pc_g.get(H, W, Cx, C, True)
             be.conv2d(dg, None, pg.dgrad_simt, pg.dgrad_tc, Cx + C, R, None, ACT_NONE, D2, res=D1, alpha=1.0)
+        gw, gb = sink.get_packed(self.cg.weight), sink.get(self.cg.bias)
+        if gw is not None or gb is not None:
+            be.conv2d_wgrad_packed(x, h, dg, R, gw if gw is not None else _scratch_packed(self.cg.weight), gb, f16=_wgrad_f16(),
+                                   amax=mx[0] if mx is not None else None)
         return D2

@@ -612,6 +612,44 @@ def test_conv16_plain_matches_exact_fp32_conv(be, R, nsrc, N):
 
 
 @pytest.mark.parametrize("R", [3, 5])
+def test_conv16_amax_out_feeds_the_scaled_weight_gradient(be, R):
+    """odex_conv16_desc.amax_out: max |sources| over the launch, accumulated atomically, in all three modes; the 5x5 two-source
+    weight gradients of the ConvGRU take such pairs (odex_conv2d_wgrad_f16_scaled) and must agree with the 3xTF32 kernel."""
+    torch.manual_seed(9 + R)
+    B, Cn = 5, 64
+    x = torch.randn(B, 16, 16, Cn, device="cuda") * 2.0
+    hw = torch.randn(B, 16, 16, 2 * Cn, device="cuda") * 0.7
+    h = hw[..., Cn:]
+    x[3] = 0.0
+    wg = torch.randn(2 * Cn, 2 * Cn, R, R, device="cuda") / (11.0 * R)
+    wc = torch.randn(Cn, 2 * Cn, R, R, device="cuda") / (11.0 * R)
+    bg, bc = torch.randn(2 * Cn, device="cuda") * 0.1, torch.randn(Cn, device="cuda") * 0.1
+    gam_g, bet_g = torch.rand(2 * Cn, device="cuda") + 0.5, torch.randn(2 * Cn, device="cuda") * 0.1
+    gam_c, bet_c = torch.rand(Cn, device="cuda") + 0.5, torch.randn(Cn, device="cuda") * 0.1
+    mx = torch.zeros(2, 2, device="cuda")
+    z, rh, stg = torch.empty(B, 16, 16, Cn, device="cuda"), torch.empty(B, 16, 16, Cn, device="cuda"), torch.empty(B * 8, device="cuda")
+    be.conv16_gru_gates(x, h, be.pack_weights(wg, False, 2), R, bg, gam_g, bet_g, 1e-5, z, rh, stg, amax_out=mx[0, 0:1])
+    hn, stc = torch.empty(B, 16, 16, Cn, device="cuda"), torch.empty(B * 4, device="cuda")
+    be.conv16_gru_out(x, rh, be.pack_weights(wc, False, 2), R, bc, gam_c, bet_c, 1e-5, z, h, hn, stc, amax_out=mx[1, 0:1])
+    dg = torch.randn(B, 16, 16, 2 * Cn, device="cuda") * 1e-4
+    D = torch.empty(B, 16, 16, 2 * Cn, device="cuda")
+    be.conv16(dg[..., :Cn], dg[..., Cn:], be.pack_weights(wg, True, 2), 2 * Cn, R, None, ACT_NONE, D, amax_out=mx[0, 1:2])
+    dc = torch.randn(B, 16, 16, Cn, device="cuda") * 1e-2
+    be.conv16(dc, None, be.pack_weights(wc, True, 2), 2 * Cn, R, None, ACT_NONE, D, amax_out=mx[1, 1:2])
+    torch.cuda.synchronize()
+    want = [[max(float(x.abs().max()), float(h.abs().max())), float(dg.abs().max())],
+            [max(float(x.abs().max()), float(rh.abs().max())), float(dc.abs().max())]]
+    assert mx.tolist() == want, (mx.tolist(), want)
+    for (x1, dy, N, row) in ((h, dg, 2 * Cn, 0), (rh, dc, Cn, 1)):
+        ref, got = torch.zeros(R * R, N, 2 * Cn, device="cuda"), torch.zeros(R * R, N, 2 * Cn, device="cuda")
+        rb, gb = torch.zeros(N, device="cuda"), torch.zeros(N, device="cuda")
+        be.conv2d_wgrad_packed(x, x1, dy, R, ref, rb)
+        be.conv2d_wgrad_packed(x, x1, dy, R, got, gb, amax=mx[row])
+        torch.cuda.synchronize()
+        assert rel_err(got, ref) < 1e-5 and rel_err(gb, rb) < 1e-5, (row, rel_err(got, ref), rel_err(gb, rb))
+
+
+@pytest.mark.parametrize("R", [3, 5])
 @pytest.mark.parametrize("scale", [1.0, 1e-6, 1e5])
 def test_conv16_fused_gru_step_matches_unfused_kernels(be, R, scale):
     """GRU_GATES + GRU_OUT (two launches) against conv (exact fp32) -> gru_gates_fwd_kernel -> conv -> gru_out_fwd_kernel:
