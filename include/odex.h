@@ -115,11 +115,14 @@ int odex_wgrad_unpack(const float* dwp, int N, int C, int R, float* dw, odex_str
  * kernel (c0, c1, N % 64 == 0, W % 16 == 0, H % 4 == 0, R in {1,3,5}). */
 int odex_conv2d_wgrad_f16(const float* x0, int ld0, int c0, const float* x1, int ld1, int c1, const float* dy, int ldy,
                           int B, int H, int W, int R, int N, float* dwp, float* db, float* scratch2, odex_stream_t s);
-/* The same kernel when the caller already holds upper bounds of the two maxima: amax2 = {>= max |X|, >= max |dy|} in device
- * memory (e.g. accumulated by odex_convnet through odex_convnet_desc.amax_out while it produced the operands).  No max pass.
- * A bound up to ~2^9 above the true maximum costs no accuracy (the lo term resolves 2^-24 absolute against 2^13). */
+/* The same kernel when the caller already holds PER-IMAGE upper bounds of the operands' maxima: amax_x[b] >= max |X[b]| (over
+ * both sources), amax_dy[b] >= max |dy[b]|, b < B, in device memory -- as odex_convnet / odex_conv16 leave them (amax_out) while
+ * they produce or read those operands.  No max pass.  The kernel scales each image's operands by its own maxima and keeps only the
+ * scale of the PRODUCT common to the launch (from max_b amax_x[b] * amax_dy[b]), so images whose magnitudes differ by any factor
+ * can share a launch: an image loses operand bits only in proportion to how little it contributes to the sum. */
 int odex_conv2d_wgrad_f16_scaled(const float* x0, int ld0, int c0, const float* x1, int ld1, int c1, const float* dy, int ldy,
-                                 int B, int H, int W, int R, int N, float* dwp, float* db, const float* amax2, odex_stream_t s);
+                                 int B, int H, int W, int R, int N, float* dwp, float* db, const float* amax_x, const float* amax_dy,
+                                 odex_stream_t s);
 
 /* ------------------------------------------------------------------------------------------------ fused conv chain
  * A chain of L 3x3 C->C convolutions (C = 64) over 16x16 images in ONE launch, the image resident in shared memory
@@ -146,10 +149,10 @@ typedef struct odex_convnet_desc {
     int split;                                  /* 0: w_tc are odex_pack_weights(tc = 1) blobs, 3xTF32 on tcgen05 kind::tf32;
                                                    1: w_tc are odex_pack_weights(tc = 2) blobs, two-term fp16 split on kind::f16
                                                       (same 22 significant bits per operand, twice the MMA rate) */
-    float* amax_out[ODEX_NET_MAX_LAYERS];       /* split = 1 only, each nullable: *amax_out[l] = max(*amax_out[l], max |a_l|) over the
-                                                   launch's images (a_0 = x, a_l = v_{l-1}), atomically; the caller zeroes them.
-                                                   These are the operands of the layers' weight gradients: odex_conv2d_wgrad_f16_scaled
-                                                   takes them instead of running a max pass.  split = 0 rejects a non-NULL entry. */
+    float* amax_out[ODEX_NET_MAX_LAYERS];       /* split = 1 only, each nullable: amax_out[l][b] <- max |a_l[b]| for every image b < B
+                                                   (a_0 = x, a_l = v_{l-1}); B floats each.  These are the operands of the layers'
+                                                   weight gradients: odex_conv2d_wgrad_f16_scaled takes them instead of running a
+                                                   max pass.  split = 0 rejects a non-NULL entry. */
 } odex_convnet_desc;
 int odex_convnet(const odex_convnet_desc* d, odex_stream_t s);
 int odex_convnet_supported(const odex_convnet_desc* d);
@@ -183,11 +186,10 @@ typedef struct odex_conv16_desc {
     const float* h; int ldh; const float* z_in;
     float* z; float* rh; float* hnew; int ld_hnew; float* cand; float* g_raw; float* stats;
     const int* skip;
-    float* amax_out;                        /* nullable: *amax_out = max(*amax_out, max |x0|, max |x1|) over the launch's images,
-                                               atomically (the kernel measures it for its operand scale anyway); the caller zeroes
-                                               it.  A bound for odex_conv2d_wgrad_f16_scaled: the sources of a forward launch are
-                                               the X of that convolution's weight gradient, the source of its data-gradient
-                                               launch (mode PLAIN over dy) is the dy. */
+    float* amax_out;                        /* nullable, B floats: amax_out[b] <- max(max |x0[b]|, max |x1[b]|) (the kernel measures it
+                                               for its operand scale anyway).  For odex_conv2d_wgrad_f16_scaled: the sources of a
+                                               forward launch are the X of that convolution's weight gradient, the source of its
+                                               data-gradient launch (mode PLAIN over dy) is the dy. */
 } odex_conv16_desc;
 int odex_conv16(const odex_conv16_desc* d, odex_stream_t s);
 int odex_conv16_supported(const odex_conv16_desc* d);

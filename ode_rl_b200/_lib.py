@@ -143,7 +143,7 @@ SIGNATURES = {
     "odex_conv2d_wgrad_packed": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
     "odex_wgrad_unpack": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "odex_conv2d_wgrad_f16": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
-    "odex_conv2d_wgrad_f16_scaled": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
+    "odex_conv2d_wgrad_f16_scaled": (_i, [_vp, _i, _i, _vp, _i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "odex_gru_gates_fwd": (_i, [_vp, _vp, _i, _vp, _vp, _f, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "odex_gru_out_fwd": (_i, [_vp, _vp, _vp, _i, _vp, _vp, _f, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "odex_gru_out_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),

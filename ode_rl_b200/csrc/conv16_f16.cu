@@ -290,7 +290,7 @@ conv16_f16_kernel(const __grid_constant__ C16Maps tm, const C16Args a) {
         asm volatile("ld.shared.u32 %0, [%1];" : "=r"(mb) : "r"(amax_s));
         float a_inv;
         const float a_scale = f16_scale_for(__uint_as_float(mb), &a_inv);
-        if (tid == 0 && a.amax_out) atomicMax(reinterpret_cast<unsigned int*>(a.amax_out), mb);
+        if (tid == 0 && a.amax_out) a.amax_out[img] = __uint_as_float(mb);      // (every output-channel block of the image writes the same value)
         C16_MARK(1);
 
         c16_convert<R>(s_base, base, m, a_scale);

@@ -57,7 +57,7 @@ struct F16Args {
     float alpha;
     const double* alpha_dev;
     const int* skip;
-    float* amax_out[kF16MaxL];      // nullable: atomic max of max |input of layer l| over the launch's images (non-negative float bits)
+    float* amax_out[kF16MaxL];      // nullable: amax_out[l][img] <- max |input of layer l| of image img
     long long* dbg;
 };
 
@@ -309,12 +309,12 @@ convnet_f16_kernel(const __grid_constant__ F16Maps tm, const F16Args a) {
             }
         }
         if (tid == 0) tma_store_wait_read();
-        // maxima of the chain input and of the outputs of layers 0 .. L-2 (all final since the last layer's closing bar.sync): the
-        // operands of the weight gradients, whose kind::f16 kernel then needs no max pass of its own
+        // this image's maxima of the chain input and of the outputs of layers 0 .. L-2 (all final since the last layer's closing
+        // bar.sync): the operands of the weight gradients, whose kind::f16 kernel then needs no max pass of its own
         if (tid < L && a.amax_out[tid]) {
             uint32_t mb;
             asm volatile("ld.shared.u32 %0, [%1];" : "=r"(mb) : "r"(amax_s + 4u * tid));
-            atomicMax(reinterpret_cast<unsigned int*>(a.amax_out[tid]), mb);
+            a.amax_out[tid][img] = __uint_as_float(mb);
         }
         tc_fence_before_sync();
         if (a.dbg && blockIdx.x == 0 && tid == 0) a.dbg[0] = clock64() - t_start;

@@ -46,7 +46,9 @@ struct Wgrad16Geom {
     int ntiles;         // B * (H / 4) * (W / 16)
     float* dwp;         // [R*R][N][Ctot], accumulated
     float* db;          // [N] or nullptr, accumulated
-    const float* amax;  // {max |X|, max |dy|} from absmax2_kernel
+    // operand maxima: one pair for the whole tensor (amax_stride 0: absmax2_kernel's, or the caller's) or one pair PER IMAGE
+    // (amax_stride 1: amax_x[b] >= max |X[b]|, amax_dy[b] >= max |dy[b]|, as the producing kernels measured them)
+    const float* amax_x; const float* amax_dy; int amax_stride;
 };
 
 // max |.| of up to three strided [P, C] fp32 matrices: out[0] <- max over a and b (the X sources), out[1] <- c (dy).
@@ -123,8 +125,41 @@ __device__ __forceinline__ void umma_f16_ts_w(uint32_t d_tmem, uint32_t a_tmem, 
         : "memory");
 }
 
-// scale that puts a tensor's max |.| in [2^12, 2^13) (f16_scale_for), from the device-side max
-__device__ __forceinline__ float w16_scale(float amax, float* inv) { return f16_scale_for(amax, inv); }
+// Operand scales.  Every tap accumulator is shared by all the tiles (images) a CTA visits, so what has to be common is the scale
+// of the PRODUCT, 2^t; how t is split between the two operands is free per image:
+//     s_x(b) puts max |X[b]| in [2^12, 2^13),      s_dy(b) = 2^t / s_x(b),
+//     t from  max_b (max |X[b]| * max |dy[b]|) * 2^t  in (2^24, 2^26]      =>  max |dy[b]| * s_dy(b) < 2^14 for every b.
+// An image whose product of maxima is the largest keeps >= 11 + 11 bits in both operands; one whose product is 2^-k of that
+// loses k bits in dy -- and contributes 2^-k of the result.  So maxima that differ by any factor between the images of a launch
+// (a state that grows by orders of magnitude over a rollout while its adjoint shrinks) cost nothing, where one pair of maxima
+// for the whole tensor would flush the small images' operands to zero.  Exponent arithmetic on the biased exponents:
+// v in [2^(e-127), 2^(e-126)).
+__device__ __forceinline__ int w16_bexp(float v) { return static_cast<int>((__float_as_uint(v) >> 23) & 0xFFu); }
+__device__ __forceinline__ float w16_pow2(int biased) {
+    biased = biased < 1 ? 1 : (biased > 254 ? 254 : biased);
+    return __uint_as_float(static_cast<uint32_t>(biased) << 23);
+}
+// max over the launch's images of e_x + e_d (0 when every product is zero); whole warp, result in every lane
+__device__ __forceinline__ int w16_pmax_exp(const Wgrad16Geom& g, int lane) {
+    int pe = 0;
+    const int n = g.amax_stride ? g.B : 1;
+    for (int b = lane; b < n; b += 32) {
+        const int ex = w16_bexp(__ldg(g.amax_x + b)), ed = w16_bexp(__ldg(g.amax_dy + b));
+        if (ex != 0 && ed != 0) pe = max(pe, ex + ed);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) pe = max(pe, __shfl_xor_sync(0xffffffffu, pe, o));
+    return pe;
+}
+// scales of image b: x * sx <= 2^13, dy * sdy < 2^14, sx * sdy = 2^(278 - pmax_e)
+__device__ __forceinline__ void w16_scales(const Wgrad16Geom& g, int b, int pmax_e, float* sx, float* sdy) {
+    const int ex = w16_bexp(__ldg(g.amax_x + b * g.amax_stride));
+    int sxe = (ex == 0 || ex == 255) ? 127 : 266 - ex;
+    sxe = sxe < 1 ? 1 : (sxe > 254 ? 254 : sxe);
+    *sx = w16_pow2(sxe);
+    // an all-zero (or denormal) X image contributes nothing: dy * 0 keeps an unbounded dy from overflowing into inf * 0
+    *sdy = ex == 0 ? 0.f : w16_pow2(pmax_e == 0 ? 127 : (278 - pmax_e) - (sxe - 127) + 127);
+}
 
 template <int R>
 __global__ void __launch_bounds__(320, 1)
@@ -261,8 +296,8 @@ wgrad_f16_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
         const uint32_t lane_addr = static_cast<uint32_t>(q * 32) << 16;
         const bool do_db = g.db != nullptr && tg == 0 && cg == 0 && part == 0;
         float dbsum = 0.f;
-        float sx_inv, sdy_inv;
-        const float sx = w16_scale(__ldg(g.amax), &sx_inv), sdy = w16_scale(__ldg(g.amax + 1), &sdy_inv);
+        const int pmax_e = w16_pmax_exp(g, lane);
+        const int tiles_per_img = (g.H / kW16TH) * (g.W / kW16TW);
         // dy element (pixel k, channel n) of the raw SWIZZLE_128B tile: plane n / 32, row k, 16-byte chunk ((n % 32) / 4) ^ (k % 8)
         const uint32_t dy_off = static_cast<uint32_t>(n >> 5) * kW16DyPlane + static_cast<uint32_t>(n & 3) * 4u;
         const uint32_t dy_chunk = static_cast<uint32_t>((n & 31) >> 2);
@@ -270,6 +305,8 @@ wgrad_f16_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
         int it = 0;
         for (int t = ps; t < g.ntiles; t += g.PS, ++it) {
             if ((it & 1) != grp) continue;
+            float sx, sdy;
+            w16_scales(g, t / tiles_per_img, pmax_e, &sx, &sdy);
             const int st = it % S;
             const uint32_t use = static_cast<uint32_t>(it / S);
             mbar_wait(bar_raw_full + 8 * st, use & 1u);
@@ -347,7 +384,9 @@ wgrad_f16_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
 
         // ---- epilogue: dwp[tap][n][c] += (D[n][c] + D[64 + n][c]) / (s_x * s_dy); the lo-row warps hand their sums over
         // through shared memory, so a CTA issues 64 x 16 vector reductions per tap
-        const float unscale = sx_inv * sdy_inv;
+        // 1 / (s_x * s_dy) = 2^-(278 - pmax_e), in two factors (the exponent can exceed what one float holds)
+        const int tsh = pmax_e == 0 ? 0 : 278 - pmax_e;
+        const float un1 = w16_pow2(127 - tsh / 2), un2 = w16_pow2(127 - (tsh - tsh / 2));
         for (int tl = 0; tl < ntap; ++tl) {
             float acc[64];
 #pragma unroll
@@ -373,8 +412,8 @@ wgrad_f16_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
                     float4 o;
                     asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(o.x), "=f"(o.y), "=f"(o.z), "=f"(o.w)
                                  : "r"(sc + ((static_cast<uint32_t>(k) ^ (n & 15)) << 4)));
-                    w16_red_add_v4(dst + 4 * k, (acc[4 * k] + o.x) * unscale, (acc[4 * k + 1] + o.y) * unscale,
-                                   (acc[4 * k + 2] + o.z) * unscale, (acc[4 * k + 3] + o.w) * unscale);
+                    w16_red_add_v4(dst + 4 * k, (acc[4 * k] + o.x) * un1 * un2, (acc[4 * k + 1] + o.y) * un1 * un2,
+                                   (acc[4 * k + 2] + o.z) * un1 * un2, (acc[4 * k + 3] + o.w) * un1 * un2);
                 }
             }
         }
@@ -428,11 +467,12 @@ bool wgrad_f16_supported(int c0, int c1, int N, int H, int W, int R) {
 }
 
 int launch_wgrad_f16(const float* x0, int ld0, int c0, const float* x1, int ld1, int c1, const float* dy, int ldy, int B,
-                     int H, int W, int R, int N, float* dwp, float* db, float* scratch2, const float* amax_ready, cudaStream_t s) {
+                     int H, int W, int R, int N, float* dwp, float* db, float* scratch2, const float* amax_x, const float* amax_dy,
+                     cudaStream_t s) {
     if (!w16_encode_fn()) return fail(ODEX_E_DRIVER, "cuTensorMapEncodeTiled not available from the driver");
-    // ---- per-tensor maxima -> scratch2 (unless the caller has upper bounds of them already)
+    // ---- per-tensor maxima -> scratch2 (unless the caller has per-image upper bounds already)
     const long P = static_cast<long>(B) * H * W;
-    if (!amax_ready) {
+    if (!amax_x) {
         cudaMemsetAsync(scratch2, 0, 2 * sizeof(float), s);
         const long work = P * ((c0 + c1 + N) / 4);
         const int blocks = static_cast<int>(std::min<long>((work + 1023) / 1024, 8L * kSMs));
@@ -457,7 +497,10 @@ int launch_wgrad_f16(const float* x0, int ld0, int c0, const float* x1, int ld1,
     g.ntiles = B * (H / kW16TH) * (W / kW16TW);
     const int units = g.TG * g.CG * g.NB;
     g.PS = std::max(1, std::min(g.ntiles, kSMs / units));
-    g.dwp = dwp; g.db = db; g.amax = amax_ready ? amax_ready : scratch2;
+    g.dwp = dwp; g.db = db;
+    g.amax_x = amax_x ? amax_x : scratch2;
+    g.amax_dy = amax_x ? amax_dy : scratch2 + 1;
+    g.amax_stride = amax_x ? 1 : 0;
     const int stages = R <= 3 ? 4 : 3;
     const int smem = 1024 + std::max(stages * (2 * g.xplane + 2 * kW16DyPlane), 32768) + 128;
     if (smem > 232448) return fail(ODEX_E_UNSUPPORTED, "wgrad(f16): needs %d bytes of shared memory", smem);
@@ -497,18 +540,18 @@ extern "C" int odex_conv2d_wgrad_f16(const float* x0, int ld0, int c0, const flo
     if (B <= 0 || (x1 == nullptr) != (c1 == 0)) return fail(ODEX_E_ARG, "wgrad_f16: bad batch / second source");
     if (!wgrad_f16_supported(c0, c1, N, H, W, R))
         return fail(ODEX_E_UNSUPPORTED, "wgrad_f16: shape not supported (c0=%d c1=%d N=%d HxW=%dx%d R=%d)", c0, c1, N, H, W, R);
-    return launch_wgrad_f16(x0, ld0, c0, x1, ld1, c1, dy, ldy, B, H, W, R, N, dwp, db, scratch2, nullptr, s);
+    return launch_wgrad_f16(x0, ld0, c0, x1, ld1, c1, dy, ldy, B, H, W, R, N, dwp, db, scratch2, nullptr, nullptr, s);
 }
 
 extern "C" int odex_conv2d_wgrad_f16_scaled(const float* x0, int ld0, int c0, const float* x1, int ld1, int c1, const float* dy,
                                             int ldy, int B, int H, int W, int R, int N, float* dwp, float* db,
-                                            const float* amax2, odex_stream_t s_) {
+                                            const float* amax_x, const float* amax_dy, odex_stream_t s_) {
     cudaStream_t s = static_cast<cudaStream_t>(s_);
-    if (!x0 || !dy || !dwp || !amax2) return fail(ODEX_E_ARG, "wgrad_f16_scaled: null pointer");
+    if (!x0 || !dy || !dwp || !amax_x || !amax_dy) return fail(ODEX_E_ARG, "wgrad_f16_scaled: null pointer");
     if (!aligned16(x0) || !aligned16(dy) || (x1 && !aligned16(x1)) || ld0 % 4 || ldy % 4 || (x1 && ld1 % 4))
         return fail(ODEX_E_ALIGN, "wgrad_f16_scaled: pointers / strides must be 16-byte aligned");
     if (B <= 0 || (x1 == nullptr) != (c1 == 0)) return fail(ODEX_E_ARG, "wgrad_f16_scaled: bad batch / second source");
     if (!wgrad_f16_supported(c0, c1, N, H, W, R))
         return fail(ODEX_E_UNSUPPORTED, "wgrad_f16_scaled: shape not supported (c0=%d c1=%d N=%d HxW=%dx%d R=%d)", c0, c1, N, H, W, R);
-    return launch_wgrad_f16(x0, ld0, c0, x1, ld1, c1, dy, ldy, B, H, W, R, N, dwp, db, nullptr, amax2, s);
+    return launch_wgrad_f16(x0, ld0, c0, x1, ld1, c1, dy, ldy, B, H, W, R, N, dwp, db, nullptr, amax_x, amax_dy, s);
 }

@@ -158,7 +158,7 @@ class Backend:
             assert split == 1, "amax_out needs the kind::f16 chain"
             for l, t in enumerate(amax_out):
                 if t is not None:
-                    assert t.dtype == torch.float32 and t.numel() == 1 and t.device == x.device
+                    assert t.dtype == torch.float32 and t.numel() == B and t.is_contiguous() and t.device == x.device
                     d.amax_out[l] = t.data_ptr()
         d.alpha = float(alpha)
         d.alpha_dev = _ptr(alpha_dev)
@@ -178,8 +178,8 @@ class Backend:
                 amax_out: Optional[Sequence[Optional[torch.Tensor]]] = None) -> None:
         """odex_convnet: the whole conv chain in one launch; layer l: v = act(conv(a_l) + bias), v *= act'(aux) (kind 1/2)
         or v = aux + alpha * v (kind 3), stored to out[l] when given (out[-1] required).  split: 0 = w_tc packed with tc = 1
-        (3xTF32), 1 = packed with tc = 2 (two-term fp16 split on kind::f16).  amax_out[l] (split = 1): one-element fp32 tensor
-        that receives max(itself, max |input of layer l|), atomically."""
+        (3xTF32), 1 = packed with tc = 2 (two-term fp16 split on kind::f16).  amax_out[l] (split = 1): fp32 tensor [B] that
+        receives max |input of layer l| per image."""
         self.require(x)
         d = self._convnet_desc(x, w_tc, bias, act, aux, aux_kind, out, alpha, alpha_dev, skip, split, amax_out)
         _lib.check(self.lib.odex_convnet(C.byref(d), _stream()), "odex_convnet")
@@ -210,7 +210,7 @@ class Backend:
                alpha: float = 1.0, alpha_dev: Optional[torch.Tensor] = None, skip: Optional[torch.Tensor] = None,
                amax_out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """odex_conv16(PLAIN): out = act(conv(cat(x0, x1)) + bias), then * act'(aux) (aux_kind 1 / 2) or aux + alpha * v (3).
-        amax_out (all three modes): one-element fp32 tensor <- max(itself, max |sources|), atomically."""
+        amax_out (all three modes): fp32 tensor [B] <- max |sources| per image."""
         self.require(x0)
         d = self._conv16_desc(x0, x1, w_f16, N, R, bias, skip)
         d.amax_out = _ptr(amax_out)
@@ -385,8 +385,8 @@ class Backend:
                             amax: Optional[torch.Tensor] = None) -> None:
         """odex_conv2d_wgrad_packed: dwp [R*R, N, c0+c1] += dy^T X (tensor-core kernel where the shape allows),
         db += colsum(dy).  f16: the kind::f16 kernel with the two-term fp16 split (odex_conv2d_wgrad_f16) where its shape test
-        passes.  amax: 2 device floats {>= max |X|, >= max |dy|} the caller already holds (odex_conv2d_wgrad_f16_scaled: the
-        same kernel without its max pass)."""
+        passes.  amax: (ax, ad), fp32 tensors [B] with ax[b] >= max |X[b]|, ad[b] >= max |dy[b]| the caller already holds
+        (odex_conv2d_wgrad_f16_scaled: the same kernel without its max pass, operands scaled per image)."""
         B, H, W, c0 = x0.shape
         if (f16 or amax is not None) and impl == CONV_AUTO and self.wgrad_f16_shape_ok(c0, 0 if x1 is None else x1.shape[3], dy.shape[3], H, W, R):
             p0, ld0 = _rows(x0)
@@ -398,9 +398,12 @@ class Backend:
             N = dy.shape[3]
             assert dwp.is_contiguous() and tuple(dwp.shape) == (R * R, N, c0 + c1), (tuple(dwp.shape), (R * R, N, c0 + c1))
             if amax is not None:
-                assert amax.dtype == torch.float32 and amax.numel() == 2 and amax.is_contiguous()
+                ax, ad = amax
+                assert ax.dtype == torch.float32 and ad.dtype == torch.float32 and ax.numel() == B and ad.numel() == B
+                assert ax.is_contiguous() and ad.is_contiguous()
                 _lib.check(self.lib.odex_conv2d_wgrad_f16_scaled(p0, ld0, c0, p1, ld1, c1, pdy, ldy, B, H, W, R, N, dwp.data_ptr(),
-                                                                 _ptr(db), amax.data_ptr(), _stream()), "odex_conv2d_wgrad_f16_scaled")
+                                                                 _ptr(db), ax.data_ptr(), ad.data_ptr(), _stream()),
+                           "odex_conv2d_wgrad_f16_scaled")
                 return
             scratch = torch.empty(2, dtype=torch.float32, device=x0.device)
             _lib.check(self.lib.odex_conv2d_wgrad_f16(p0, ld0, c0, p1, ld1, c1, pdy, ldy, B, H, W, R, N, dwp.data_ptr(),

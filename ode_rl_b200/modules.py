@@ -878,10 +878,16 @@ class _EncoderFn(torch.autograd.Function):
         Lf = len(f_op.layers)
         if save and Lf > 1 and all(c.out_channels == C for c, _ in f_op.layers[:-1]):
             arenas = [torch.empty((T, B, H, W, C), dtype=torch.float32, device=x.device) for _ in range(Lf - 1)]
+        # per-image operand maxima of f's layers over the T iterations ([L, 2, T, B]): measured by the chain launches, read by the
+        # merged weight gradients (ConvNetOp.new_maxima)
+        mx_arena = None
+        if save and T > 0 and B > 0 and f_op.maxima_ok(h):
+            mx_arena = torch.empty((Lf, 2, T, B), dtype=torch.float32, device=x.device)
         for n, i in enumerate(order):
             ht = torch.empty_like(h)
             r = f_op.fwd(h, save=save, out=ht, res=h, alpha=1.0, alpha_dev=deltas[n:n + 1],
-                         bufs=[a_[n] for a_ in arenas] if arenas is not None else None)
+                         bufs=[a_[n] for a_ in arenas] if arenas is not None else None,
+                         maxima=mx_arena[:, :, n] if mx_arena is not None else None)
             g = g_op.fwd(x[i], ht, save=save, out=hs[n])
             if save:
                 saved.append((r[1], g[1]))

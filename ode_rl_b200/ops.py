@@ -53,8 +53,8 @@ def _wgrad_scaled() -> bool:
 
 
 class SavedActs(list):
-    """The activations ConvNetOp.fwd(save=True) keeps for the backward, plus the [L, 2] maxima buffer their max |a_l| went into
-    (column 0; the backward adds max |d_l| in column 1).  None: not measured."""
+    """The activations ConvNetOp.fwd(save=True) keeps for the backward, plus the [L, 2, B] maxima buffer their per-image max |a_l|
+    went into ([l, 0]; the backward adds max |d_l| in [l, 1]).  None: not measured."""
     maxima: Optional[torch.Tensor] = None
 
 
@@ -121,8 +121,8 @@ class GradSink:
         """dW(conv) += x^T dy, db += colsum(dy).  While `deferred`, the request is only recorded: weight gradients are off
         the critical path of a backward pass, and requests whose operands are consecutive slices of one buffer (the RK
         stages of a step, allocated as [s, B, ...] arenas) run as ONE launch over s*B images.
-        amax: 2 device floats {>= max |x|, >= max |dy|} (a row of a maxima buffer the chain kernels filled); such requests run on
-        the kind::f16 kernel without a max pass, and only requests that share the row merge."""
+        amax = (ax, ad): per-image maxima [B] of x and dy, as the chain kernels measured them; such requests run on the kind::f16
+        kernel without a max pass, and merge when their maxima are consecutive slices too."""
         if (conv.weight is None or not conv.weight.requires_grad) and (conv.bias is None or not conv.bias.requires_grad):
             return
         if not self.deferred:
@@ -138,13 +138,10 @@ class GradSink:
 
     def flush(self) -> None:
         for conv, items in self._pending.values():
-            # requests measured into the same maxima row merge among themselves (one kind::f16 launch per run), the rest likewise
-            groups: Dict[object, list] = {}
-            for x, dy, amax in items:
-                groups.setdefault(None if amax is None else amax.data_ptr(), []).append((x, dy, amax))
-            for group in groups.values():
-                for x, dy in _slice_runs([(x, dy) for x, dy, _ in group]):
-                    self._launch(conv, x, dy, group[0][2])
+            # requests with measured maxima merge among themselves (one kind::f16 launch per run), the rest likewise
+            for group in ([it for it in items if it[2] is not None], [it for it in items if it[2] is None]):
+                for run in _slice_runs(group):
+                    self._launch(conv, *run)
         self._pending.clear()
 
     def get_packed(self, w: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
@@ -178,30 +175,40 @@ class GradSink:
 
 
 def _slice_runs(items):
-    """[(x, dy)] -> the same requests with every run of consecutive dense slices of one storage merged into one
-    (x [n*B, ...], dy [n*B, ...]) pair."""
+    """[(x, dy[, amax])] -> the same requests with every run of consecutive dense slices of one storage merged into one
+    (x [n*B, ...], dy [n*B, ...][, amax]) request.  amax = (ax, ad) per-image maxima [B] or None; a run merges only while the
+    maxima (when present) are consecutive slices as well, and comes back with ax, ad of n*B entries."""
+    items = [(it[0], it[1], it[2] if len(it) > 2 else None) for it in items]
+    with_amax = any(it[2] is not None for it in items)
     items = sorted(items, key=lambda it: it[0].data_ptr())
+
+    def follows(t0, t1, n):
+        return (t1.shape == t0.shape and t1.is_contiguous() and t1.data_ptr() == t0.data_ptr() + n * t0.numel() * t0.element_size()
+                and t1.untyped_storage().data_ptr() == t0.untyped_storage().data_ptr())
+
     out, i = [], 0
     while i < len(items):
-        x0, d0 = items[i]
+        x0, d0, a0 = items[i]
         n = 1
-        if x0.dim() == 4 and x0.is_contiguous() and d0.is_contiguous():
-            sx, sd = x0.numel() * x0.element_size(), d0.numel() * d0.element_size()
-            while i + n < len(items):
-                x1, d1 = items[i + n]
-                if (x1.shape == x0.shape and d1.shape == d0.shape and x1.is_contiguous() and d1.is_contiguous()
-                        and x1.data_ptr() == x0.data_ptr() + n * sx and d1.data_ptr() == d0.data_ptr() + n * sd
-                        and x1.untyped_storage().data_ptr() == x0.untyped_storage().data_ptr()
-                        and d1.untyped_storage().data_ptr() == d0.untyped_storage().data_ptr()):
-                    n += 1
-                else:
-                    break
+        ok = x0.dim() == 4 and x0.is_contiguous() and d0.is_contiguous() and (a0 is None or (a0[0].is_contiguous() and a0[1].is_contiguous()))
+        while ok and i + n < len(items):
+            x1, d1, a1 = items[i + n]
+            if not (follows(x0, x1, n) and follows(d0, d1, n)) or (a0 is None) != (a1 is None):
+                break
+            if a0 is not None and not (follows(a0[0], a1[0], n) and follows(a0[1], a1[1], n)):
+                break
+            n += 1
         if n > 1:
             B = x0.shape[0]
-            out.append((torch.as_strided(x0, (n * B,) + tuple(x0.shape[1:]), x0.stride()),
-                        torch.as_strided(d0, (n * B,) + tuple(d0.shape[1:]), d0.stride())))
+            run = [torch.as_strided(x0, (n * B,) + tuple(x0.shape[1:]), x0.stride()),
+                   torch.as_strided(d0, (n * B,) + tuple(d0.shape[1:]), d0.stride())]
+            if a0 is not None:
+                run.append((torch.as_strided(a0[0], (n * B,), (1,)), torch.as_strided(a0[1], (n * B,), (1,))))
         else:
-            out.append((x0, d0))
+            run = [x0, d0] + ([a0] if a0 is not None else [])
+        if with_amax and len(run) == 2:
+            run.append(None)
+        out.append(tuple(run))
         i += n
     return out
 
@@ -316,16 +323,19 @@ class ConvNetOp:
         self.c_in = self.layers[0][0].in_channels
         self.c_out = self.layers[-1][0].out_channels
 
-    def new_maxima(self, x: torch.Tensor) -> Optional[torch.Tensor]:
-        """A zeroed [L, 2] maxima buffer for fwd(save=True, maxima=...) when the weight gradients of this chain can use it
-        (fused kind::f16 chain + odex_conv2d_wgrad_f16_scaled), else None.  Row l = {max |a_l|, max |d_l|} over every launch
-        that is given the buffer, so share one only between launches whose operands have the same order of magnitude (the
-        stages of one RK step): a bound far above a launch's own maximum pushes its fp16 operands towards underflow."""
+    def maxima_ok(self, x: torch.Tensor) -> bool:
+        """True when the chain kernels can measure the operand maxima of this input's weight gradients (see new_maxima)."""
         if CONV_SPLIT != "f16" or not _wgrad_scaled() or not self._fused(K.backend(), x):
+            return False
+        return K.backend().wgrad_f16_shape_ok(64, 0, 64, x.shape[1], x.shape[2], 3)
+
+    def new_maxima(self, x: torch.Tensor) -> Optional[torch.Tensor]:
+        """An [L, 2, B] maxima buffer for fwd(save=True, maxima=...) when the weight gradients of this chain can use it (fused
+        kind::f16 chain + odex_conv2d_wgrad_f16_scaled), else None.  [l, 0, b] <- max |a_l[b]| (forward launch), [l, 1, b] <-
+        max |d_l[b]| (backward launch): per image, so launches of any magnitude may later share one weight-gradient launch."""
+        if not self.maxima_ok(x):
             return None
-        if not K.backend().wgrad_f16_shape_ok(64, 0, 64, x.shape[1], x.shape[2], 3):
-            return None
-        return torch.zeros((len(self.layers), 2), dtype=torch.float32, device=x.device)
+        return torch.empty((len(self.layers), 2, x.shape[0]), dtype=torch.float32, device=x.device)
 
     def params(self) -> List[torch.Tensor]:
         ps = []
@@ -354,7 +364,8 @@ class ConvNetOp:
             skip: Optional[torch.Tensor] = None, need_dgrad: bool = False,
             bufs: Optional[List[torch.Tensor]] = None, maxima: Optional[torch.Tensor] = None):
         """bufs: optional caller-owned buffers for the outputs of layers 0 .. L-2 (the saved activations).  maxima: a buffer from
-        new_maxima(); the chain adds max |a_l| of this launch to column 0 and the saved activations carry it to bwd()."""
+        new_maxima() (or an [L, 2, B] view with dense rows); the chain writes max |a_l| per image and the saved activations
+        carry it to bwd()."""
         be = K.backend()
         B, H, W, _ = x.shape
         L = len(self.layers)
@@ -364,7 +375,7 @@ class ConvNetOp:
             f16 = CONV_SPLIT == "f16"
             amax_out = None
             if f16 and save and maxima is not None:
-                amax_out = [maxima[l, 0:1] for l in range(L)]
+                amax_out = [maxima[l, 0] for l in range(L)]
                 saved.maxima = maxima
             if f16:
                 wts = [self.caches[l].get_f16(False).fwd_f16 for l in range(L)]
@@ -465,14 +476,14 @@ class ConvNetOp:
             am = getattr(saved, "maxima", None) if f16 else None
             extra = {}
             if am is not None:
-                extra["amax_out"] = [am[l, 1:2] for l in ls]
+                extra["amax_out"] = [am[l, 1] for l in ls]
             be.convnet(d, wts, [None] * len(ls), [ACT_NONE] * len(ls), aux, kinds, outs, alpha=1.0, split=1 if f16 else 0, **extra)
             grads = {L - 1: d}
             for k, l in enumerate(ls):
                 grads[l - 1] = outs[k]               # outs[k] = gradient w.r.t. the input of layer l = d_{l-1}
             for l in range(L - 1, -1, -1):
                 sink.add_wgrad(self.layers[l][0], saved[l], grads[l],
-                               amax=am[l] if am is not None and l >= lo else None)
+                               amax=(am[l, 0], am[l, 1]) if am is not None and l >= lo else None)
             return grads[-1] if need_dx else None
         for l in range(L - 1, -1, -1):
             conv, _ = self.layers[l]
@@ -540,12 +551,12 @@ class GruOp:
             st_g = torch.empty((B * (2 * C // 32) * 2,), dtype=f32, device=dev)
             st_c = torch.empty((B * (C // 32) * 2,), dtype=f32, device=dev)
             g = torch.empty((B, H, W, 2 * C), dtype=f32, device=dev) if save else None
-            # [2, 2] maxima of this step: row 0 = conv_gates {max |(x, h)|, max |dg|}, row 1 = conv_can {max |(x, rh)|, max |dcpre|};
-            # the conv16 launches measure them for their operand scales anyway, the weight gradients of the step take them
+            # [2, 2, B] per-image maxima of this step: [0] = conv_gates {max |(x, h)|, max |dg|}, [1] = conv_can {max |(x, rh)|,
+            # max |dcpre|}; the conv16 launches measure them for their operand scales anyway, the weight gradients take them
             mx = None
             if save and _wgrad_scaled() and be.wgrad_f16_shape_ok(Cx, C, 2 * C, H, W, R):
-                mx = torch.zeros((2, 2), dtype=f32, device=dev)
-            mxa = (lambda i, j: {"amax_out": mx[i, j:j + 1]}) if mx is not None else (lambda i, j: {})
+                mx = torch.empty((2, 2, B), dtype=f32, device=dev)
+            mxa = (lambda i, j: {"amax_out": mx[i, j]}) if mx is not None else (lambda i, j: {})
             be.conv16_gru_gates(x, h, wg, R, self.cg.bias, self.gn_g.weight, self.gn_g.bias, self.gn_g.eps, z, rh, st_g, g_raw=g,
                                 **mxa(0, 0))
             hnew = out if out is not None else torch.empty((B, H, W, C), dtype=f32, device=dev)
@@ -598,14 +609,14 @@ class GruOp:
         if f16:
             # the data-gradient launch reads dcpre: its max |dcpre| completes row 1 of the maxima before the weight gradient runs
             be.conv16(dcpre, None, self.pc_c.get_f16(True).dgrad_f16, Cx + C, R, None, ACT_NONE, D1,
-                      **({"amax_out": mx[1, 1:2]} if mx is not None else {}))
+                      **({"amax_out": mx[1, 1]} if mx is not None else {}))
         else:
             pc = self.pc_c.get(H, W, Cx, C, True)
             be.conv2d(dcpre, None, pc.dgrad_simt, pc.dgrad_tc, Cx + C, R, None, ACT_NONE, D1)
         gw, gb = sink.get_packed(self.cc.weight), sink.get(self.cc.bias)
         if gw is not None or gb is not None:
             be.conv2d_wgrad_packed(x, rh, dcpre, R, gw if gw is not None else _scratch_packed(self.cc.weight), gb, f16=_wgrad_f16(),
-                                   amax=mx[1] if mx is not None else None)
+                                   amax=(mx[1, 0], mx[1, 1]) if mx is not None else None)
         dg = torch.empty((B, H, W, 2 * C), dtype=f32, device=dev)
         drh = D1[..., Cx:]
         be.gru_gates_bwd(dz, drh, dh_a, g, h, self.gn_g.weight, self.gn_g.bias, st_g, dg, drh,
@@ -614,12 +625,12 @@ class GruOp:
         if f16:
             pgf = self.pc_g.get_f16(True).dgrad_f16
             be.conv16(dg[..., :C], dg[..., C:], pgf, Cx + C, R, None, ACT_NONE, D2, aux=D1, aux_kind=3, alpha=1.0,
-                      **({"amax_out": mx[0, 1:2]} if mx is not None else {}))
+                      **({"amax_out": mx[0, 1]} if mx is not None else {}))
         else:
             pg = self.pc_g.get(H, W, Cx, C, True)
             be.conv2d(dg, None, pg.dgrad_simt, pg.dgrad_tc, Cx + C, R, None, ACT_NONE, D2, res=D1, alpha=1.0)
         gw, gb = sink.get_packed(self.cg.weight), sink.get(self.cg.bias)
         if gw is not None or gb is not None:
             be.conv2d_wgrad_packed(x, h, dg, R, gw if gw is not None else _scratch_packed(self.cg.weight), gb, f16=_wgrad_f16(),
-                                   amax=mx[0] if mx is not None else None)
+                                   amax=(mx[0, 0], mx[0, 1]) if mx is not None else None)
         return D2

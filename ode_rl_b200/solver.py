@@ -80,9 +80,11 @@ def rk_step_fwd(be, op: ConvNetOp, tab: Tableau, y: torch.Tensor, y_next: torch.
         yi_arena = torch.empty((s,) + tuple(y.shape), dtype=y.dtype, device=y.device)
         if all(c.out_channels == y.shape[3] for c, _ in op.layers[:-1]):
             arenas = [torch.empty((s,) + tuple(y.shape), dtype=y.dtype, device=y.device) for _ in range(len(op.layers) - 1)]
-    # one maxima buffer for the s stages of this step (same order of magnitude): their merged weight gradients then run on the
-    # kind::f16 kernel without a max pass (ConvNetOp.new_maxima)
-    maxima = op.new_maxima(y) if save else None
+    # per-image operand maxima of the s stages in an [L, 2, s, B] arena: the merged weight gradients of a layer then run on the
+    # kind::f16 kernel without a max pass (ConvNetOp.new_maxima, GradSink.add_wgrad)
+    mx_arena = None
+    if save and op.maxima_ok(y):
+        mx_arena = torch.empty((len(op.layers), 2, s, y.shape[0]), dtype=torch.float32, device=y.device)
     for i in range(s):
         if i == 0:
             yi = y
@@ -98,7 +100,7 @@ def rk_step_fwd(be, op: ConvNetOp, tab: Tableau, y: torch.Tensor, y_next: torch.
             continue
         kout = k_bufs[i] if k_bufs is not None else None
         r = op.fwd(yi, save=save, out=kout, skip=skip, bufs=[a[i] for a in arenas] if arenas is not None else None,
-                   maxima=maxima)
+                   maxima=mx_arena[:, :, i] if mx_arena is not None else None)
         if save:
             ks.append(r[0])
             saved.append(r[1])

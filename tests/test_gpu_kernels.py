@@ -337,44 +337,73 @@ def test_convnet_f16_split_holds_fp32_accuracy_at_any_magnitude(be, scale):
 
 
 def test_convnet_amax_out_and_scaled_weight_gradient(be):
-    """odex_convnet_desc.amax_out: the kind::f16 chain leaves max |input of layer l| (over all images of the launch, accumulated
-    atomically over launches) where the caller points; odex_conv2d_wgrad_f16_scaled takes such maxima instead of a max pass and
-    must agree with the 3xTF32 weight gradient."""
+    """odex_convnet_desc.amax_out: the kind::f16 chain leaves max |input of layer l| PER IMAGE where the caller points;
+    odex_conv2d_wgrad_f16_scaled takes such maxima instead of a max pass and must agree with the 3xTF32 weight gradient."""
     torch.manual_seed(5)
     B, L = 7, 4
     x = torch.randn(B, 16, 16, 64, device="cuda") * 3.0
     x[2] = 0.0
+    x[4] *= 1e-4
     ws = [torch.randn(64, 64, 3, 3, device="cuda") / 24.0 for _ in range(L)]
     bs = [torch.randn(64, device="cuda") * 0.1 for _ in range(L)]
     acts = [ACT_RELU] * (L - 1) + [ACT_NONE]
     outs = [torch.empty_like(x) for _ in range(L)]
-    am = torch.zeros(L, 2, device="cuda")
+    am = torch.full((L, 2, B), -1.0, device="cuda")
     packs = [be.pack_weights(w, False, 2) for w in ws]
-    be.convnet(x, packs, bs, acts, [None] * L, [0] * L, outs, split=1, amax_out=[am[l, 0:1] for l in range(L)])
+    be.convnet(x, packs, bs, acts, [None] * L, [0] * L, outs, split=1, amax_out=[am[l, 0] for l in range(L)])
     torch.cuda.synchronize()
     ins = [x] + outs[:-1]
     for l in range(L):
-        assert float(am[l, 0]) == float(ins[l].abs().max()), (l, float(am[l, 0]), float(ins[l].abs().max()))
-    # a second launch on smaller data leaves the maxima where they are; on larger data it raises them
-    be.convnet(x * 0.5, packs, bs, acts, [None] * L, [0] * L, [torch.empty_like(x) for _ in range(L)], split=1,
-               amax_out=[am[l, 0:1] for l in range(L)])
-    assert float(am[0, 0]) == float(x.abs().max())
-    be.convnet(x * 4.0, packs, bs, acts, [None] * L, [0] * L, [torch.empty_like(x) for _ in range(L)], split=1,
-               amax_out=[am[l, 0:1] for l in range(L)])
-    assert float(am[0, 0]) == float((x * 4.0).abs().max())
+        assert torch.equal(am[l, 0], ins[l].abs().amax(dim=(1, 2, 3))), l
     # the tf32 chain refuses the request instead of ignoring it
     with pytest.raises(Exception):
         be.convnet(x, [be.pack_weights(w, False, 1) for w in ws], bs, acts, [None] * L, [0] * L, outs, split=0,
-                   amax_out=[am[l, 0:1] for l in range(L)])
-    # weight gradient of layer 1 from (a_1, dy) with bounds {max |a_1| * 4 (see above), a loose bound of max |dy|}
+                   amax_out=[am[l, 0] for l in range(L)])
+    # weight gradient of layer 1 from (a_1, dy) with the measured maxima of a_1 and loose (x37) per-image bounds of dy
     dy = torch.randn(B, 16, 16, 64, device="cuda") * 1e-3
-    am[1, 1] = dy.abs().max() * 37.0
+    am[1, 1] = dy.abs().amax(dim=(1, 2, 3)) * 37.0
     ref, got = torch.zeros(9, 64, 64, device="cuda"), torch.zeros(9, 64, 64, device="cuda")
     rb, gb = torch.zeros(64, device="cuda"), torch.zeros(64, device="cuda")
     be.conv2d_wgrad_packed(ins[1], None, dy, 3, ref, rb)
-    be.conv2d_wgrad_packed(ins[1], None, dy, 3, got, gb, amax=am[1])
+    be.conv2d_wgrad_packed(ins[1], None, dy, 3, got, gb, amax=(am[1, 0], am[1, 1]))
     torch.cuda.synchronize()
     assert rel_err(got, ref) < 1e-5 and rel_err(gb, rb) < 1e-5, (rel_err(got, ref), rel_err(gb, rb))
+
+
+@pytest.mark.parametrize("R,c1,N", [(3, 0, 64), (5, 64, 128)])
+def test_scaled_weight_gradient_with_images_of_any_magnitude(be, R, c1, N):
+    """Per-image operand scales with one common PRODUCT scale (csrc/wgrad_f16.cu): images whose X is 1e11 times smaller while
+    their dy is 1e11 times larger (a state that blows up over a rollout, its adjoint shrinking: the products stay comparable) all
+    contribute at full accuracy -- one pair of maxima for the whole tensor would flush them to zero.  Also: an all-zero image, an
+    image that contributes nothing (both operands tiny), tiny and huge overall magnitudes."""
+    torch.manual_seed(R)
+    B = 12
+    for gx, gd in ((1.0, 1.0), (1e-9, 1e-9), (1e8, 1e-3)):
+        mag = torch.tensor([10.0 ** (-11 * i / (B - 1)) for i in range(B)], device="cuda").view(B, 1, 1, 1)
+        x0 = torch.randn(B, 16, 16, 64, device="cuda") * mag * gx
+        x1 = torch.randn(B, 16, 16, c1, device="cuda") * mag * gx * 0.3 if c1 else None
+        dy = torch.randn(B, 16, 16, N, device="cuda") / mag * gd
+        x0[3] = 0.0
+        if x1 is not None:
+            x1[3] = 0.0
+        dy[5] *= 1e-20                                  # image 5: negligible product
+        xm = x0.abs().amax(dim=(1, 2, 3)) if x1 is None else torch.maximum(x0.abs().amax(dim=(1, 2, 3)), x1.abs().amax(dim=(1, 2, 3)))
+        dm = dy.abs().amax(dim=(1, 2, 3))
+        Cc = 64 + c1
+        ref, got = torch.zeros(R * R, N, Cc, device="cuda"), torch.zeros(R * R, N, Cc, device="cuda")
+        rb, gb = torch.zeros(N, device="cuda"), torch.zeros(N, device="cuda")
+        be.conv2d_wgrad_packed(x0, x1, dy, R, ref, rb)
+        be.conv2d_wgrad_packed(x0, x1, dy, R, got, gb, amax=(xm.contiguous(), dm.contiguous()))
+        torch.cuda.synchronize()
+        assert bool(torch.isfinite(got).all())
+        assert rel_err(got, ref) < 1e-5 and rel_err(gb, rb) < 1e-5, (gx, gd, rel_err(got, ref), rel_err(gb, rb))
+        # every image on its own: the per-image contributions are right, not only their sum
+        for b in (0, B - 1):
+            r1, g1 = torch.zeros_like(ref), torch.zeros_like(ref)
+            be.conv2d_wgrad_packed(x0[b:b + 1], None if x1 is None else x1[b:b + 1], dy[b:b + 1], R, r1, None)
+            be.conv2d_wgrad_packed(x0[b:b + 1], None if x1 is None else x1[b:b + 1], dy[b:b + 1], R, g1, None,
+                                   amax=(xm[b:b + 1].contiguous(), dm[b:b + 1].contiguous()))
+            assert rel_err(g1, r1) < 1e-5, (gx, gd, b, rel_err(g1, r1))
 
 
 @pytest.mark.parametrize("split", [0, 1], ids=["tf32", "f16"])
@@ -613,7 +642,7 @@ def test_conv16_plain_matches_exact_fp32_conv(be, R, nsrc, N):
 
 @pytest.mark.parametrize("R", [3, 5])
 def test_conv16_amax_out_feeds_the_scaled_weight_gradient(be, R):
-    """odex_conv16_desc.amax_out: max |sources| over the launch, accumulated atomically, in all three modes; the 5x5 two-source
+    """odex_conv16_desc.amax_out: max |sources| per image, in all three modes; the 5x5 two-source
     weight gradients of the ConvGRU take such pairs (odex_conv2d_wgrad_f16_scaled) and must agree with the 3xTF32 kernel."""
     torch.manual_seed(9 + R)
     B, Cn = 5, 64
@@ -626,25 +655,25 @@ def test_conv16_amax_out_feeds_the_scaled_weight_gradient(be, R):
     bg, bc = torch.randn(2 * Cn, device="cuda") * 0.1, torch.randn(Cn, device="cuda") * 0.1
     gam_g, bet_g = torch.rand(2 * Cn, device="cuda") + 0.5, torch.randn(2 * Cn, device="cuda") * 0.1
     gam_c, bet_c = torch.rand(Cn, device="cuda") + 0.5, torch.randn(Cn, device="cuda") * 0.1
-    mx = torch.zeros(2, 2, device="cuda")
+    mx = torch.full((2, 2, B), -1.0, device="cuda")
     z, rh, stg = torch.empty(B, 16, 16, Cn, device="cuda"), torch.empty(B, 16, 16, Cn, device="cuda"), torch.empty(B * 8, device="cuda")
-    be.conv16_gru_gates(x, h, be.pack_weights(wg, False, 2), R, bg, gam_g, bet_g, 1e-5, z, rh, stg, amax_out=mx[0, 0:1])
+    be.conv16_gru_gates(x, h, be.pack_weights(wg, False, 2), R, bg, gam_g, bet_g, 1e-5, z, rh, stg, amax_out=mx[0, 0])
     hn, stc = torch.empty(B, 16, 16, Cn, device="cuda"), torch.empty(B * 4, device="cuda")
-    be.conv16_gru_out(x, rh, be.pack_weights(wc, False, 2), R, bc, gam_c, bet_c, 1e-5, z, h, hn, stc, amax_out=mx[1, 0:1])
+    be.conv16_gru_out(x, rh, be.pack_weights(wc, False, 2), R, bc, gam_c, bet_c, 1e-5, z, h, hn, stc, amax_out=mx[1, 0])
     dg = torch.randn(B, 16, 16, 2 * Cn, device="cuda") * 1e-4
     D = torch.empty(B, 16, 16, 2 * Cn, device="cuda")
-    be.conv16(dg[..., :Cn], dg[..., Cn:], be.pack_weights(wg, True, 2), 2 * Cn, R, None, ACT_NONE, D, amax_out=mx[0, 1:2])
+    be.conv16(dg[..., :Cn], dg[..., Cn:], be.pack_weights(wg, True, 2), 2 * Cn, R, None, ACT_NONE, D, amax_out=mx[0, 1])
     dc = torch.randn(B, 16, 16, Cn, device="cuda") * 1e-2
-    be.conv16(dc, None, be.pack_weights(wc, True, 2), 2 * Cn, R, None, ACT_NONE, D, amax_out=mx[1, 1:2])
+    be.conv16(dc, None, be.pack_weights(wc, True, 2), 2 * Cn, R, None, ACT_NONE, D, amax_out=mx[1, 1])
     torch.cuda.synchronize()
-    want = [[max(float(x.abs().max()), float(h.abs().max())), float(dg.abs().max())],
-            [max(float(x.abs().max()), float(rh.abs().max())), float(dc.abs().max())]]
-    assert mx.tolist() == want, (mx.tolist(), want)
+    pm = lambda t: t.abs().amax(dim=(1, 2, 3))      # noqa: E731
+    assert torch.equal(mx[0, 0], torch.maximum(pm(x), pm(h))) and torch.equal(mx[0, 1], pm(dg))
+    assert torch.equal(mx[1, 0], torch.maximum(pm(x), pm(rh))) and torch.equal(mx[1, 1], pm(dc))
     for (x1, dy, N, row) in ((h, dg, 2 * Cn, 0), (rh, dc, Cn, 1)):
         ref, got = torch.zeros(R * R, N, 2 * Cn, device="cuda"), torch.zeros(R * R, N, 2 * Cn, device="cuda")
         rb, gb = torch.zeros(N, device="cuda"), torch.zeros(N, device="cuda")
         be.conv2d_wgrad_packed(x, x1, dy, R, ref, rb)
-        be.conv2d_wgrad_packed(x, x1, dy, R, got, gb, amax=mx[row])
+        be.conv2d_wgrad_packed(x, x1, dy, R, got, gb, amax=(mx[row, 0], mx[row, 1]))
         torch.cuda.synchronize()
         assert rel_err(got, ref) < 1e-5 and rel_err(gb, rb) < 1e-5, (row, rel_err(got, ref), rel_err(gb, rb))
 

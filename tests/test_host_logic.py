@@ -101,13 +101,17 @@ def test_dopri5_gradients(fake_backend, nonlinear):
             assert rel_l2(p.grad, ps[n].grad) < 1e-3, n
 
 
-def test_encoder_recurrence_forward_and_grad(fake_backend):
+@pytest.mark.parametrize("C,hw", [(32, (8, 16)), (64, (16, 16))], ids=["c32", "fused_chain_shape"])
+def test_encoder_recurrence_forward_and_grad(fake_backend, C, hw):
+    """(64, 16x16): f runs as the fused chain with per-image maxima in a [L, 2, T, B] arena, and the weight gradients merged over
+    the T iterations take them (the fake backend checks every pair against the operands it is handed)."""
     torch.manual_seed(0)
-    f = make_ode_func(odex, C=32, n_units=32)
-    cell = odex.ODEConvGRUCell(f, None, (8, 16), 32, device=torch.device("cpu"))
+    f = make_ode_func(odex, C=C, n_units=C)
+    cell = odex.ODEConvGRUCell(f, None, hw, C, device=torch.device("cpu"))
     obs, _ = timesteps(5, 5)
     torch.manual_seed(4)
-    x = torch.randn(5, 2, 32, 8, 16, requires_grad=True)
+    x = torch.randn(5, 2, C, hw[0], hw[1], requires_grad=True)
+    n_scaled = fake_backend.wgrad_scaled
     mean, std = cell(x, obs)
     w1, w2 = torch.randn_like(mean), torch.randn_like(std)
     ((mean * w1).sum() + (std * w2).sum()).backward()
@@ -119,6 +123,7 @@ def test_encoder_recurrence_forward_and_grad(fake_backend):
     assert rel_err(x.grad, x1.grad) < 1e-4
     for n, p in cell.named_parameters():
         assert rel_err(p.grad, ps[n].grad) < 2e-4, n
+    assert (fake_backend.wgrad_scaled > n_scaled) == (C == 64)
     yi, lat = cell.run_ode_conv_gru(x.detach(), obs)
     ry, rl = refmodel.run_ode_conv_gru(_sd(cell), x.detach(), obs)
     assert lat.shape == rl.shape and rel_err(lat, rl) < 1e-5 and rel_err(yi, ry) < 1e-5

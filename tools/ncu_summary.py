@@ -8,7 +8,7 @@ import re
 import subprocess
 import sys
 
-KERNELS = ["convnet_f16_kernel", "conv16_f16_kernel", "wgrad_tc_kernel", "lincomb_kernel"]
+KERNELS = ["convnet_f16_kernel", "conv16_f16_kernel", "wgrad_f16_kernel", "wgrad_tc_kernel", "lincomb_kernel"]
 METRICS = [
     ("launch__grid_size", "grid"),
     ("launch__registers_per_thread", "registers / thread"),
