@@ -23,6 +23,7 @@ import torch.nn as nn
 
 from . import kernels as K
 from .kernels import ACT_NONE, CONV_TC
+from . import ops as _ops
 from .ops import ConvNetOp, GradSink, GruOp, _wgrad_f16, from_nhwc, live, live_input, to_nhwc
 from .solver import FIXED, odeint_dopri5, odeint_fixed
 
@@ -133,6 +134,34 @@ def _ct_dwt(dw3: torch.Tensor, cin: int, cout: int) -> torch.Tensor:
     return torch.stack(rows, dim=-2).permute(1, 0, 2, 3).contiguous()                                  # [Cin, Cout, 4, 4]
 
 
+# ---- the 3x3 "same" convolutions of ConvEncode / ConvDecode on the 16x16 cell grid with 64-channel sources (config A): the
+# image-resident kind::f16 kernel of the ConvGRU (odex_conv16, two-term fp16 split) instead of the 3xTF32 tile kernel, and --
+# since that kernel measures its sources' per-image maxima anyway -- the weight gradient without a max pass
+# (odex_conv2d_wgrad_f16_scaled).  Other shapes (VidODE's 32x32 ... 128x128) stay on odex_conv2d / odex_conv2d_wgrad_packed.
+def _c16_ok(be, x: torch.Tensor, n_in: int, n_out: int) -> bool:
+    return (_ops.CONV_SPLIT == "f16" and _ops.CONV_IMPL != "simt" and hasattr(be, "conv16") and x.dim() == 4
+            and tuple(x.shape[1:3]) == (16, 16) and x.shape[3] == n_in and n_in in (64, 128) and n_out % 64 == 0
+            and be.conv16_shape_ok(x[..., :64], x[..., 64:] if n_in == 128 else None, n_out, 3))
+
+
+def _conv3(be, x: torch.Tensor, w3: torch.Tensor, dgrad: bool, n_out: int, bias, out: torch.Tensor, want_amax: bool):
+    """out = conv3x3(x; w3) (dgrad: with the transposed operator of w3) + bias.  Returns the per-image max |x| [n] when the
+    kind::f16 kernel ran and want_amax, else None."""
+    n_in = x.shape[3]
+    if _c16_ok(be, x, n_in, n_out):
+        amax = torch.empty((x.shape[0],), dtype=torch.float32, device=x.device) if want_amax and _ops._wgrad_scaled() else None
+        be.conv16(x[..., :64], x[..., 64:] if n_in == 128 else None, be.pack_weights(w3, dgrad=dgrad, tc=2), n_out, 3, bias,
+                  ACT_NONE, out, **({"amax_out": amax} if amax is not None else {}))
+        return amax
+    be.conv2d(x, None, None, be.pack_weights(w3, dgrad=dgrad, tc=True), n_out, 3, bias, ACT_NONE, out, impl=CONV_TC)
+    return None
+
+
+def _conv3_wgrad(be, x: torch.Tensor, dy: torch.Tensor, dwp: torch.Tensor, db, amax_x, amax_dy) -> None:
+    both = amax_x is not None and amax_dy is not None
+    be.conv2d_wgrad_packed(x, None, dy, 3, dwp, db, f16=_wgrad_f16(), **({"amax": (amax_x, amax_dy)} if both else {}))
+
+
 class _ConvT4x4s2Fn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor]):
@@ -146,7 +175,7 @@ class _ConvT4x4s2Fn(torch.autograd.Function):
         w3 = _ct_w3(weight.float())
         b3 = bias.detach().float().repeat(4) if bias is not None else None
         P = torch.empty((n, H, W, 4 * cout), dtype=torch.float32, device=xn.device)
-        be.conv2d(xn, None, None, be.pack_weights(w3, dgrad=False, tc=True), 4 * cout, 3, b3, ACT_NONE, P, impl=CONV_TC)
+        ctx.amax_x = _conv3(be, xn, w3, False, 4 * cout, b3, P, True)
         ctx.save_for_backward(xn, w3)
         ctx.has_bias = bias is not None
         return P                                                # phase-blocked: P[n, Y, X, (a*2+b)*Cout + co]
@@ -159,14 +188,15 @@ class _ConvT4x4s2Fn(torch.autograd.Function):
         cout = w3.shape[0] // 4
         dP = dP.float().contiguous()
         dx = dw = db = None
+        amax_dy = None
         if ctx.needs_input_grad[0]:
             dxn = torch.empty((n, H, W, cin), dtype=torch.float32, device=xn.device)
-            be.conv2d(dP, None, None, be.pack_weights(w3, dgrad=True, tc=True), cin, 3, None, ACT_NONE, dxn, impl=CONV_TC)
+            amax_dy = _conv3(be, dP, w3, True, cin, None, dxn, ctx.amax_x is not None)
             dx = from_nhwc(dxn)
         if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
             dwp = torch.zeros((9, 4 * cout, cin), dtype=torch.float32, device=xn.device)
             db3 = torch.zeros((4 * cout,), dtype=torch.float32, device=xn.device)
-            be.conv2d_wgrad_packed(xn, None, dP, 3, dwp, db3, f16=_wgrad_f16())
+            _conv3_wgrad(be, xn, dP, dwp, db3, ctx.amax_x, amax_dy)
             dw3 = torch.zeros((4 * cout, cin, 3, 3), dtype=torch.float32, device=xn.device)
             be.wgrad_unpack(dwp, dw3)
             dw = _ct_dwt(dw3, cin, cout)
@@ -236,8 +266,7 @@ class _Conv3x3s2Fn(torch.autograd.Function):
         xs = x.detach().float().reshape(n, cin, H, 2, W, 2).permute(0, 2, 4, 3, 5, 1).reshape(n, H, W, 4 * cin).contiguous()
         w3 = _cs_w3(weight.float())
         out = torch.empty((n, H, W, cout), dtype=torch.float32, device=x.device)
-        be.conv2d(xs, None, None, be.pack_weights(w3, dgrad=False, tc=True), cout, 3,
-                  bias.detach().float() if bias is not None else None, ACT_NONE, out, impl=CONV_TC)
+        ctx.amax_x = _conv3(be, xs, w3, False, cout, bias.detach().float() if bias is not None else None, out, True)
         ctx.save_for_backward(xs, w3)
         ctx.has_bias = bias is not None
         ctx.cin, ctx.k = cin, weight.shape[-1]
@@ -253,14 +282,15 @@ class _Conv3x3s2Fn(torch.autograd.Function):
         if not dy.is_contiguous():
             dy = dy.contiguous()
         dx = dw = db = None
+        amax_dy = None
         if ctx.needs_input_grad[0]:
             dxs = torch.empty((n, H, W, c4), dtype=torch.float32, device=xs.device)
-            be.conv2d(dy, None, None, be.pack_weights(w3, dgrad=True, tc=True), c4, 3, None, ACT_NONE, dxs, impl=CONV_TC)
+            amax_dy = _conv3(be, dy, w3, True, c4, None, dxs, ctx.amax_x is not None)
             dx = dxs.view(n, H, W, 2, 2, cin).permute(0, 5, 1, 3, 2, 4).reshape(n, cin, 2 * H, 2 * W)
         if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
             dwp = torch.zeros((9, cout, c4), dtype=torch.float32, device=xs.device)
             dbv = torch.zeros((cout,), dtype=torch.float32, device=xs.device)
-            be.conv2d_wgrad_packed(xs, None, dy, 3, dwp, dbv, f16=_wgrad_f16())
+            _conv3_wgrad(be, xs, dy, dwp, dbv, ctx.amax_x, amax_dy)
             dw3 = torch.zeros((cout, c4, 3, 3), dtype=torch.float32, device=xs.device)
             be.wgrad_unpack(dwp, dw3)
             dw = _cs_dw(dw3, cout, cin, ctx.k)
@@ -282,8 +312,7 @@ class _ConvCellsFn(torch.autograd.Function):
         xs = xs.detach()
         w3 = _cs_w3(weight.float())
         out = torch.empty((n, H, W, cout), dtype=torch.float32, device=xs.device)
-        be.conv2d(xs, None, None, be.pack_weights(w3, dgrad=False, tc=True), cout, 3,
-                  bias.detach().float() if bias is not None else None, ACT_NONE, out, impl=CONV_TC)
+        ctx.amax_x = _conv3(be, xs, w3, False, cout, bias.detach().float() if bias is not None else None, out, True)
         ctx.save_for_backward(xs, w3)
         ctx.has_bias = bias is not None
         ctx.cin, ctx.k = c4 // 4, weight.shape[-1]
@@ -299,13 +328,14 @@ class _ConvCellsFn(torch.autograd.Function):
         if not dy.is_contiguous():
             dy = dy.contiguous()
         dxs = dw = db = None
+        amax_dy = None
         if ctx.needs_input_grad[0]:
             dxs = torch.empty((n, H, W, c4), dtype=torch.float32, device=xs.device)
-            be.conv2d(dy, None, None, be.pack_weights(w3, dgrad=True, tc=True), c4, 3, None, ACT_NONE, dxs, impl=CONV_TC)
+            amax_dy = _conv3(be, dy, w3, True, c4, None, dxs, ctx.amax_x is not None)
         if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
             dwp = torch.zeros((9, cout, c4), dtype=torch.float32, device=xs.device)
             dbv = torch.zeros((cout,), dtype=torch.float32, device=xs.device)
-            be.conv2d_wgrad_packed(xs, None, dy, 3, dwp, dbv, f16=_wgrad_f16())
+            _conv3_wgrad(be, xs, dy, dwp, dbv, ctx.amax_x, amax_dy)
             dw3 = torch.zeros((cout, c4, 3, 3), dtype=torch.float32, device=xs.device)
             be.wgrad_unpack(dwp, dw3)
             dw = _cs_dw(dw3, cout, cin, ctx.k)
