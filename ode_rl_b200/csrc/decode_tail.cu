@@ -18,8 +18,10 @@ constexpr int kDtCells = 16;                 // cells per side
 constexpr int kDtC = 32;                     // channels of the hidden layer
 constexpr int kDtCh = 4 * kDtC;              // phase-blocked channels per cell
 constexpr int kDtPad = kDtCells + 2;
-constexpr int kDtFwdSmem = (kDtPad * kDtPad * kDtCh + 16 * kDtC) * 4;
-constexpr int kDtBwdSmem = (kDtCells * kDtCells * kDtCh + 66 * 66 + 16 * kDtC + 8) * 4;
+constexpr int kDtChP = kDtCh + 4;            // cell pitch in shared memory: 132 floats, so the 8 lanes of a 128-bit access that sit
+                                             // on neighbouring cells fall on different banks (a 128-float pitch is an 8-way conflict)
+constexpr int kDtFwdSmem = (kDtPad * kDtPad * kDtChP + 16 * kDtC) * 4;
+constexpr int kDtBwdSmem = (kDtCells * kDtCells * kDtChP + 66 * 66 + 16 * kDtC + 8) * 4;
 
 __device__ __forceinline__ float leaky(float v, float slope) { return v > 0.f ? v : v * slope; }
 
@@ -31,22 +33,31 @@ __global__ void __launch_bounds__(256, 1)
 decode_tail_fwd_kernel(const float* __restrict__ p, const float* __restrict__ w, const float* __restrict__ b, float slope,
                        float* __restrict__ out) {
     extern __shared__ float sm[];
-    float* tile = sm;                                   // [18][18][128], zero border
-    float* ws = sm + kDtPad * kDtPad * kDtCh;           // [16 taps][32 ci]
+    float* tile = sm;                                   // [18][18][132], zero border
+    float* ws = sm + kDtPad * kDtPad * kDtChP;          // [16 taps][32 ci]
     pdl_wait();
     pdl_trigger();
     const int tid = threadIdx.x;
     const float* src = p + static_cast<long>(blockIdx.x) * kDtCells * kDtCells * kDtCh;
     for (int i = tid; i < 16 * kDtC; i += 256) ws[(i % 16) * kDtC + i / 16] = w[i];        // w[ci][tap] -> ws[tap][ci]
-    for (int i = tid; i < kDtPad * kDtPad * (kDtCh / 4); i += 256) {
-        const int cell = i / (kDtCh / 4), q = i % (kDtCh / 4);
-        const int yy = cell / kDtPad, xx = cell % kDtPad;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (yy >= 1 && yy <= kDtCells && xx >= 1 && xx <= kDtCells) {
-            v = ld4(src + ((yy - 1) * kDtCells + (xx - 1)) * kDtCh + 4 * q);
-            v.x = leaky(v.x, slope); v.y = leaky(v.y, slope); v.z = leaky(v.z, slope); v.w = leaky(v.w, slope);
+    // zero border: 68 cells
+    for (int i = tid; i < 68 * (kDtCh / 4); i += 256) {
+        const int c = i / (kDtCh / 4), q = i % (kDtCh / 4);
+        const int yy = c < 18 ? 0 : (c < 36 ? 17 : 1 + (c - 36) / 2), xx = c < 18 ? c : (c < 36 ? c - 18 : ((c - 36) & 1) * 17);
+        st4(tile + (yy * kDtPad + xx) * kDtChP + 4 * q, make_float4(0.f, 0.f, 0.f, 0.f));
+    }
+    // interior: the image's 128 KB read once, fully coalesced, 8 independent 16-byte loads in flight per thread
+#pragma unroll 1
+    for (int i0 = 0; i0 < kDtCells * kDtCells * (kDtCh / 4); i0 += 8 * 256) {
+        float4 v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = ld4(src + 4 * (i0 + k * 256 + tid));
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int i = i0 + k * 256 + tid, cell = i >> 5, q = i & 31;
+            v[k].x = leaky(v[k].x, slope); v[k].y = leaky(v[k].y, slope); v[k].z = leaky(v[k].z, slope); v[k].w = leaky(v[k].w, slope);
+            st4(tile + ((1 + (cell >> 4)) * kDtPad + 1 + (cell & 15)) * kDtChP + 4 * q, v[k]);
         }
-        st4(tile + cell * kDtCh + 4 * q, v);
     }
     __syncthreads();
     const int Y = tid / kDtCells, X = tid % kDtCells;
@@ -63,7 +74,7 @@ decode_tail_fwd_kernel(const float* __restrict__ p, const float* __restrict__ w,
         for (int u = 0; u < 4; ++u)
 #pragma unroll
             for (int c = 0; c < 4; ++c)
-                h[u][c] = ld4(tile + ((Y + 1 + dt_dr(u)) * kDtPad + (X + 1 + dt_dr(c))) * kDtCh +
+                h[u][c] = ld4(tile + ((Y + 1 + dt_dr(u)) * kDtPad + (X + 1 + dt_dr(c))) * kDtChP +
                               (dt_ph(u) * 2 + dt_ph(c)) * kDtC + 4 * q);
 #pragma unroll
         for (int t = 0; t < 16; ++t) wt[t] = ld4(ws + t * kDtC + 4 * q);
@@ -93,76 +104,113 @@ __global__ void __launch_bounds__(256, 1)
 decode_tail_bwd_kernel(const float* __restrict__ p, const float* __restrict__ dout, const float* __restrict__ w, float slope,
                        float* __restrict__ dp, float* __restrict__ dw, float* __restrict__ db) {
     extern __shared__ float sm[];
-    float* ht = sm;                                            // [256 cells][128]: h = leaky(P), for the weight gradient
-    float* dt = ht + kDtCells * kDtCells * kDtCh;              // [66][66]: dout with a zero border, index (oy + 1, ox + 1)
+    float* ht = sm;                                            // [256 cells][132]: h = leaky(P), for the weight gradient
+    float* dt = ht + kDtCells * kDtCells * kDtChP;             // [66][66]: dout with a zero border, index (oy + 1, ox + 1)
     float* ws = dt + 66 * 66;                                  // [16 taps][32 ci]
     float* red = ws + 16 * kDtC;                               // [8]
     pdl_wait();
     pdl_trigger();
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const long img = blockIdx.x;
     const float* src = p + img * kDtCells * kDtCells * kDtCh;
     const float* dsrc = dout + img * 64 * 64;
     for (int i = tid; i < 16 * kDtC; i += 256) ws[(i % 16) * kDtC + i / 16] = w[i];
+    // dout tile: zero border (260 entries), interior by coalesced 16-byte loads
+    for (int i = tid; i < 260; i += 256) {
+        const int yy = i < 66 ? 0 : (i < 132 ? 65 : 1 + (i - 132) / 2), xx = i < 66 ? i : (i < 132 ? i - 66 : ((i - 132) & 1) * 65);
+        dt[yy * 66 + xx] = 0.f;
+    }
     float bsum = 0.f;
-    for (int i = tid; i < 66 * 66; i += 256) {
-        const int yy = i / 66, xx = i % 66;
-        float v = 0.f;
-        if (yy >= 1 && yy <= 64 && xx >= 1 && xx <= 64) v = dsrc[(yy - 1) * 64 + xx - 1];
-        dt[i] = v;
-        bsum += v;
+    {
+        float4 v[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) v[k] = ld4(dsrc + 4 * (k * 256 + tid));
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int i = k * 256 + tid, yy = 1 + (i >> 4), xx = 1 + 4 * (i & 15);
+            float* d = dt + yy * 66 + xx;
+            d[0] = v[k].x; d[1] = v[k].y; d[2] = v[k].z; d[3] = v[k].w;
+            bsum += (v[k].x + v[k].y) + (v[k].z + v[k].w);
+        }
     }
     __syncthreads();
-    // ---- phase A: thread = cell; dP for its 4 fine pixels x 32 channels, h into shared memory
+    // ---- phase A: lane = (cell of a group of 4, 16-byte chunk q of the 32 channels): P read and dP written in 128-byte runs;
+    // dP[cell][ph][ci] = leaky'(P) * sum_t dout[2fy-1+kh][2fx-1+kw] * w[ci][t]; h = leaky(P) into shared memory
     {
-        const int Y = tid / kDtCells, X = tid % kDtCells;
-#pragma unroll 1
-        for (int ph = 0; ph < 4; ++ph) {
-            const int fy = 2 * Y + (ph >> 1), fx = 2 * X + (ph & 1);
-            float dv[16];
+        const int q = lane & 7, sub = lane >> 3;
+        float4 wt[16];
 #pragma unroll
-            for (int kh = 0; kh < 4; ++kh)
-#pragma unroll
-                for (int kw = 0; kw < 4; ++kw) dv[kh * 4 + kw] = dt[(2 * fy + kh) * 66 + 2 * fx + kw];   // dout[2fy-1+kh][2fx-1+kw]
+        for (int t = 0; t < 16; ++t) wt[t] = ld4(ws + t * kDtC + 4 * q);
 #pragma unroll 2
-            for (int q = 0; q < kDtC / 4; ++q) {
-                const int off = tid * kDtCh + ph * kDtC + 4 * q;
-                const float4 pv = ld4(src + off);
+        for (int it = 0; it < 8; ++it) {
+            const int cell = warp * 32 + it * 4 + sub;
+            const int Y = cell >> 4, X = cell & 15;
+            float4 pv[4];
+#pragma unroll
+            for (int ph = 0; ph < 4; ++ph) pv[ph] = ld4(src + cell * kDtCh + ph * kDtC + 4 * q);
+#pragma unroll
+            for (int ph = 0; ph < 4; ++ph) {
+                const int fy = 2 * Y + (ph >> 1), fx = 2 * X + (ph & 1);
                 float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-                for (int t = 0; t < 16; ++t) {
-                    const float4 ww = ld4(ws + t * kDtC + 4 * q);
-                    g.x = fmaf(dv[t], ww.x, g.x); g.y = fmaf(dv[t], ww.y, g.y);
-                    g.z = fmaf(dv[t], ww.z, g.z); g.w = fmaf(dv[t], ww.w, g.w);
+                for (int kh = 0; kh < 4; ++kh) {
+                    const float2 d01 = *reinterpret_cast<const float2*>(dt + (2 * fy + kh) * 66 + 2 * fx);
+                    const float2 d23 = *reinterpret_cast<const float2*>(dt + (2 * fy + kh) * 66 + 2 * fx + 2);
+                    const float dv[4] = {d01.x, d01.y, d23.x, d23.y};
+#pragma unroll
+                    for (int kw = 0; kw < 4; ++kw) {
+                        const float4 ww = wt[kh * 4 + kw];
+                        g.x = fmaf(dv[kw], ww.x, g.x); g.y = fmaf(dv[kw], ww.y, g.y);
+                        g.z = fmaf(dv[kw], ww.z, g.z); g.w = fmaf(dv[kw], ww.w, g.w);
+                    }
                 }
-                g.x *= pv.x > 0.f ? 1.f : slope; g.y *= pv.y > 0.f ? 1.f : slope;
-                g.z *= pv.z > 0.f ? 1.f : slope; g.w *= pv.w > 0.f ? 1.f : slope;
-                st4(dp + img * kDtCells * kDtCells * kDtCh + off, g);
-                st4(ht + off, make_float4(leaky(pv.x, slope), leaky(pv.y, slope), leaky(pv.z, slope), leaky(pv.w, slope)));
+                const float4 pp = pv[ph];
+                g.x *= pp.x > 0.f ? 1.f : slope; g.y *= pp.y > 0.f ? 1.f : slope;
+                g.z *= pp.z > 0.f ? 1.f : slope; g.w *= pp.w > 0.f ? 1.f : slope;
+                st4(dp + img * kDtCells * kDtCells * kDtCh + cell * kDtCh + ph * kDtC + 4 * q, g);
+                st4(ht + cell * kDtChP + ph * kDtC + 4 * q,
+                    make_float4(leaky(pp.x, slope), leaky(pp.y, slope), leaky(pp.z, slope), leaky(pp.w, slope)));
             }
         }
     }
     __syncthreads();
-    // ---- phase B: thread = (channel, pair of taps); dw over the image's 1024 fine pixels
+    // ---- phase B: lane = channel, warp = 32 cells; all 16 taps per h value (dout window by broadcast 8-byte loads), then the
+    // 8 warps' partial sums meet in shared memory: 512 atomics per image
     if (dw) {
-        const int ci = tid & 31, t0 = (tid >> 5) * 2;
-        const int kh0 = t0 >> 2, kw0 = t0 & 3;                 // taps t0, t0 + 1 share kh (t0 is even)
-        float a0 = 0.f, a1 = 0.f;
-#pragma unroll 4
-        for (int px = 0; px < 4 * kDtCells * kDtCells; ++px) {
-            const int cell = px >> 2, ph = px & 3;
-            const int fy = 2 * (cell / kDtCells) + (ph >> 1), fx = 2 * (cell % kDtCells) + (ph & 1);
-            const float h = ht[cell * kDtCh + ph * kDtC + ci];
-            const float* d = dt + (2 * fy + kh0) * 66 + 2 * fx + kw0;
-            a0 = fmaf(h, d[0], a0);
-            a1 = fmaf(h, d[1], a1);
+        float acc[16];
+#pragma unroll
+        for (int t = 0; t < 16; ++t) acc[t] = 0.f;
+#pragma unroll 1
+        for (int c = 0; c < 32; ++c) {
+            const int cell = warp * 32 + c;
+            const int Y = cell >> 4, X = cell & 15;
+#pragma unroll
+            for (int ph = 0; ph < 4; ++ph) {
+                const int fy = 2 * Y + (ph >> 1), fx = 2 * X + (ph & 1);
+                const float h = ht[cell * kDtChP + ph * kDtC + lane];
+#pragma unroll
+                for (int kh = 0; kh < 4; ++kh) {
+                    const float2 d01 = *reinterpret_cast<const float2*>(dt + (2 * fy + kh) * 66 + 2 * fx);
+                    const float2 d23 = *reinterpret_cast<const float2*>(dt + (2 * fy + kh) * 66 + 2 * fx + 2);
+                    acc[kh * 4 + 0] = fmaf(h, d01.x, acc[kh * 4 + 0]); acc[kh * 4 + 1] = fmaf(h, d01.y, acc[kh * 4 + 1]);
+                    acc[kh * 4 + 2] = fmaf(h, d23.x, acc[kh * 4 + 2]); acc[kh * 4 + 3] = fmaf(h, d23.y, acc[kh * 4 + 3]);
+                }
+            }
         }
-        atomicAdd(dw + ci * 16 + t0, a0);
-        atomicAdd(dw + ci * 16 + t0 + 1, a1);
+        __syncthreads();                                       // every warp has finished reading ht: reuse it for the partials
+#pragma unroll
+        for (int t = 0; t < 16; ++t) ht[(warp * 16 + t) * 32 + lane] = acc[t];
+        __syncthreads();
+        for (int o = tid; o < 16 * kDtC; o += 256) {           // o = t * 32 + ci
+            float sacc = 0.f;
+#pragma unroll
+            for (int ww = 0; ww < 8; ++ww) sacc += ht[ww * 512 + o];
+            atomicAdd(dw + (o & 31) * 16 + (o >> 5), sacc);
+        }
     }
     if (db) {
         bsum = warp_sum(bsum);
-        if ((tid & 31) == 0) red[tid >> 5] = bsum;
+        if (lane == 0) red[warp] = bsum;
         __syncthreads();
         if (tid == 0) {
             float s = 0.f;
