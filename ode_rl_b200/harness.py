@@ -76,9 +76,12 @@ class ODEConvGRUHarness(nn.Module):
 
     def forward(self, inputs, observed_tp, tp_to_predict, return_latents=True):
         b, t, c, h, w = inputs.size()
-        enc = self.conv_encoder(inputs.view(b * t, c, h, w))
+        # models/ODEConvGRU.py:63-66 encodes the frames in batch-major order and permutes the FEATURES to time-first; the encoder
+        # is per frame, so the same result comes from permuting the (64x smaller) frames instead: the recurrence then reads its
+        # [T, B, ...] input in place and its input gradient goes back without a copy (2 x 84 MB per step at B = 128)
+        enc = self.conv_encoder(inputs.transpose(0, 1).reshape(t * b, c, h, w))
         _, c_, h_, w_ = enc.size()
-        enc = enc.view(b, -1, c_, h_, w_).permute(1, 0, 2, 3, 4)             # time first
+        enc = enc.view(t, b, c_, h_, w_)                                     # time first
         mean_z0, std_z0 = self.ode_convgru_cell(enc, observed_tp)
         sol_y = self.diffeq_solver(mean_z0, tp_to_predict)                  # [T,B,C,H,W]
         T, B, C, H, W = sol_y.size()
@@ -190,8 +193,9 @@ class VidODEHarness(nn.Module):
     def latents(self, inputs, batch_dict):
         """The hot path alone: frames -> (mean_z0, sol_y [B,T,C,H',W'])."""
         b, t, c, h, w = inputs.size()
-        enc = self.conv_encoder(inputs.view(b * t, c, h, w))
-        enc = enc.view(b, t, *enc.shape[-3:]).permute(1, 0, 2, 3, 4)          # time first
+        # frames permuted to time-major before the (per-frame, batch-statistics) encoder instead of its features after it
+        enc = self.conv_encoder(inputs.transpose(0, 1).reshape(t * b, c, h, w))
+        enc = enc.view(t, b, *enc.shape[-3:])                                 # time first
         mean_z0, _ = self.encoder_z0(enc, batch_dict['observed_tp'], batch_dict.get("observed_mask"))
         sol_y = self.diffeq_solver(mean_z0, batch_dict['tp_to_predict'])      # [T,B,C,H',W']
         return mean_z0, sol_y.permute(1, 0, 2, 3, 4)
