@@ -321,10 +321,13 @@ wgrad_f16_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
                 const uint32_t row = xs + static_cast<uint32_t>(ok ? i : 0) * 128u;
                 const uint32_t sw = static_cast<uint32_t>(i) & 7u;
                 float4 xv[8];
+                // the two lanes of a pair read the same slot of the two raw planes, which are a multiple of 1 KB apart: the same
+                // banks.  Lane 1 therefore walks its eight 16-byte chunks rotated by four (xv[c] = chunk c ^ 4).
+                const uint32_t rot = static_cast<uint32_t>(xhalf) << 2;
                 if (ok) {
 #pragma unroll
                     for (int c = 0; c < 8; ++c)
-                        xv[c] = lds128f(row + static_cast<uint32_t>(xhalf) * g.xplane + ((static_cast<uint32_t>(c) ^ sw) << 4));
+                        xv[c] = lds128f(row + static_cast<uint32_t>(xhalf) * g.xplane + (((static_cast<uint32_t>(c) ^ rot) ^ sw) << 4));
                 }
                 __syncwarp();
                 if (ok) {
@@ -341,7 +344,7 @@ wgrad_f16_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
                             h[e] = *reinterpret_cast<const uint32_t*>(&hh);
                             l[e] = *reinterpret_cast<const uint32_t*>(&ll);
                         }
-                        const uint32_t off = (static_cast<uint32_t>(4 * xhalf + c8) ^ sw) << 4;
+                        const uint32_t off = (static_cast<uint32_t>(4 * xhalf + (c8 ^ (2 * xhalf))) ^ sw) << 4;   // xv[2 c8], xv[2 c8 + 1] = 8 channels (c8 ^ 2 xhalf)
                         sts128(row + off, make_uint4(h[0], h[1], h[2], h[3]));
                         sts128(row + g.xplane + off, make_uint4(l[0], l[1], l[2], l[3]));
                     }
