@@ -21,8 +21,11 @@
 // layer's mask / residual operand by TMA and is the source of the TMA stores of the layer outputs that go to global memory.
 //   warp 0   TMA producer: input tile, weight ring [w_hi ; w_lo] per tap (runs ahead across layers)
 //   warp 1   TMEM allocator + MMA issue (whole warp loops, one elected lane issues)
-//   warps 2-5 input conversion, then every layer's epilogue: TMEM -> registers -> unscale / bias / act / act' / residual ->
-//            fp32 into S (if stored) and fp16 hi / lo into the planes (next layer's operands); TMA aux loads and stores by tid 0
+//   warps 2-9 input conversion, then every layer's epilogue: TMEM -> registers -> unscale / bias / act / act' / residual ->
+//            fp32 into S (if stored) and fp16 hi / lo into the planes (next layer's operands); TMA aux loads and stores by tid 0.
+//            Two groups of four warps (a warp reaches the TMEM lanes of its quarter only), one per 32-channel half of every pixel:
+//            the epilogue is a latency chain (tcgen05.ld -> FMA -> cvt -> st.shared) and runs between two layers' MMAs, not under
+//            them, so two warps per scheduler instead of one shorten every layer
 #include <cuda.h>
 #include <cuda_fp16.h>
 
@@ -38,6 +41,8 @@ namespace odex {
 constexpr int kF16MaxL = ODEX_NET_MAX_LAYERS;
 constexpr int kF16BStage = 2 * kF16C * 128;    // [w_hi ; w_lo] of one tap: 16 KB
 constexpr int kF16SB = 3;
+constexpr int kF16EpiThreads = 256;             // 8 epilogue warps
+constexpr int kF16Threads = 64 + kF16EpiThreads;
 constexpr int kF16Smem = 1024 + 2 * kF16Plane + 2 * kF16SHalf + kF16SB * kF16BStage + 256 + kF16MaxL * 256 + 64;
 
 struct F16Maps {
@@ -62,7 +67,7 @@ struct F16Args {
 };
 
 template <bool kTanh>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(kF16Threads, 1)
 convnet_f16_kernel(const __grid_constant__ F16Maps tm, const F16Args a) {
     constexpr int N = kF16C;
     constexpr int taps = 9;
@@ -91,7 +96,7 @@ convnet_f16_kernel(const __grid_constant__ F16Maps tm, const F16Args a) {
         mbar_init(bar_in, 1);
         for (int i = 0; i < kF16SB; ++i) { mbar_init(bar_b_full + 8 * i, 1); mbar_init(bar_b_empty + 8 * i, 1); }
         mbar_init(bar_acc, 1);
-        mbar_init(bar_next, 128);
+        mbar_init(bar_next, kF16EpiThreads);
         mbar_init(bar_aux, 1);
         fence_barrier_init();
     }
@@ -173,19 +178,20 @@ convnet_f16_kernel(const __grid_constant__ F16Maps tm, const F16Args a) {
     } else {
         // ===================== input conversion, then every layer's epilogue =====================
         const int tid = threadIdx.x - 64;
-        for (int i = tid; i < L * (N / 4); i += 128) {
+        for (int i = tid; i < L * (N / 4); i += kF16EpiThreads) {
             const int l = i / (N / 4), j = i % (N / 4);
             float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
             if (a.bias[l]) bv = __ldg(reinterpret_cast<const float4*>(a.bias[l]) + j);
             asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(bias_s + 16u * i), "f"(bv.x), "f"(bv.y), "f"(bv.z), "f"(bv.w) : "memory");
         }
         // zero both planes (the 1-pixel border is the convolution's padding and is never written again)
-        for (uint32_t i = tid; i < 2u * kF16Plane / 16u; i += 128) sts128(base + i * 16u, make_uint4(0u, 0u, 0u, 0u));
+        for (uint32_t i = tid; i < 2u * kF16Plane / 16u; i += kF16EpiThreads) sts128(base + i * 16u, make_uint4(0u, 0u, 0u, 0u));
         float alpha = a.alpha;
         if (a.alpha_dev) alpha *= static_cast<float>(*a.alpha_dev);
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 1, 256;" ::: "memory");
 
         const int q = warp & 3;
+        const int hh = tid >> 7;                      // this warp group's 32-channel half
         const int m = q * 32 + lane;                  // TMEM lane = pixel of the M-tile: (y, x) = (m / 8, mt * 8 + m % 8)
         const uint32_t lane_addr = static_cast<uint32_t>(q * 32) << 16;
         const float4* bias4 = reinterpret_cast<const float4*>(smem_raw + (bias_s - smem_u32(smem_raw)));
@@ -195,20 +201,20 @@ convnet_f16_kernel(const __grid_constant__ F16Maps tm, const F16Args a) {
         float cur_inv;                                // 1 / (scale of the operands now in the planes)
         {
             float mx = 0.f;
-            float4 xv[2][16];
+            float4 xv[2][8];
 #pragma unroll
             for (int mt = 0; mt < 2; ++mt) {
                 const uint32_t p = static_cast<uint32_t>((m >> 3) * 16 + mt * 8 + (m & 7));
 #pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    xv[mt][j] = lds128f(s_base + static_cast<uint32_t>(j >> 3) * kF16SHalf + p * 128u + ((static_cast<uint32_t>(j & 7) ^ (p & 7u)) << 4));
+                for (int j = 0; j < 8; ++j) {
+                    xv[mt][j] = lds128f(s_base + static_cast<uint32_t>(hh) * kF16SHalf + p * 128u + ((static_cast<uint32_t>(j) ^ (p & 7u)) << 4));
                     mx = fmaxf(mx, fmaxf(fmaxf(fabsf(xv[mt][j].x), fabsf(xv[mt][j].y)), fmaxf(fabsf(xv[mt][j].z), fabsf(xv[mt][j].w))));
                 }
             }
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
             if (lane == 0) asm volatile("atom.shared.max.u32 _, [%0], %1;" ::"r"(amax_s), "r"(__float_as_uint(mx)) : "memory");   // NaN compares high: it propagates
-            asm volatile("bar.sync 1, 128;" ::: "memory");
+            asm volatile("bar.sync 1, 256;" ::: "memory");
             uint32_t mb;
             asm volatile("ld.shared.u32 %0, [%1];" : "=r"(mb) : "r"(amax_s));
             const float s0 = f16_scale_for(__uint_as_float(mb), &cur_inv);
@@ -217,12 +223,12 @@ convnet_f16_kernel(const __grid_constant__ F16Maps tm, const F16Args a) {
                 const uint32_t srow = f16_slot(m >> 3, mt * 8 + (m & 7));
                 const uint32_t row = base + srow * 128u;
 #pragma unroll
-                for (int c8 = 0; c8 < 8; ++c8) {
+                for (int c8 = 0; c8 < 4; ++c8) {
                     const float4 u = xv[mt][2 * c8], w = xv[mt][2 * c8 + 1];
                     const float o[8] = {u.x * s0, u.y * s0, u.z * s0, u.w * s0, w.x * s0, w.y * s0, w.z * s0, w.w * s0};
                     uint4 hi, lo;
                     f16_split8(o, &hi, &lo);
-                    const uint32_t off = (static_cast<uint32_t>(c8) ^ (srow & 7u)) << 4;
+                    const uint32_t off = (static_cast<uint32_t>(4 * hh + c8) ^ (srow & 7u)) << 4;
                     sts128(row + off, hi);
                     sts128(row + kF16Plane + off, lo);
                 }
@@ -230,7 +236,7 @@ convnet_f16_kernel(const __grid_constant__ F16Maps tm, const F16Args a) {
         }
         fence_proxy_async_smem();
         mbar_arrive(bar_next);
-        asm volatile("bar.sync 1, 128;" ::: "memory");          // S (the input) has been consumed by every thread
+        asm volatile("bar.sync 1, 256;" ::: "memory");          // S (the input) has been consumed by every thread
 
         uint32_t aux_phase = 0;
         bool stores_pending = false;
@@ -266,16 +272,16 @@ convnet_f16_kernel(const __grid_constant__ F16Maps tm, const F16Args a) {
             mbar_wait(bar_acc, static_cast<uint32_t>(l) & 1u);
             tc_fence_after_sync();
             if (a.dbg && blockIdx.x == 0 && tid == 0) a.dbg[1 + 2 * l] = clock64() - t_start;
-            if (touch_s) asm volatile("bar.sync 1, 128;" ::: "memory");      // tid 0's wait_read / aux issue above is done
+            if (touch_s) asm volatile("bar.sync 1, 256;" ::: "memory");      // tid 0's wait_read / aux issue above is done
             if (kind) { mbar_wait(bar_aux, aux_phase); aux_phase ^= 1u; }
             const int act = a.act[l];
             const float4* bl = bias4 + l * (N / 4);
             const bool st = a.store[l] != 0;
             float amax = 0.f;
 #define ODEX_F16_EPI(A, K) \
-    amax = last ? f16_epilogue<A, K, true, true>(tmem_base, lane_addr, base, s_base, m, bl, alpha, unscale, next_scale) \
-                : (st ? f16_epilogue<A, K, true, false>(tmem_base, lane_addr, base, s_base, m, bl, alpha, unscale, next_scale) \
-                      : f16_epilogue<A, K, false, false>(tmem_base, lane_addr, base, s_base, m, bl, alpha, unscale, next_scale))
+    amax = last ? f16_epilogue<A, K, true, true>(tmem_base, lane_addr, base, s_base, m, bl, alpha, unscale, next_scale, hh, hh + 1) \
+                : (st ? f16_epilogue<A, K, true, false>(tmem_base, lane_addr, base, s_base, m, bl, alpha, unscale, next_scale, hh, hh + 1) \
+                      : f16_epilogue<A, K, false, false>(tmem_base, lane_addr, base, s_base, m, bl, alpha, unscale, next_scale, hh, hh + 1))
             switch (act * 4 + kind) {
                 case ODEX_ACT_NONE * 4 + 0: ODEX_F16_EPI(ODEX_ACT_NONE, 0); break;
                 case ODEX_ACT_NONE * 4 + 1: ODEX_F16_EPI(ODEX_ACT_NONE, 1); break;
@@ -298,7 +304,7 @@ convnet_f16_kernel(const __grid_constant__ F16Maps tm, const F16Args a) {
             fence_proxy_async_smem();
             if (!last) mbar_arrive(bar_next);
             if (a.dbg && blockIdx.x == 0 && tid == 0) a.dbg[2 + 2 * l] = clock64() - t_start;
-            asm volatile("bar.sync 1, 128;" ::: "memory");       // every thread has left S (aux read / result written) and amax_s[l+1] is final
+            asm volatile("bar.sync 1, 256;" ::: "memory");       // every thread has left S (aux read / result written) and amax_s[l+1] is final
             if (a.store[l]) {
                 if (tid == 0) {
                     tma_store_4d(&tm.out[l], s_base, 0, 0, 0, img);
@@ -424,7 +430,7 @@ int launch_convnet_f16(const odex_convnet_desc* d, cudaStream_t s) {
         cudaMemsetAsync(dbuf, 0, 16 * sizeof(long long), s);
         a.dbg = dbuf;
     }
-    launch_pdl(kern, d->B, 192, kF16Smem, s, tm, a);
+    launch_pdl(kern, d->B, kF16Threads, kF16Smem, s, tm, a);
     if (debug) {
         long long h[16];
         cudaStreamSynchronize(s);

@@ -67,11 +67,12 @@ constexpr int kF16SHalf = 256 * 128;           // 32 channels x 256 pixels, fp32
 
 __device__ __forceinline__ uint32_t f16_slot(int y, int x) { return static_cast<uint32_t>((y + 1) * kF16P + x + 1); }
 
-// One layer's epilogue for the two pixels (M-tiles) of this thread.  ACT / KIND as in convnet_tc.cu; STORE: fp32 result into S;
-// LAST: no operands for a next layer.  Returns max |v| of this thread's outputs.
+// One layer's epilogue for the two pixels (M-tiles) of this thread and the 32-channel halves [h0, h1) (both by default; the fused
+// chain runs two warp groups, one per half).  ACT / KIND as in convnet_tc.cu; STORE: fp32 result into S; LAST: no operands for a
+// next layer.  Returns max |v| of this thread's outputs.
 template <int ACT, int KIND, bool STORE, bool LAST>
 __device__ __forceinline__ float f16_epilogue(uint32_t tmem_base, uint32_t lane_addr, uint32_t base, uint32_t s_base, int m,
-                                              const float4* bl, float alpha, float unscale, float next_scale) {
+                                              const float4* bl, float alpha, float unscale, float next_scale, int h0 = 0, int h1 = 2) {
     constexpr int N = kF16C;
     float amax = 0.f;
 #pragma unroll 1
@@ -81,8 +82,8 @@ __device__ __forceinline__ float f16_epilogue(uint32_t tmem_base, uint32_t lane_
         const uint32_t p = static_cast<uint32_t>(y * 16 + x);
         const uint32_t plane_row = base + srow * 128u;
         const uint32_t psw = srow & 7u, ssw = p & 7u;
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
+#pragma unroll 1
+        for (int h = h0; h < h1; ++h) {
             uint32_t vm[32], vc[32];
             tmem_ld32(tmem_base + lane_addr + mt * 2 * N + h * 32, vm);
             tmem_ld32(tmem_base + lane_addr + mt * 2 * N + N + h * 32, vc);
