@@ -51,6 +51,9 @@ struct C16Maps {
     CUtensorMap graw, omain, ocand; // GRU modes: the pre-norm convolution, z | r*h | h', the candidate
 };
 
+constexpr int kC16EpiThreads = 256;      // 8 epilogue warps: two groups of four, one per 32-channel half (= one GroupNorm group)
+constexpr int kC16Threads = 64 + kC16EpiThreads;
+
 struct C16Args {
     int nsrc, N, mode;
     const float* x1; int ld1;       // source 1 again as a plain pointer (its max is read directly)
@@ -77,9 +80,9 @@ __device__ __forceinline__ float sigmoid_fast(float x) {
 }
 __device__ __forceinline__ float tanh_fast(float x) { return fmaf(2.f, sigmoid_fast(2.f * x), -1.f); }
 
-// fp32 tile in S (TMA box layout) -> hi / lo planes, this thread's two pixels
+// fp32 tile in S (TMA box layout) -> hi / lo planes, this thread's two pixels, channels [32 hh, +32)
 template <int R>
-__device__ __forceinline__ void c16_convert(uint32_t s_base, uint32_t base, int m, float scale) {
+__device__ __forceinline__ void c16_convert(uint32_t s_base, uint32_t base, int m, int hh, float scale) {
     using Cfg = C16Cfg<R>;
 #pragma unroll 1
     for (int mt = 0; mt < 2; ++mt) {
@@ -87,17 +90,17 @@ __device__ __forceinline__ void c16_convert(uint32_t s_base, uint32_t base, int 
         const uint32_t p = static_cast<uint32_t>(y * 16 + x);
         const uint32_t srow = static_cast<uint32_t>((y + Cfg::pad) * Cfg::P + x + Cfg::pad);
         const uint32_t row = base + srow * 128u;
-        float4 xv[16];
+        float4 xv[8];
 #pragma unroll
-        for (int j = 0; j < 16; ++j)
-            xv[j] = lds128f(s_base + static_cast<uint32_t>(j >> 3) * kF16SHalf + p * 128u + ((static_cast<uint32_t>(j & 7) ^ (p & 7u)) << 4));
+        for (int j = 0; j < 8; ++j)
+            xv[j] = lds128f(s_base + static_cast<uint32_t>(hh) * kF16SHalf + p * 128u + ((static_cast<uint32_t>(j) ^ (p & 7u)) << 4));
 #pragma unroll
-        for (int c8 = 0; c8 < 8; ++c8) {
+        for (int c8 = 0; c8 < 4; ++c8) {
             const float4 u = xv[2 * c8], w = xv[2 * c8 + 1];
             const float o[8] = {u.x * scale, u.y * scale, u.z * scale, u.w * scale, w.x * scale, w.y * scale, w.z * scale, w.w * scale};
             uint4 hi, lo;
             f16_split8(o, &hi, &lo);
-            const uint32_t off = (static_cast<uint32_t>(c8) ^ (srow & 7u)) << 4;
+            const uint32_t off = (static_cast<uint32_t>(4 * hh + c8) ^ (srow & 7u)) << 4;
             sts128(row + off, hi);
             sts128(row + Cfg::plane + off, lo);
         }
@@ -121,7 +124,7 @@ __device__ __forceinline__ void c16_load32(uint32_t tmem_base, uint32_t lane_add
 }
 
 template <int R>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(kC16Threads, 1)
 conv16_f16_kernel(const __grid_constant__ C16Maps tm, const C16Args a) {
     using Cfg = C16Cfg<R>;
     constexpr int taps = Cfg::taps;
@@ -152,7 +155,7 @@ conv16_f16_kernel(const __grid_constant__ C16Maps tm, const C16Args a) {
     if (threadIdx.x == 0) {
         mbar_init(bar_in, 1); mbar_init(bar_in + 8, 1);
         for (int i = 0; i < kC16SB; ++i) { mbar_init(bar_b_full + 8 * i, 1); mbar_init(bar_b_empty + 8 * i, 1); }
-        mbar_init(bar_next, 128);
+        mbar_init(bar_next, kC16EpiThreads);
         mbar_init(bar_mma, 1);
         mbar_init(bar_aux, 1);
         asm volatile("st.shared.u32 [%0], %1;" ::"r"(amax_s), "r"(0u) : "memory");
@@ -247,11 +250,12 @@ conv16_f16_kernel(const __grid_constant__ C16Maps tm, const C16Args a) {
             const float4 v = __ldg(reinterpret_cast<const float4*>(src + n_off) + j);
             asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(bias_s + 256u * (tid < 32 ? 1u : 2u) + 16u * j), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
         }
-        for (uint32_t i = tid; i < 2u * Cfg::plane / 16u; i += 128) sts128(base + i * 16u, make_uint4(0u, 0u, 0u, 0u));
+        for (uint32_t i = tid; i < 2u * Cfg::plane / 16u; i += kC16EpiThreads) sts128(base + i * 16u, make_uint4(0u, 0u, 0u, 0u));
         float alpha = a.alpha;
         if (a.alpha_dev) alpha *= static_cast<float>(*a.alpha_dev);
 
         const int q = warp & 3;
+        const int hh_own = tid >> 7;                  // this warp group's 32-channel half of the 64 outputs (= one GroupNorm group)
         const int m = q * 32 + lane;                  // TMEM lane = pixel of the M-tile: (y, x) = (m / 8, mt * 8 + m % 8)
         const uint32_t lane_addr = static_cast<uint32_t>(q * 32) << 16;
         const uint32_t p0 = static_cast<uint32_t>((m >> 3) * 16 + (m & 7));          // pixel of M-tile 0; M-tile 1: + 8
@@ -262,11 +266,11 @@ conv16_f16_kernel(const __grid_constant__ C16Maps tm, const C16Args a) {
             // a max does not care which thread sees which element: fully coalesced 16-byte reads (pixel = i / 16, chunk = i % 16)
             const float* xb = a.x1 + static_cast<long>(img) * 256 * a.ld1;
 #pragma unroll 1
-            for (int i0_ = 0; i0_ < 4096; i0_ += 8 * 128) {
+            for (int i0_ = 0; i0_ < 4096; i0_ += 8 * kC16EpiThreads) {
                 float4 t[8];
 #pragma unroll
                 for (int k = 0; k < 8; ++k) {
-                    const int i = i0_ + k * 128 + tid;
+                    const int i = i0_ + k * kC16EpiThreads + tid;
                     t[k] = __ldg(reinterpret_cast<const float4*>(xb + static_cast<long>(i >> 4) * a.ld1) + (i & 15));
                 }
 #pragma unroll
@@ -278,14 +282,14 @@ conv16_f16_kernel(const __grid_constant__ C16Maps tm, const C16Args a) {
         for (int mt = 0; mt < 2; ++mt) {
             const uint32_t p = p0 + 8u * mt;
 #pragma unroll
-            for (int j = 0; j < 16; ++j)
-                mx = absmax4(mx, lds128f(s_base + static_cast<uint32_t>(j >> 3) * kF16SHalf + p * 128u + ((static_cast<uint32_t>(j & 7) ^ (p & 7u)) << 4)));
+            for (int j = 0; j < 8; ++j)
+                mx = absmax4(mx, lds128f(s_base + static_cast<uint32_t>(hh_own) * kF16SHalf + p * 128u + ((static_cast<uint32_t>(j) ^ (p & 7u)) << 4)));
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-        asm volatile("bar.sync 1, 128;" ::: "memory");          // planes zeroed, bias in place, amax_s initialised
+        asm volatile("bar.sync 1, 256;" ::: "memory");          // planes zeroed, bias in place, amax_s initialised
         if (lane == 0) asm volatile("atom.shared.max.u32 _, [%0], %1;" ::"r"(amax_s), "r"(__float_as_uint(mx)) : "memory");
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 1, 256;" ::: "memory");
         uint32_t mb;
         asm volatile("ld.shared.u32 %0, [%1];" : "=r"(mb) : "r"(amax_s));
         float a_inv;
@@ -293,10 +297,10 @@ conv16_f16_kernel(const __grid_constant__ C16Maps tm, const C16Args a) {
         if (tid == 0 && a.amax_out) a.amax_out[img] = __uint_as_float(mb);      // (every output-channel block of the image writes the same value)
         C16_MARK(1);
 
-        c16_convert<R>(s_base, base, m, a_scale);
+        c16_convert<R>(s_base, base, m, hh_own, a_scale);
         fence_proxy_async_smem();
         mbar_arrive(bar_next);
-        asm volatile("bar.sync 1, 128;" ::: "memory");          // S (source 0) has been consumed by every thread
+        asm volatile("bar.sync 1, 256;" ::: "memory");          // S (source 0) has been consumed by every thread
         C16_MARK(2);
         if (nsrc == 2) {
             if (tid == 0) {
@@ -308,10 +312,10 @@ conv16_f16_kernel(const __grid_constant__ C16Maps tm, const C16Args a) {
             C16_MARK(3);
             mbar_wait(bar_mma, 0u);                              // source 0's MMAs have read the planes
             C16_MARK(4);
-            c16_convert<R>(s_base, base, m, a_scale);
+            c16_convert<R>(s_base, base, m, hh_own, a_scale);
             fence_proxy_async_smem();
             mbar_arrive(bar_next);
-            asm volatile("bar.sync 1, 128;" ::: "memory");      // S (source 1) consumed
+            asm volatile("bar.sync 1, 256;" ::: "memory");      // S (source 1) consumed
             C16_MARK(5);
         }
         const int kind = a.mode == ODEX_C16_PLAIN ? a.aux_kind : 0;
@@ -330,7 +334,7 @@ conv16_f16_kernel(const __grid_constant__ C16Maps tm, const C16Args a) {
         if (a.mode == ODEX_C16_PLAIN) {
             if (kind) mbar_wait(bar_aux, 0u);
             const float4* bl = reinterpret_cast<const float4*>(bias_sm);
-#define ODEX_C16_EPI(A, K) f16_epilogue<A, K, true, true>(tmem_base, lane_addr, base, s_base, m, bl, alpha, unscale, 1.f)
+#define ODEX_C16_EPI(A, K) f16_epilogue<A, K, true, true>(tmem_base, lane_addr, base, s_base, m, bl, alpha, unscale, 1.f, hh_own, hh_own + 1)
             switch (a.act * 4 + kind) {
                 case ODEX_ACT_NONE * 4 + 0: ODEX_C16_EPI(ODEX_ACT_NONE, 0); break;
                 case ODEX_ACT_NONE * 4 + 1: ODEX_C16_EPI(ODEX_ACT_NONE, 1); break;
@@ -345,7 +349,7 @@ conv16_f16_kernel(const __grid_constant__ C16Maps tm, const C16Args a) {
 #undef ODEX_C16_EPI
             tc_fence_before_sync();
             fence_proxy_async_smem();
-            asm volatile("bar.sync 1, 128;" ::: "memory");
+            asm volatile("bar.sync 1, 256;" ::: "memory");
             if (tid == 0) {
                 tma_store_4d(&tm.out, s_base, n_off, 0, 0, img);
                 tma_store_4d(&tm.out, s_base + kF16SHalf, n_off + 32, 0, 0, img);
@@ -354,11 +358,11 @@ conv16_f16_kernel(const __grid_constant__ C16Maps tm, const C16Args a) {
             }
         } else {
             // ---- GroupNorm statistics of the two 32-channel groups of this block: chunk mean / M2, merged pairwise (Chan)
-            float gmean[2], gM2[2];
+            float gmean_o = 0.f, gM2_o = 0.f;                // this group's (mean, M2)
 #pragma unroll 1
             for (int mt = 0; mt < 2; ++mt) {
-#pragma unroll
-                for (int hh = 0; hh < 2; ++hh) {
+#pragma unroll 1
+                for (int hh = hh_own; hh <= hh_own; ++hh) {
                     float v[32];
                     c16_load32(tmem_base, lane_addr, mt, hh, bias_sm, unscale, v);
                     if (a.g_raw) {              // the pre-norm convolution goes out through S (TMA store below)
@@ -376,37 +380,35 @@ conv16_f16_kernel(const __grid_constant__ C16Maps tm, const C16Args a) {
                     float cq = 0.f;
 #pragma unroll
                     for (int j = 0; j < 32; ++j) { const float d = v[j] - cm; cq = fmaf(d, d, cq); }
-                    if (mt == 0) { gmean[hh] = cm; gM2[hh] = cq; }
-                    else { const float d = cm - gmean[hh]; gmean[hh] += 0.5f * d; gM2[hh] += cq + d * d * 16.f; }
+                    if (mt == 0) { gmean_o = cm; gM2_o = cq; }
+                    else { const float d = cm - gmean_o; gmean_o += 0.5f * d; gM2_o += cq + d * d * 16.f; }
                 }
             }
             float n_half = 32.f;                        // n / 2 of each side of the next merge (n = 64 per thread)
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) {
-#pragma unroll
-                for (int hh = 0; hh < 2; ++hh) {
-                    const float mo = __shfl_xor_sync(0xffffffffu, gmean[hh], o), qo = __shfl_xor_sync(0xffffffffu, gM2[hh], o);
-                    const float d = mo - gmean[hh];
-                    gM2[hh] = (gM2[hh] + qo) + d * d * n_half;
-                    gmean[hh] = 0.5f * (gmean[hh] + mo);
+#pragma unroll 1
+                for (int hh = hh_own; hh <= hh_own; ++hh) {
+                    const float mo = __shfl_xor_sync(0xffffffffu, gmean_o, o), qo = __shfl_xor_sync(0xffffffffu, gM2_o, o);
+                    const float d = mo - gmean_o;
+                    gM2_o = (gM2_o + qo) + d * d * n_half;
+                    gmean_o = 0.5f * (gmean_o + mo);
                 }
                 n_half *= 2.f;
             }
-            if (lane == 0) {
-#pragma unroll
-                for (int hh = 0; hh < 2; ++hh)
-                    asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(gn_s + static_cast<uint32_t>(q * 2 + hh) * 8u), "f"(gmean[hh]), "f"(gM2[hh]) : "memory");
-            }
+            if (lane == 0)
+                asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(gn_s + static_cast<uint32_t>(q * 2 + hh_own) * 8u),
+                             "f"(gmean_o), "f"(gM2_o) : "memory");
             if (a.g_raw) fence_proxy_async_smem();
-            asm volatile("bar.sync 1, 128;" ::: "memory");
+            asm volatile("bar.sync 1, 256;" ::: "memory");
             if (a.g_raw && tid == 0) {
                 tma_store_4d(&tm.graw, s_base, n_off, 0, 0, img);
                 tma_store_4d(&tm.graw, s_base + kF16SHalf, n_off + 32, 0, 0, img);
                 tma_store_commit();
             }
-            float mean[2], rstd[2];
-#pragma unroll
-            for (int hh = 0; hh < 2; ++hh) {
+            float mean_o = 0.f, rstd_o = 0.f;
+#pragma unroll 1
+            for (int hh = hh_own; hh <= hh_own; ++hh) {
                 float mu, q2;
                 asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(mu) , "=f"(q2) : "r"(gn_s + static_cast<uint32_t>(hh) * 8u));
                 float n = 2048.f;
@@ -419,16 +421,13 @@ conv16_f16_kernel(const __grid_constant__ C16Maps tm, const C16Args a) {
                     mu += d * (2048.f / nn);
                     n = nn;
                 }
-                mean[hh] = mu;
-                rstd[hh] = 1.f / sqrtf(q2 * (1.f / 8192.f) + a.eps);
+                mean_o = mu;
+                rstd_o = 1.f / sqrtf(q2 * (1.f / 8192.f) + a.eps);
             }
             const int G = a.N >> 5;
-            if (tid == 0) {
-#pragma unroll
-                for (int hh = 0; hh < 2; ++hh) {
-                    float* st = a.stats + (static_cast<long>(img) * G + (n_off >> 5) + hh) * 2;
-                    st[0] = mean[hh]; st[1] = rstd[hh];
-                }
+            if ((tid & 127) == 0) {
+                float* st = a.stats + (static_cast<long>(img) * G + (n_off >> 5) + hh_own) * 2;
+                st[0] = mean_o; st[1] = rstd_o;
             }
             // ---- apply: normalise, gate, blend.  Results are staged in shared memory in the TMA box layout and stored by TMA: the
             // main result (z | r*h | h') in the operand planes, which every MMA has finished reading; the candidate in S once
@@ -440,14 +439,14 @@ conv16_f16_kernel(const __grid_constant__ C16Maps tm, const C16Args a) {
             const bool want_cand = a.mode == ODEX_C16_GRU_OUT && a.cand != nullptr;
             if (want_cand) {
                 if (tid == 0) tma_store_wait_read();
-                asm volatile("bar.sync 1, 128;" ::: "memory");
+                asm volatile("bar.sync 1, 256;" ::: "memory");
             }
 #pragma unroll 1
             for (int mt = 0; mt < 2; ++mt) {
                 const uint32_t p = p0 + 8u * mt;
                 const long gp = static_cast<long>(img) * 256 + p;
 #pragma unroll 1
-                for (int hh = 0; hh < 2; ++hh) {
+                for (int hh = hh_own; hh <= hh_own; ++hh) {
                     const int cb = n_off + hh * 32;                   // first channel of this group among the N outputs
                     float4 hv[8], zv[8];
                     if (a.mode == ODEX_C16_GRU_OUT) {
@@ -462,7 +461,7 @@ conv16_f16_kernel(const __grid_constant__ C16Maps tm, const C16Args a) {
                     }
                     float v[32];
                     c16_load32(tmem_base, lane_addr, mt, hh, bias_sm, unscale, v);
-                    const float mu = hh ? mean[1] : mean[0], rs = hh ? rstd[1] : rstd[0];
+                    const float mu = mean_o, rs = rstd_o;
 #pragma unroll
                     for (int j = 0; j < 32; ++j) v[j] = fmaf((v[j] - mu) * rs, gam[hh * 32 + j], bet[hh * 32 + j]);
                     const uint32_t t_row = base + static_cast<uint32_t>(hh) * kF16SHalf + p * 128u;
@@ -499,7 +498,7 @@ conv16_f16_kernel(const __grid_constant__ C16Maps tm, const C16Args a) {
             }
             tc_fence_before_sync();
             fence_proxy_async_smem();
-            asm volatile("bar.sync 1, 128;" ::: "memory");
+            asm volatile("bar.sync 1, 256;" ::: "memory");
             if (tid == 0) {
                 const bool r_block = a.mode == ODEX_C16_GRU_GATES && !z_block;
                 const int c_main = r_block ? n_off - C : n_off;
@@ -646,7 +645,7 @@ static int c16_launch(const odex_conv16_desc* d, cudaStream_t s) {
     static cudaError_t attr_err = cudaSuccess;
     std::call_once(once, [&] { attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::smem); });
     if (attr_err != cudaSuccess) return fail(-static_cast<int>(attr_err), "conv16: cudaFuncSetAttribute: %s", cudaGetErrorString(attr_err));
-    launch_pdl(kern, d->B * (d->N / 64), 192, Cfg::smem, s, tm, a);
+    launch_pdl(kern, d->B * (d->N / 64), kC16Threads, Cfg::smem, s, tm, a);
     if (debug) {
         long long h[16];
         cudaStreamSynchronize(s);
