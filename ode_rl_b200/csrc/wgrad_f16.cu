@@ -49,6 +49,7 @@ struct Wgrad16Geom {
     // operand maxima: one pair for the whole tensor (amax_stride 0: absmax2_kernel's, or the caller's) or one pair PER IMAGE
     // (amax_stride 1: amax_x[b] >= max |X[b]|, amax_dy[b] >= max |dy[b]|, as the producing kernels measured them)
     const float* amax_x; const float* amax_dy; int amax_stride;
+    long long* dbg;     // diagnostic: per-role cycle counters of CTA 0 (ODEX_WGRAD_DEBUG=1), else nullptr
 };
 
 // max |.| of up to three strided [P, C] fp32 matrices: out[0] <- max over a and b (the X sources), out[1] <- c (dy).
@@ -231,10 +232,13 @@ wgrad_f16_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
             const int cx = second ? cabs - g.c0 : cabs;
             constexpr uint32_t tx_bytes = 2u * hrows * 128u + 2u * kW16DyPlane;
             int it = 0;
+            long long w_empty = 0, t_begin = clock64();
             for (int t = ps; t < g.ntiles; t += g.PS, ++it) {
                 const int st = it % S;
                 const uint32_t use = static_cast<uint32_t>(it / S);
+                const long long c0_ = clock64();
                 mbar_wait(bar_stage_empty + 8 * st, (use & 1u) ^ 1u);
+                w_empty += clock64() - c0_;
                 int img, y0, x0;
                 w16_tile_coords(g, t, img, y0, x0);
                 const uint32_t xs = base + st * stage_bytes;
@@ -246,6 +250,7 @@ wgrad_f16_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
                 tma_load_4d(ds, &tmDY, bar, nb * 64, x0, y0, img);
                 tma_load_4d(ds + kW16DyPlane, &tmDY, bar, nb * 64 + 32, x0, y0, img);
             }
+            if (g.dbg && blockIdx.x == 0) { g.dbg[0] = w_empty; g.dbg[1] = clock64() - t_begin; g.dbg[2] = it; }
         }
     } else if (warp == 1) {
         // ===================== MMA issue (whole warp loops, one elected lane issues) =====================
@@ -254,10 +259,13 @@ wgrad_f16_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
         const uint32_t b_lbo = ((static_cast<uint32_t>(g.xplane) >> 4) & 0x3FFFu) << 16;      // (one 64-channel atom along N: unused)
         const uint32_t lo_delta = static_cast<uint32_t>(g.xplane) >> 4;                       // X hi plane -> X lo plane
         int it = 0;
+        long long w_split = 0, t_begin = clock64();
         for (int t = ps; t < g.ntiles; t += g.PS, ++it) {
             const int st = it % S;
             const uint32_t use = static_cast<uint32_t>(it / S);
+            const long long c0_ = clock64();
             mbar_wait(bar_split_full + 8 * st, use & 1u);
+            w_split += clock64() - c0_;
             tc_fence_after_sync();
             const uint32_t xs = base + st * stage_bytes;
             const uint32_t a_tmem = tmem_base + a_col0 + static_cast<uint32_t>(st) * 32u;
@@ -282,6 +290,7 @@ wgrad_f16_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
         }
         if (elect_one()) umma_commit(bar_acc);
         __syncwarp();
+        if (g.dbg && blockIdx.x == 0 && lane == 0) { g.dbg[3] = w_split; g.dbg[4] = clock64() - t_begin; }
     } else {
         // ===================== operand preparation (8 warps), then epilogue (the first 4 of them) =====================
         // thread <-> TMEM lane L = 32 * (warp % 4) + lane: dy channel n = L % 64, part = L / 64 (0: hi rows, 1: lo rows).  The
@@ -303,13 +312,17 @@ wgrad_f16_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
         const uint32_t dy_chunk = static_cast<uint32_t>((n & 31) >> 2);
         const int xhalf = tid & 1;                        // X: a lane pair owns a pixel slot, one 32-channel raw plane each
         int it = 0;
+        long long w_raw = 0, t_x = 0, t_dy = 0, t_begin = clock64();
         for (int t = ps; t < g.ntiles; t += g.PS, ++it) {
             if ((it & 1) != grp) continue;
             float sx, sdy;
             w16_scales(g, t / tiles_per_img, pmax_e, &sx, &sdy);
             const int st = it % S;
             const uint32_t use = static_cast<uint32_t>(it / S);
+            const long long c0_ = clock64();
             mbar_wait(bar_raw_full + 8 * st, use & 1u);
+            const long long c1_ = clock64();
+            w_raw += c1_ - c0_;
             const uint32_t xs = base + st * stage_bytes;
             const uint32_t ds = xs + 2u * g.xplane + dy_off;
             // ---- X: slot i holds 32 + 32 fp32 channels in the two raw planes; it becomes 64 fp16 hi (plane 0) + 64 fp16 lo
@@ -351,6 +364,8 @@ wgrad_f16_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
                 }
             }
             // ---- dy: this lane's channel at 32 of the tile's pixels -> A operand row in TMEM (K-major, two pixels per column)
+            const long long c2_ = clock64();
+            t_x += c2_ - c1_;
             tc_fence_after_sync();
             uint32_t a[32];
 #pragma unroll
@@ -379,7 +394,9 @@ wgrad_f16_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
             tc_fence_before_sync();
             fence_proxy_async_smem();
             mbar_arrive(bar_split_full + 8 * st);
+            t_dy += clock64() - c2_;
         }
+        if (g.dbg && blockIdx.x == 0 && tid == 0 && grp == 0) { g.dbg[5] = w_raw; g.dbg[6] = t_x; g.dbg[7] = t_dy; g.dbg[8] = clock64() - t_begin; }
         if (do_db) atomicAdd(g.db + nb * 64 + n, dbsum);
         if (grp == 0) {
         mbar_wait(bar_acc, 0u);             // every MMA has completed: the stage buffers are free as well
@@ -526,7 +543,23 @@ int launch_wgrad_f16(const float* x0, int ld0, int c0, const float* x1, int ld1,
         if (attr_err == cudaSuccess) attr_err = cudaFuncSetAttribute(wgrad_f16_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
     });
     if (attr_err != cudaSuccess) return fail(-static_cast<int>(attr_err), "wgrad(f16): cudaFuncSetAttribute: %s", cudaGetErrorString(attr_err));
+    g.dbg = nullptr;
+    static const bool debug = getenv("ODEX_WGRAD_DEBUG") != nullptr;
+    if (debug) {
+        static long long* dbuf = nullptr;
+        if (!dbuf) cudaMalloc(&dbuf, 16 * sizeof(long long));
+        cudaMemsetAsync(dbuf, 0, 16 * sizeof(long long), s);
+        g.dbg = dbuf;
+    }
     launch_pdl(kern, units * g.PS, 320, smem, s, tmX0, tmX1, tmDY, g);
+    if (debug) {
+        long long h[16];
+        cudaStreamSynchronize(s);
+        cudaMemcpy(h, g.dbg, sizeof(h), cudaMemcpyDeviceToHost);
+        fprintf(stderr, "[wgrad_f16 R=%d C=%d N=%d B=%d grid=%d tiles/cta=%lld] producer: wait_empty=%lld total=%lld | mma: wait_split=%lld total=%lld | "
+                "transform group 0 (every other tile): wait_raw=%lld x=%lld dy=%lld total=%lld (cycles)\n", R, g.Ctot, N, B, units * g.PS, h[2], h[0],
+                h[1], h[3], h[4], h[5], h[6], h[7], h[8]);
+    }
     return launched("wgrad_f16_kernel");
 }
 
