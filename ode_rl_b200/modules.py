@@ -913,18 +913,26 @@ class _EncoderFn(torch.autograd.Function):
         mx_arena = None
         if save and T > 0 and B > 0 and f_op.maxima_ok(h):
             mx_arena = torch.empty((Lf, 2, T, B), dtype=torch.float32, device=x.device)
+        # the ConvGRU's weight-gradient operands over the T steps in arenas indexed by FRAME (like x): h~, r*h, and their maxima
+        gru_ar = None
+        if save and T > 1 and B > 0 and g_op._fused16(be, x[0], h):
+            gru_ar = {"ht": torch.empty((T, B, H, W, C), dtype=torch.float32, device=x.device),
+                      "rh": torch.empty((T, B, H, W, C), dtype=torch.float32, device=x.device),
+                      "mx": torch.empty((2, 2, T, B), dtype=torch.float32, device=x.device)}
         for n, i in enumerate(order):
-            ht = torch.empty_like(h)
+            ht = gru_ar["ht"][i] if gru_ar is not None else torch.empty_like(h)
             r = f_op.fwd(h, save=save, out=ht, res=h, alpha=1.0, alpha_dev=deltas[n:n + 1],
                          bufs=[a_[n] for a_ in arenas] if arenas is not None else None,
                          maxima=mx_arena[:, :, n] if mx_arena is not None else None)
-            g = g_op.fwd(x[i], ht, save=save, out=hs[n])
+            g = g_op.fwd(x[i], ht, save=save, out=hs[n],
+                         bufs={"rh": gru_ar["rh"][i], "mx": gru_ar["mx"][:, :, i]} if gru_ar is not None else None)
             if save:
                 saved.append((r[1], g[1]))
             h = hs[n]
         if save:
             ctx.f_op, ctx.g_op, ctx.n_f, ctx.order, ctx.deltas, ctx.saved, ctx.params = f_op, g_op, n_f, order, deltas, saved, params
             ctx.x_shape = (T, B, H, W, Cx)
+            ctx.gru_arenas = gru_ar is not None
         return from_nhwc(hs)
 
     @staticmethod
@@ -947,6 +955,10 @@ class _EncoderFn(torch.autograd.Function):
         if Lf > 1 and all(c.in_channels == C for c, _ in f_op.layers[1:]):
             g_arenas = [torch.empty((T, B, H, W, C), dtype=torch.float32, device=d.device) for _ in range(Lf - 1)]
         DX = torch.empty((T, B, H, W, Cx + C), dtype=torch.float32, device=d.device)   # [dx_i | dh~] per frame
+        gru_bw = None
+        if ctx.gru_arenas:                                    # dy of the ConvGRU's weight gradients, indexed by frame like x
+            gru_bw = {"dcpre": torch.empty((T, B, H, W, C), dtype=torch.float32, device=d.device),
+                      "dg": torch.empty((T, B, H, W, 2 * C), dtype=torch.float32, device=d.device)}
         a = None                                              # adjoint of h after iteration n
         for n in range(T - 1, -1, -1):
             i = order[n]
@@ -956,7 +968,8 @@ class _EncoderFn(torch.autograd.Function):
                 dh = torch.empty_like(a)
                 be.lincomb(dh, [a, d[n]], [1.0, 1.0])
             sv_f, sv_g = saved[n]
-            D = g_op.bwd(sv_g, dh, sink, out=DX[i])
+            D = g_op.bwd(sv_g, dh, sink, out=DX[i],
+                         bufs={"dcpre": gru_bw["dcpre"][i], "dg": gru_bw["dg"][i]} if gru_bw is not None else None)
             dht = D[..., Cx:]                                 # adjoint of h~ (row stride Cx+C)
             if n == 0:
                 # h_0 = 0 is a constant: only the parameter gradients of f(0) remain

@@ -117,24 +117,25 @@ class GradSink:
         self._pending: Dict[int, Tuple[nn.Conv2d, list]] = {}
         self.deferred = False                           # True: add_wgrad only records; flush() launches, batched
 
-    def add_wgrad(self, conv: nn.Conv2d, x: torch.Tensor, dy: torch.Tensor, amax=None) -> None:
+    def add_wgrad(self, conv: nn.Conv2d, x: torch.Tensor, dy: torch.Tensor, amax=None, x1: Optional[torch.Tensor] = None) -> None:
         """dW(conv) += x^T dy, db += colsum(dy).  While `deferred`, the request is only recorded: weight gradients are off
         the critical path of a backward pass, and requests whose operands are consecutive slices of one buffer (the RK
         stages of a step, allocated as [s, B, ...] arenas) run as ONE launch over s*B images.
         amax = (ax, ad): per-image maxima [B] of x and dy, as the chain kernels measured them; such requests run on the kind::f16
-        kernel without a max pass, and merge when their maxima are consecutive slices too."""
+        kernel without a max pass, and merge when their maxima are consecutive slices too.  x1: second source of a convolution
+        over torch.cat((x, x1)) (the ConvGRU's), merged under the same rule."""
         if (conv.weight is None or not conv.weight.requires_grad) and (conv.bias is None or not conv.bias.requires_grad):
             return
         if not self.deferred:
-            self._launch(conv, x, dy, amax)
+            self._launch(conv, x, dy, amax, x1)
         else:
-            self._pending.setdefault(id(conv.weight), (conv, []))[1].append((x, dy, amax))
+            self._pending.setdefault(id(conv.weight), (conv, []))[1].append((x, dy, amax, x1))
 
-    def _launch(self, conv: nn.Conv2d, x: torch.Tensor, dy: torch.Tensor, amax=None) -> None:
+    def _launch(self, conv: nn.Conv2d, x: torch.Tensor, dy: torch.Tensor, amax=None, x1: Optional[torch.Tensor] = None) -> None:
         gw, gb = self.get_packed(conv.weight), self.get(conv.bias)
         if gw is None:          # bias-only gradient: the kernel still needs a dw target
             gw = _scratch_packed(conv.weight)
-        K.backend().conv2d_wgrad_packed(x, None, dy, conv.kernel_size[0], gw, gb, f16=_wgrad_f16(), amax=amax)
+        K.backend().conv2d_wgrad_packed(x, x1, dy, conv.kernel_size[0], gw, gb, f16=_wgrad_f16(), amax=amax)
 
     def flush(self) -> None:
         for conv, items in self._pending.values():
@@ -175,40 +176,54 @@ class GradSink:
 
 
 def _slice_runs(items):
-    """[(x, dy[, amax])] -> the same requests with every run of consecutive dense slices of one storage merged into one
-    (x [n*B, ...], dy [n*B, ...][, amax]) request.  amax = (ax, ad) per-image maxima [B] or None; a run merges only while the
-    maxima (when present) are consecutive slices as well, and comes back with ax, ad of n*B entries."""
-    items = [(it[0], it[1], it[2] if len(it) > 2 else None) for it in items]
-    with_amax = any(it[2] is not None for it in items)
+    """[(x, dy[, amax[, x1]])] -> the same requests with every run of consecutive dense slices of one storage merged into one
+    (x [n*B, ...], dy [n*B, ...], amax, x1) request.  amax = (ax, ad) per-image maxima [B] or None, x1 = second source or None;
+    a run merges only while EVERY tensor of the request (x, dy, and when present x1, ax, ad) continues its predecessor's, and
+    comes back with all of them n*B long.  Requests given as (x, dy) pairs come back as pairs."""
+    pairs = all(len(it) == 2 for it in items)
+    items = [(it[0], it[1], it[2] if len(it) > 2 else None, it[3] if len(it) > 3 else None) for it in items]
     items = sorted(items, key=lambda it: it[0].data_ptr())
 
+    def parts(it):
+        x, dy, amax, x1 = it
+        return [x, dy] + ([x1] if x1 is not None else []) + (list(amax) if amax is not None else [])
+
     def follows(t0, t1, n):
-        return (t1.shape == t0.shape and t1.is_contiguous() and t1.data_ptr() == t0.data_ptr() + n * t0.numel() * t0.element_size()
+        return (t1.shape == t0.shape and t1.stride() == t0.stride()
+                and t1.data_ptr() == t0.data_ptr() + n * t0.shape[0] * t0.stride(0) * t0.element_size()
                 and t1.untyped_storage().data_ptr() == t0.untyped_storage().data_ptr())
+
+    def mergeable(t):
+        # dense image slices: [B, H, W, C] whose rows may be a channel slice of a wider buffer, images back to back
+        if t.dim() == 1:
+            return t.is_contiguous()
+        return t.dim() == 4 and t.stride(3) == 1 and t.stride(1) == t.shape[2] * t.stride(2) and t.stride(0) == t.shape[1] * t.stride(1)
 
     out, i = [], 0
     while i < len(items):
-        x0, d0, a0 = items[i]
+        p0 = parts(items[i])
         n = 1
-        ok = x0.dim() == 4 and x0.is_contiguous() and d0.is_contiguous() and (a0 is None or (a0[0].is_contiguous() and a0[1].is_contiguous()))
+        ok = all(mergeable(t) for t in p0)
         while ok and i + n < len(items):
-            x1, d1, a1 = items[i + n]
-            if not (follows(x0, x1, n) and follows(d0, d1, n)) or (a0 is None) != (a1 is None):
+            it1 = items[i + n]
+            if (it1[2] is None) != (items[i][2] is None) or (it1[3] is None) != (items[i][3] is None):
                 break
-            if a0 is not None and not (follows(a0[0], a1[0], n) and follows(a0[1], a1[1], n)):
+            if not all(follows(t0, t1, n) for t0, t1 in zip(p0, parts(it1))):
                 break
             n += 1
         if n > 1:
-            B = x0.shape[0]
-            run = [torch.as_strided(x0, (n * B,) + tuple(x0.shape[1:]), x0.stride()),
-                   torch.as_strided(d0, (n * B,) + tuple(d0.shape[1:]), d0.stride())]
-            if a0 is not None:
-                run.append((torch.as_strided(a0[0], (n * B,), (1,)), torch.as_strided(a0[1], (n * B,), (1,))))
+            m = [torch.as_strided(t, (n * t.shape[0],) + tuple(t.shape[1:]), t.stride()) for t in p0]
+            x, dy = m[0], m[1]
+            k = 2
+            x1 = None
+            if items[i][3] is not None:
+                x1 = m[k]
+                k += 1
+            amax = (m[k], m[k + 1]) if items[i][2] is not None else None
+            run = (x, dy, amax, x1)
         else:
-            run = [x0, d0] + ([a0] if a0 is not None else [])
-        if with_amax and len(run) == 2:
-            run.append(None)
-        out.append(tuple(run))
+            run = items[i]
+        out.append(run[:2] if pairs else run)
         i += n
     return out
 
@@ -535,7 +550,10 @@ class GruOp:
         return (CONV_SPLIT == "f16" and CONV_IMPL != "simt" and hasattr(be, "conv16") and self.C == 64 and self.Cx == 64
                 and be.conv16_shape_ok(x, h, 2 * self.C, self.R))
 
-    def fwd(self, x: torch.Tensor, h: torch.Tensor, save: bool = False, out: Optional[torch.Tensor] = None):
+    def fwd(self, x: torch.Tensor, h: torch.Tensor, save: bool = False, out: Optional[torch.Tensor] = None,
+            bufs: Optional[dict] = None):
+        """bufs (fused path, optional): caller-owned {"rh": [B,H,W,C], "mx": [2,2,B]} -- slices of arenas over the steps of a
+        recurrence, so that the steps' weight gradients can run as one launch (GradSink.add_wgrad)."""
         be = K.backend()
         B, H, W, Cx = x.shape
         C, R = self.C, self.R
@@ -547,7 +565,7 @@ class GruOp:
             wg = self.pc_g.get_f16(save).fwd_f16
             wc = self.pc_c.get_f16(save).fwd_f16
             z = torch.empty((B, H, W, C), dtype=f32, device=dev)
-            rh = torch.empty((B, H, W, C), dtype=f32, device=dev)
+            rh = bufs["rh"] if bufs is not None else torch.empty((B, H, W, C), dtype=f32, device=dev)
             st_g = torch.empty((B * (2 * C // 32) * 2,), dtype=f32, device=dev)
             st_c = torch.empty((B * (C // 32) * 2,), dtype=f32, device=dev)
             g = torch.empty((B, H, W, 2 * C), dtype=f32, device=dev) if save else None
@@ -555,7 +573,7 @@ class GruOp:
             # max |dcpre|}; the conv16 launches measure them for their operand scales anyway, the weight gradients take them
             mx = None
             if save and _wgrad_scaled() and be.wgrad_f16_shape_ok(Cx, C, 2 * C, H, W, R):
-                mx = torch.empty((2, 2, B), dtype=f32, device=dev)
+                mx = bufs["mx"] if bufs is not None and bufs.get("mx") is not None else torch.empty((2, 2, B), dtype=f32, device=dev)
             mxa = (lambda i, j: {"amax_out": mx[i, j]}) if mx is not None else (lambda i, j: {})
             be.conv16_gru_gates(x, h, wg, R, self.cg.bias, self.gn_g.weight, self.gn_g.bias, self.gn_g.eps, z, rh, st_g, g_raw=g,
                                 **mxa(0, 0))
@@ -585,8 +603,10 @@ class GruOp:
             return hnew, (x, h, g, z, rh, st_g, cpre, cand, st_c)
         return hnew
 
-    def bwd(self, saved, dhnew: torch.Tensor, sink: GradSink, out: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """Returns D = [dx | dh] as one [B,H,W,Cx+C] buffer (channel slices are the two gradients)."""
+    def bwd(self, saved, dhnew: torch.Tensor, sink: GradSink, out: Optional[torch.Tensor] = None,
+            bufs: Optional[dict] = None) -> torch.Tensor:
+        """Returns D = [dx | dh] as one [B,H,W,Cx+C] buffer (channel slices are the two gradients).  bufs (optional): caller-owned
+        {"dcpre": [B,H,W,C], "dg": [B,H,W,2C]} arena slices (see fwd)."""
         be = K.backend()
         x, h, g, z, rh, st_g, cpre, cand, st_c = saved[:9]
         mx = saved[9] if len(saved) > 9 else None       # the step's maxima (fused forward only)
@@ -598,7 +618,7 @@ class GruOp:
             t = sink.get(p)
             return t if t is not None else torch.zeros_like(p)
 
-        dcpre = torch.empty((B, H, W, C), dtype=f32, device=dev)
+        dcpre = bufs["dcpre"] if bufs is not None else torch.empty((B, H, W, C), dtype=f32, device=dev)
         dz = torch.empty((B, H, W, C), dtype=f32, device=dev)
         dh_a = torch.empty((B, H, W, C), dtype=f32, device=dev)
         be.gru_out_bwd(dhnew, cpre, cand, z, h, self.gn_c.weight, st_c, dcpre, dz, dh_a,
@@ -613,11 +633,8 @@ class GruOp:
         else:
             pc = self.pc_c.get(H, W, Cx, C, True)
             be.conv2d(dcpre, None, pc.dgrad_simt, pc.dgrad_tc, Cx + C, R, None, ACT_NONE, D1)
-        gw, gb = sink.get_packed(self.cc.weight), sink.get(self.cc.bias)
-        if gw is not None or gb is not None:
-            be.conv2d_wgrad_packed(x, rh, dcpre, R, gw if gw is not None else _scratch_packed(self.cc.weight), gb, f16=_wgrad_f16(),
-                                   amax=(mx[1, 0], mx[1, 1]) if mx is not None else None)
-        dg = torch.empty((B, H, W, 2 * C), dtype=f32, device=dev)
+        sink.add_wgrad(self.cc, x, dcpre, amax=(mx[1, 0], mx[1, 1]) if mx is not None else None, x1=rh)
+        dg = bufs["dg"] if bufs is not None else torch.empty((B, H, W, 2 * C), dtype=f32, device=dev)
         drh = D1[..., Cx:]
         be.gru_gates_bwd(dz, drh, dh_a, g, h, self.gn_g.weight, self.gn_g.bias, st_g, dg, drh,
                          grad_or_scratch(self.gn_g.weight), grad_or_scratch(self.gn_g.bias))   # D1[..., Cx:] <- dh_a + drh*r
@@ -629,8 +646,5 @@ class GruOp:
         else:
             pg = self.pc_g.get(H, W, Cx, C, True)
             be.conv2d(dg, None, pg.dgrad_simt, pg.dgrad_tc, Cx + C, R, None, ACT_NONE, D2, res=D1, alpha=1.0)
-        gw, gb = sink.get_packed(self.cg.weight), sink.get(self.cg.bias)
-        if gw is not None or gb is not None:
-            be.conv2d_wgrad_packed(x, h, dg, R, gw if gw is not None else _scratch_packed(self.cg.weight), gb, f16=_wgrad_f16(),
-                                   amax=(mx[0, 0], mx[0, 1]) if mx is not None else None)
+        sink.add_wgrad(self.cg, x, dg, amax=(mx[0, 0], mx[0, 1]) if mx is not None else None, x1=h)
         return D2
