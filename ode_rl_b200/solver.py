@@ -503,12 +503,25 @@ class _Dopri5Fn(torch.autograd.Function):
             ai, t0, t1, dt, js = steps[m]
             dt_dev = ws.log[ai, 1:2]
             y, k0 = ws.ysave[m], ws.fsave[m]
-            # ---- recompute the six stages of this accepted step, keeping the conv activations
+            # ---- recompute the six stages of this accepted step, keeping the conv activations -- in [6, B, ...] arenas (stage
+            # inputs, activations, gradient planes, per-image maxima), so that a layer's six weight gradients of the step run as
+            # one launch at the step's end (GradSink.add_wgrad)
+            L_ = len(op.layers)
+            ar = None
+            if L_ > 1 and all(c.out_channels == like.shape[3] and c.in_channels == like.shape[3] for c, _ in op.layers):
+                mk = lambda: torch.empty((6,) + tuple(like.shape), dtype=like.dtype, device=like.device)   # noqa: E731
+                ar = {"yi": mk(), "act": [mk() for _ in range(L_ - 1)], "dk": mk(), "g": [mk() for _ in range(L_ - 1)],
+                      "mx": torch.empty((L_, 2, 6, like.shape[0]), dtype=torch.float32, device=like.device) if op.maxima_ok(like) else None}
+                sink.deferred = True
             ks, saved = [k0], [None]
             for s in range(6):
-                yi = new()
+                yi = ar["yi"][s] if ar is not None else new()
                 _lin(be, yi, [y] + ks, [1.0] + DP_BETA[s], dt_dev=dt_dev, dt_from=1)
-                ki, sv = op.fwd(yi, save=True, maxima=op.new_maxima(yi))      # per evaluation: the weight gradients are not merged here
+                if ar is not None:
+                    ki, sv = op.fwd(yi, save=True, bufs=[a_[s] for a_ in ar["act"]],
+                                    maxima=ar["mx"][:, :, s] if ar["mx"] is not None else None)
+                else:
+                    ki, sv = op.fwd(yi, save=True, maxima=op.new_maxima(yi))
                 ks.append(ki)
                 saved.append(sv)
             # ---- dense-output adjoints: sol_j = P(x_j) . (y0, y1, y_mid, dt f0, dt f1)
@@ -530,10 +543,12 @@ class _Dopri5Fn(torch.autograd.Function):
             dys: List[Optional[torch.Tensor]] = [None] * 7
             if terms:
                 dk6 = terms[0] if len(terms) == 1 else _sum_into(be, new(), terms, [1.0] * len(terms))
-                dys[6] = op.bwd(saved[6], dk6, sink)
+                dys[6] = op.bwd(saved[6], dk6, sink, gbufs=[g_[5] for g_ in ar["g"]] if ar is not None else None)
                 Ay6_terms.append(dys[6])
             if not Ay6_terms:
                 A_y, A_f = None, None
+                sink.flush()
+                sink.deferred = False
                 continue
             Ay6 = Ay6_terms[0] if len(Ay6_terms) == 1 else _sum_into(be, new(), Ay6_terms, [1.0] * len(Ay6_terms))
             # ---- stages 5..1, then k0 (an input of the step: its adjoint goes to the previous step's k6)
@@ -548,7 +563,7 @@ class _Dopri5Fn(torch.autograd.Function):
                 extra = E.get(i)
                 if not keep and extra is None:
                     continue
-                dk = new()
+                dk = ar["dk"][i - 1] if (ar is not None and i > 0) else new()
                 if keep:
                     n_dt = len(keep)
                     ops_ = [a_ for a_, _ in keep] + ([extra] if extra is not None else [])
@@ -559,7 +574,9 @@ class _Dopri5Fn(torch.autograd.Function):
                 if i == 0:
                     dk0 = dk
                 else:
-                    dys[i] = op.bwd(saved[i], dk, sink)
+                    dys[i] = op.bwd(saved[i], dk, sink, gbufs=[g_[i - 1] for g_ in ar["g"]] if ar is not None else None)
+            sink.flush()                                      # the step's weight gradients, merged over its stages
+            sink.deferred = False
             terms = [Ay6] + [dys[i] for i in range(1, 6) if dys[i] is not None]
             if "y0" in E:
                 terms.append(E["y0"])

@@ -612,3 +612,38 @@ def test_chain_maxima_stay_tight_when_the_state_blows_up(fake_backend):
                 assert rel_err(g, ps[n].grad) < tol, (method, n)
         for p in solver.parameters():
             p.grad = None
+
+
+def test_weight_gradient_launches_merge_over_stages_and_steps(fake_backend):
+    """The arenas that make a layer's weight gradients consecutive slices (solver.RolloutArenas, the dopri5 backward's per-step
+    arenas): rk4 on a 10-point grid = 36 evaluations of the chain, yet every layer but the first runs ONE launch over all 36 x B
+    images and the first two (its stage-0 input is the solution buffer) -- and dopri5 one launch per layer and accepted step
+    (+ the FSAL stage's own gradient plane for the last layer, + the first evaluation)."""
+    from ode_rl_b200 import kernels as K
+    be = K.backend()
+    calls = []
+    orig = be.conv2d_wgrad_packed
+
+    def spy(x0, x1, dy, R, dwp, db, **kw):
+        calls.append((x0.shape[0], kw.get("amax") is not None))
+        return orig(x0, x1, dy, R, dwp, db, **kw)
+
+    be.conv2d_wgrad_packed = spy
+    try:
+        f = make_ode_func(odex, C=64, n_units=64, n_layers=2)
+        L = len(f.op().layers)
+        _, tp = timesteps(10, 10)
+        torch.manual_seed(0)
+        z0 = torch.randn(2, 64, 16, 16, requires_grad=True)
+        solver = odex.DiffEqSolver(f, "rk4")
+        solver(z0, tp).sum().backward()
+        assert sorted(calls) == sorted([(72, True)] * (L - 1) + [(54, True), (18, True)]), calls
+        del calls[:]
+        solver = odex.DiffEqSolver(f, "dopri5", odeint_rtol=1e-3, odeint_atol=1e-4)
+        solver(z0, tp).sum().backward()
+        n_acc = solver.last_stats.n_accept
+        big = [c for c in calls if c[0] >= 10]
+        assert len(big) == L * n_acc and all(c[1] for c in big), (n_acc, calls)     # 5-6 stages x B = 2 merged per layer and step
+        assert len(calls) <= L * n_acc + 2 * n_acc + L, (n_acc, calls)
+    finally:
+        be.conv2d_wgrad_packed = orig
