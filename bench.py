@@ -30,7 +30,7 @@ FEVAL_FLOPS = 94371840            # per sample, 5 x conv3x3 64->64 at 16x16 (SUR
 CONV3_FLOPS = 2 * 256 * 64 * 576  # one 3x3 64->64 conv, per sample
 
 
-NET_TRAFFIC_F16_B128 = 9804416  # bytes per launch at batch 128: dram read 9.22 MB + written 0.28-0.89 MB (mean of the two launches captured; ncu --set full, profiles/r02_ncu.md)
+NET_TRAFFIC_F16_B128 = 10748416  # bytes per launch at batch 128: dram read 9.21 MB + written 1.01-2.06 MB (mean of the two launches captured; ncu --set full, profiles/r02c_ncu.md)
 NET_TRAFFIC_B128 = 10654848  # bytes per launch at batch 128: dram read 9.95 MB + written 0.42-0.98 MB (mean of the two launches captured; ncu --set full, profiles/r01_final_ncu.md)
 
 
@@ -785,7 +785,7 @@ def main():
                 # dram__bytes_read.sum + dram__bytes_write.sum of one launch at batch 128 (ncu --set full,
                 # profiles/r01_final_ncu.md), scaled with the batch; None until that capture exists
                 "traffic": (NET_TRAFFIC_F16_B128 if split else NET_TRAFFIC_B128) and int((NET_TRAFFIC_F16_B128 if split else NET_TRAFFIC_B128) * B / 128),
-                "traffic_source": "profiles/r02_ncu.md (ncu --set full, per launch)" if split else "profiles/r01_final_ncu.md (ncu --set full, per launch)",
+                "traffic_source": "profiles/r02c_ncu.md (ncu --set full, per launch)" if split else "profiles/r01_final_ncu.md (ncu --set full, per launch)",
                 "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (of measured)" if peaks else "fallback 1.4 PF (of fallback)",
                 "note": ("achieved counts algorithmic FLOPs once (2*M*N*K per layer, 5 layers per launch); fp32-level accuracy costs 3 fp16 "
                          "MMAs per useful one (hi.hi, hi.lo, lo.hi) at the bf16 / fp16 rate, so the ceiling of useful FLOPs is 1/3 of "

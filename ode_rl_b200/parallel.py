@@ -15,7 +15,7 @@ All collectives go through torch.distributed on the current stream (NCCL on GPUs
 """
 from __future__ import annotations
 
-from typing import Iterable, List, Optional, Tuple
+from typing import Iterable, List, Optional, Sequence, Tuple
 
 import torch
 import torch.distributed as dist
@@ -61,30 +61,96 @@ def shard_solver(solver, mode: str = "sum", group=None):
 
 
 class GradBucket:
-    """Flat fp32 bucket over the parameters' gradients: one all-reduce per step, averaged over ranks."""
+    """Flat fp32 bucket(s) over the parameters' gradients, averaged over ranks.
 
-    def __init__(self, params: Iterable[torch.nn.Parameter], group=None):
-        self.params: List[torch.nn.Parameter] = [p for p in params if p.requires_grad]
+    Plain use: one all-reduce per step (`allreduce()` after the backward).
+    `stages`: parameter groups in the order their gradients become FINAL during the backward (for ODEConvGRU: the decoder side
+    -- ConvDecode + the solver's ODE function -- then the encoder cell, then ConvEncode).  Each group gets its own flat bucket,
+    and its copy-in / all-reduce / copy-out is launched from a post-accumulate-grad hook as soon as the group's last gradient
+    has landed, on a side stream that forks from the backward's stream at that point: the decoder side's all-reduce runs under
+    the encoder recurrence's backward instead of after it.  `allreduce()` then only reduces what is left and joins the side
+    stream.  The launch order is the same on every rank (the backward is the same program), so the collectives match up; the
+    fork / join are stream waits, which a CUDA graph capture records as edges."""
+
+    def __init__(self, params: Iterable[torch.nn.Parameter], group=None,
+                 stages: Optional[Sequence[Iterable[torch.nn.Parameter]]] = None):
+        seen = set()
+        self.params: List[torch.nn.Parameter] = []
+        for p in params:
+            if p.requires_grad and id(p) not in seen:
+                seen.add(id(p))
+                self.params.append(p)
         self.group = group
-        self.flat: Optional[torch.Tensor] = None
+        self.flat: dict = {}
+        self.stages: List[List[torch.nn.Parameter]] = []
+        self._count: List[int] = []
+        self._launched: List[bool] = []
+        self._side = None
+        self._handles = []
+        staged = set()
+        for st in (stages or []):
+            ps = []
+            for p in st:
+                if p.requires_grad and id(p) in seen and id(p) not in staged:
+                    staged.add(id(p))
+                    ps.append(p)
+            if ps:
+                k = len(self.stages)
+                self.stages.append(ps)
+                self._count.append(0)
+                self._launched.append(False)
+                for p in ps:
+                    self._handles.append(p.register_post_accumulate_grad_hook(lambda _p, k=k: self._on_grad(k)))
+        self._rest = [p for p in self.params if id(p) not in staged]
 
-    def allreduce(self) -> int:
-        """Averages .grad over the ranks in place; returns the bucket size in bytes."""
-        ps = [p for p in self.params if p.grad is not None]
+    def _on_grad(self, k: int) -> None:
+        self._count[k] += 1
+        if self._count[k] == len(self.stages[k]) and not self._launched[k] and dist.is_initialized():
+            ps = self.stages[k]
+            if ps[0].grad is not None and ps[0].grad.is_cuda:
+                if self._side is None:
+                    self._side = torch.cuda.Stream(device=ps[0].grad.device)
+                self._side.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(self._side):
+                    self._reduce(ps, k)
+            else:
+                self._reduce(ps, k)
+            self._launched[k] = True
+
+    def _reduce(self, params: List[torch.nn.Parameter], key) -> int:
+        ps = [p for p in params if p.grad is not None]
         if not ps:
             return 0
         n = sum(p.grad.numel() for p in ps)
-        if self.flat is None or self.flat.numel() != n or self.flat.device != ps[0].grad.device:
-            self.flat = torch.empty(n, dtype=torch.float32, device=ps[0].grad.device)
+        flat = self.flat.get(key)
+        if flat is None or flat.numel() != n or flat.device != ps[0].grad.device:
+            flat = torch.empty(n, dtype=torch.float32, device=ps[0].grad.device)
+            self.flat[key] = flat
         views = []
         o = 0
         for p in ps:
-            v = self.flat[o:o + p.grad.numel()].view_as(p.grad)
-            views.append(v)
+            views.append(flat[o:o + p.grad.numel()].view_as(p.grad))
             o += p.grad.numel()
         torch._foreach_copy_(views, [p.grad for p in ps])
         world = dist.get_world_size(self.group)
-        dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=self.group)
-        self.flat.div_(world)
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group)
+        flat.div_(world)
         torch._foreach_copy_([p.grad for p in ps], views)
         return n * 4
+
+    def allreduce(self) -> int:
+        """Averages .grad over the ranks in place (whatever the hooks have not reduced yet); returns the bytes reduced in total."""
+        rest = list(self._rest)
+        done = 0
+        for k, ps in enumerate(self.stages):
+            if self._launched[k]:
+                done += sum(p.grad.numel() for p in ps if p.grad is not None) * 4
+            else:
+                rest += ps
+        nbytes = self._reduce(rest, "rest") + done
+        if self._side is not None and any(self._launched):
+            torch.cuda.current_stream().wait_stream(self._side)
+        for k in range(len(self.stages)):
+            self._count[k] = 0
+            self._launched[k] = False
+        return nbytes

@@ -58,10 +58,15 @@ def _worker(rank, world, port, mode, q):
         # ---- rk4 training gradient through the flat bucket
         rk = odex.DiffEqSolver(f, "rk4")
         z = z_all[lo:hi].clone()
+        # staged bucket: the first half of the parameters is reduced from a post-accumulate hook during the backward, the rest
+        # by allreduce() -- same averaged gradients as the single flat bucket
+        plist = list(rk.parameters())
+        bucket = parallel.GradBucket(plist, stages=[plist[:len(plist) // 2]])
         out = rk(z, tp[:3])
         (out.square().sum() / 5.0).backward()                # global mean over 5 samples -> per-rank partial sums
-        bucket = parallel.GradBucket(rk.parameters())
+        assert any(bucket._launched)
         nbytes = bucket.allreduce()
+        assert not any(bucket._launched)
         g = torch.cat([p.grad.reshape(-1) for p in rk.parameters()]) * world   # bucket averages; undo for the sum
         q.put((rank, sol.contiguous().numpy().copy(), [(a[1], a[3]) for a in st.attempts], (st.n_accept, st.n_reject),
                g.detach().numpy().copy(), nbytes))
