@@ -17,7 +17,8 @@
 // SAME pair of planes one after the other (both must carry the same power-of-two scale, taken from the larger of their maxima):
 // source 1 is TMA-loaded into the fp32 staging tile S while source 0's MMAs run and converted once they have retired.
 //   warp 0  TMA producer (source 0 tile, weight ring)      warp 1  TMEM allocator + MMA issue
-//   warps 2-5  conversion (+ source-1 / aux TMA by its thread 0), then the epilogue
+//   warps 2-9  conversion (+ source-1 / aux TMA by its thread 0), then the epilogue: two groups of four warps, one per 32-channel
+//              half of the block's 64 outputs (= one GroupNorm group), so that every scheduler holds two epilogue warps
 // GroupNorm statistics: per-thread chunk mean / M2 -> Chan merges (warp shuffles, then 4 warps through shared memory): the
 // centred sum of squares, not E[x^2] - mean^2; a second pass over TMEM applies them.
 #include <cuda.h>
