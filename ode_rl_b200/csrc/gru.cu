@@ -138,6 +138,7 @@ __global__ void __launch_bounds__(256) gru_out_bwd_kernel(const float* __restric
     const float ga[4] = {ga4.x, ga4.y, ga4.z, ga4.w};
     float s1 = 0.f, s2 = 0.f;
     float dgm[4] = {0.f, 0.f, 0.f, 0.f}, dbt[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 4
     for (int u = threadIdx.x; u < HW * 8; u += blockDim.x) {
         const long o = (static_cast<long>(b) * HW + (u >> 3)) * C + c0 + c4;
         const float4 d4 = ld4(dhnew + o), x4 = ld4(cpre + o), cc4 = ld4(cand + o), z4 = ld4(z + o);
@@ -155,6 +156,7 @@ __global__ void __launch_bounds__(256) gru_out_bwd_kernel(const float* __restric
     const float invM = 1.f / static_cast<float>(HW * 32);
     const float m1 = block_sum(s1, sh) * invM;
     const float m2 = block_sum(s2, sh) * invM;
+#pragma unroll 4
     for (int u = threadIdx.x; u < HW * 8; u += blockDim.x) {
         const long p = static_cast<long>(b) * HW + (u >> 3);
         const long o = p * C + c0 + c4;
@@ -207,6 +209,7 @@ __global__ void __launch_bounds__(256) gru_gates_bwd_kernel(const float* __restr
             m1 = block_sum(s1, sh) * invM;
             m2 = block_sum(s2, sh) * invM;
         }
+#pragma unroll 4
         for (int u = threadIdx.x; u < HW * 8; u += blockDim.x) {
             const long p = static_cast<long>(b) * HW + (u >> 3);
             const float4 x4 = ld4(g + p * 2 * C + c0 + c4);
