@@ -40,7 +40,7 @@ namespace odex {
 
 constexpr int kF16MaxL = ODEX_NET_MAX_LAYERS;
 constexpr int kF16BStage = 2 * kF16C * 128;    // [w_hi ; w_lo] of one tap: 16 KB
-constexpr int kF16SB = 3;
+constexpr int kF16SB = 4;
 constexpr int kF16EpiThreads = 256;             // 8 epilogue warps
 constexpr int kF16Threads = 64 + kF16EpiThreads;
 constexpr int kF16Smem = 1024 + 2 * kF16Plane + 2 * kF16SHalf + kF16SB * kF16BStage + 256 + kF16MaxL * 256 + 64;
@@ -78,13 +78,13 @@ convnet_f16_kernel(const __grid_constant__ F16Maps tm, const F16Args a) {
     const uint32_t bst0 = s_base + 2u * kF16SHalf;
     const uint32_t bars = bst0 + kF16SB * kF16BStage;
     const uint32_t bar_in = bars;                  // input tile landed in S
-    const uint32_t bar_b_full = bars + 8;          // [3]
-    const uint32_t bar_b_empty = bars + 32;        // [3]
-    const uint32_t bar_acc = bars + 56;            // a layer's MMAs have retired            (one phase per layer)
-    const uint32_t bar_next = bars + 64;           // a layer's operands are in the planes   (128 arrivals per layer, layer 0 included)
-    const uint32_t bar_aux = bars + 72;            // a mask / residual tile landed in S     (one phase per use)
-    const uint32_t tmem_slot = bars + 80;
-    const uint32_t amax_s = bars + 96;             // [L + 1] measured max |a_l| (float bits, >= 0)
+    const uint32_t bar_b_full = bars + 8;          // [kF16SB <= 4]
+    const uint32_t bar_b_empty = bars + 40;        // [kF16SB <= 4]
+    const uint32_t bar_acc = bars + 72;            // a layer's MMAs have retired            (one phase per layer)
+    const uint32_t bar_next = bars + 80;           // a layer's operands are in the planes   (128 arrivals per layer, layer 0 included)
+    const uint32_t bar_aux = bars + 88;            // a mask / residual tile landed in S     (one phase per use)
+    const uint32_t tmem_slot = bars + 96;
+    const uint32_t amax_s = bars + 112;            // [L + 1] measured max |a_l| (float bits, >= 0)
     const uint32_t bias_s = bars + 256;            // [L][64] floats
 
     const int warp = threadIdx.x >> 5;
