@@ -61,6 +61,10 @@ long long odex_launch_count(void);
  * Sizes are in floats.  Replaces: nothing in the reference (cuDNN/oneDNN do their own packing). */
 size_t odex_packed_weight_floats(int n_out, int c_in, int R, int tc);
 int odex_pack_weights(const float* w_oihw, int N, int C, int R, int dgrad, int tc, float* out, odex_stream_t s);
+/* odex_pack_weights(tc = 2) of BOTH orientations of one weight tensor (dgrad = 0 into out_fwd, dgrad = 1 into out_dgrad; each
+ * odex_packed_weight_floats(N, C, R, 2) floats) in one pair of launches: a training step repacks every convolution after the
+ * optimizer step, and the four tiny launches per convolution were 2.5 % of the config-A step.  N, C multiples of 64. */
+int odex_pack_weights_f16_pair(const float* w_oihw, int N, int C, int R, float* out_fwd, float* out_dgrad, odex_stream_t s);
 
 /* ------------------------------------------------------------------------------------------------ conv
  * out[p, n] = epi( bias[n] + sum_{r,s,c} X[p + (r,s) - pad, c] * W[n, c, r, s] ),  stride 1, pad (R-1)/2,

@@ -121,6 +121,7 @@ SIGNATURES = {
     "odex_launch_count": (_ll, []),
     "odex_packed_weight_floats": (_sz, [_i, _i, _i, _i]),
     "odex_pack_weights": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _vp]),
+    "odex_pack_weights_f16_pair": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp]),
     "odex_conv2d": (_i, [C.POINTER(ConvDesc), _vp]),
     "odex_conv2d_repeat": (_i, [C.POINTER(ConvDesc), _i, _vp]),
     "odex_convnet": (_i, [C.POINTER(ConvNetDesc), _vp]),

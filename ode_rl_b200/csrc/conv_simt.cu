@@ -115,6 +115,57 @@ __global__ void pack_f16_kernel(const float* __restrict__ w, int N, int C, int R
     if (blockIdx.x == 0 && threadIdx.x == 0) tail[0] = 1.f / s;
 }
 
+// Both orientations of one weight tensor in one pair of launches (odex_pack_weights_f16_pair): blocks [0, N) are the forward
+// operator's rows, blocks [N, N + C) the data-gradient operator's; same arithmetic as the single-orientation kernels.
+__global__ void pack_f16_stats2_kernel(const float* __restrict__ w, int N, int C, int R, float* __restrict__ tail_f,
+                                       float* __restrict__ tail_d) {
+    const int dgrad = static_cast<int>(blockIdx.x) >= N;
+    const int No = dgrad ? C : N, Ci = dgrad ? N : C;
+    const int n = dgrad ? static_cast<int>(blockIdx.x) - N : static_cast<int>(blockIdx.x);
+    if (n >= No) return;
+    float* tail = dgrad ? tail_d : tail_f;
+    __shared__ float sh[33];
+    float sum = 0.f, mx = 0.f;
+    const int per = Ci * R * R;
+    for (int i = threadIdx.x; i < per; i += blockDim.x) {
+        const int c = i / (R * R), t = i % (R * R);
+        const float v = fabsf(packed_src(w, N, C, R, dgrad, n, c, t / R, t % R));
+        sum += v;
+        mx = fmaxf(mx, v);
+    }
+    sum = block_sum(sum, sh);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((threadIdx.x & 31) == 0) atomicMax(reinterpret_cast<unsigned int*>(tail + 2), __float_as_uint(mx));
+    if (threadIdx.x == 0) atomicMax(reinterpret_cast<unsigned int*>(tail + 1), __float_as_uint(sum));
+}
+
+__global__ void pack_f16_2_kernel(const float* __restrict__ w, int N, int C, int R, __half* __restrict__ out_f, float* __restrict__ tail_f,
+                                  __half* __restrict__ out_d, float* __restrict__ tail_d) {
+    const int taps = R * R;
+    const long total = static_cast<long>(N) * C * taps;            // elements per orientation
+    const float s_f = f16_pack_scale(tail_f[2]), s_d = f16_pack_scale(tail_d[2]);
+    for (long j = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; j < 2 * total;
+         j += static_cast<long>(gridDim.x) * blockDim.x) {
+        const int dgrad = j >= total;
+        const long i = dgrad ? j - total : j;
+        const int No = dgrad ? C : N;
+        const int kk = static_cast<int>(i & 63);
+        const int n = static_cast<int>((i >> 6) % No);
+        const long kb = (i >> 6) / No;
+        const int tap = static_cast<int>(kb % taps);
+        const int grp = static_cast<int>(kb / taps);
+        const float v = packed_src(w, N, C, R, dgrad, n, grp * 64 + kk, tap / R, tap % R) * (dgrad ? s_d : s_f);
+        const __half hi = __float2half_rn(v);
+        const __half lo = __float2half_rn((v - __half2float(hi)) * 2048.f);
+        const long base = kb * (2L * No * 64);
+        __half* out = dgrad ? out_d : out_f;
+        out[base + static_cast<long>(n) * 64 + kk] = hi;
+        out[base + static_cast<long>(No + n) * 64 + kk] = lo;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) { tail_f[0] = 1.f / s_f; tail_d[0] = 1.f / s_d; }
+}
+
 // ------------------------------------------------------------------------------------------------- forward
 struct SimtConvArgs {
     const float* x0; int ld0; int c0;
@@ -422,6 +473,23 @@ extern "C" int odex_pack_weights(const float* w, int N, int C, int R, int dgrad,
     }
     pack_simt_kernel<<<blocks, 256, 0, s>>>(w, N, C, R, dgrad, out);
     return launched("pack_simt_kernel");
+}
+
+extern "C" int odex_pack_weights_f16_pair(const float* w, int N, int C, int R, float* out_fwd, float* out_dgrad, odex_stream_t s_) {
+    cudaStream_t s = static_cast<cudaStream_t>(s_);
+    if (!w || !out_fwd || !out_dgrad || N <= 0 || C <= 0 || R <= 0) return fail(ODEX_E_ARG, "pack_weights_f16_pair: bad argument");
+    if (N % 64 != 0 || C % 64 != 0) return fail(ODEX_E_SHAPE, "pack_weights_f16_pair: N and C must be multiples of 64 (got %d, %d)", N, C);
+    if (!aligned16(out_fwd) || !aligned16(out_dgrad)) return fail(ODEX_E_ALIGN, "pack_weights_f16_pair: outputs not 16-byte aligned");
+    const long total = static_cast<long>(N) * C * R * R;
+    float* tail_f = out_fwd + total;
+    float* tail_d = out_dgrad + total;
+    cudaMemsetAsync(tail_f, 0, 4 * sizeof(float), s);
+    cudaMemsetAsync(tail_d, 0, 4 * sizeof(float), s);
+    pack_f16_stats2_kernel<<<N + C, 128, 0, s>>>(w, N, C, R, tail_f, tail_d);
+    if (int rc = launched("pack_f16_stats2_kernel")) return rc;
+    const int blocks = static_cast<int>(std::min<long>((2 * total + 255) / 256, 8L * kSMs));
+    pack_f16_2_kernel<<<blocks, 256, 0, s>>>(w, N, C, R, reinterpret_cast<__half*>(out_fwd), tail_f, reinterpret_cast<__half*>(out_dgrad), tail_d);
+    return launched("pack_f16_2_kernel");
 }
 
 namespace odex {

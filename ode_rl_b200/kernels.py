@@ -100,6 +100,19 @@ class Backend:
                                               out.data_ptr(), _stream()), "odex_pack_weights")
         return out
 
+    def pack_weights_f16_pair(self, w: torch.Tensor):
+        """odex_pack_weights_f16_pair: (pack_weights(w, False, 2), pack_weights(w, True, 2)) in one pair of launches."""
+        self.require(w)
+        w = w.detach()
+        assert w.dtype == torch.float32 and w.is_contiguous() and w.dim() == 4 and w.shape[2] == w.shape[3]
+        N, Cc, R, _ = w.shape
+        nfl = self.lib.odex_packed_weight_floats(N, Cc, R, 2)
+        fwd = torch.empty(nfl, dtype=torch.float32, device=w.device)
+        dgr = torch.empty(nfl, dtype=torch.float32, device=w.device)
+        _lib.check(self.lib.odex_pack_weights_f16_pair(w.data_ptr(), N, Cc, R, fwd.data_ptr(), dgr.data_ptr(), _stream()),
+                   "odex_pack_weights_f16_pair")
+        return fwd, dgr
+
     # ------------------------------------------------------------------ convolution
     def conv2d(self, x0: torch.Tensor, x1: Optional[torch.Tensor], w_simt: Optional[torch.Tensor],
                w_tc: Optional[torch.Tensor], N: int, R: int, bias: Optional[torch.Tensor], act: int,

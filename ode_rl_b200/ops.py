@@ -253,6 +253,9 @@ class _PackCache:
             self.key16 = key
         pk = self.pk16
         be = K.backend()
+        if need_dgrad and pk.fwd_f16 is None and pk.dgrad_f16 is None and hasattr(be, "pack_weights_f16_pair") \
+                and w.shape[0] % 64 == 0 and w.shape[1] % 64 == 0 and w.is_contiguous():
+            pk.fwd_f16, pk.dgrad_f16 = be.pack_weights_f16_pair(w)      # a training step needs both: one pair of launches
         if pk.fwd_f16 is None:
             pk.fwd_f16 = be.pack_weights(w, dgrad=False, tc=2)
         if need_dgrad and pk.dgrad_f16 is None:
@@ -393,7 +396,7 @@ class ConvNetOp:
                 amax_out = [maxima[l, 0] for l in range(L)]
                 saved.maxima = maxima
             if f16:
-                wts = [self.caches[l].get_f16(False).fwd_f16 for l in range(L)]
+                wts = [self.caches[l].get_f16(save or need_dgrad).fwd_f16 for l in range(L)]
             else:
                 wts = [self.caches[l].get(H, W, 64, 0, need_dgrad or save).fwd_tc for l in range(L)]
             last_act = self.layers[-1][1]

@@ -336,6 +336,19 @@ def test_convnet_f16_split_holds_fp32_accuracy_at_any_magnitude(be, scale):
     assert bool(torch.isnan(outs[-1][0]).any()) and bool(torch.isfinite(outs[-1][4]).all())
 
 
+@pytest.mark.parametrize("shape", [(64, 64, 3), (128, 128, 5), (64, 128, 5), (128, 64, 3)], ids=str)
+def test_pack_weights_f16_pair_equals_the_two_single_packs(be, shape):
+    """odex_pack_weights_f16_pair = odex_pack_weights(tc = 2) of both orientations, bit for bit (rows and the scale tail)."""
+    torch.manual_seed(sum(shape))
+    N, Cc, R = shape
+    w = torch.randn(N, Cc, R, R, device="cuda") * 0.07
+    w[3, 5] *= 40.0
+    f2, d2 = be.pack_weights_f16_pair(w)
+    f1, d1 = be.pack_weights(w, False, 2), be.pack_weights(w, True, 2)
+    torch.cuda.synchronize()
+    assert torch.equal(f1.view(torch.int32), f2.view(torch.int32)) and torch.equal(d1.view(torch.int32), d2.view(torch.int32))
+
+
 def test_convnet_amax_out_and_scaled_weight_gradient(be):
     """odex_convnet_desc.amax_out: the kind::f16 chain leaves max |input of layer l| PER IMAGE where the caller points;
     odex_conv2d_wgrad_f16_scaled takes such maxima instead of a max pass and must agree with the 3xTF32 weight gradient."""
