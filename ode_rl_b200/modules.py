@@ -887,10 +887,13 @@ class ConvGRUCell(nn.Module):
 class _EncoderFn(torch.autograd.Function):
     """The ODE-ConvGRU recurrence of modules/ODEConvGRUCell.py:53-74 as one autograd node: for every observed
     frame, walked in `order`, h~ = h + f(h)*dt_i (explicit Euler, fused into the last conv's epilogue) and
-    h = ConvGRU(x_i, h~).  Returns all hidden states, iteration-major [T,B,C,H,W]."""
+    h = ConvGRU(x_i, h~).  Returns all hidden states, iteration-major [T,B,C,H,W], and the final one once more as an output of
+    its own [B,C,H,W]: the model reads only that (modules/ODEConvGRUCell.py:32-37), and as a separate output its gradient arrives
+    alone -- no [T,B,...] gradient that is zero but for its last slice has to be built, laid out and added step by step."""
 
     @staticmethod
     def forward(ctx, f_op: ConvNetOp, g_op: GruOp, n_f: int, order, inputs: torch.Tensor, deltas: torch.Tensor, *params):
+        ctx.set_materialize_grads(False)
         be = K.backend()
         be.require(inputs)
         x = to_nhwc(inputs.detach().float())                 # [T,B,H,W,C]
@@ -933,40 +936,50 @@ class _EncoderFn(torch.autograd.Function):
             ctx.f_op, ctx.g_op, ctx.n_f, ctx.order, ctx.deltas, ctx.saved, ctx.params = f_op, g_op, n_f, order, deltas, saved, params
             ctx.x_shape = (T, B, H, W, Cx)
             ctx.gru_arenas = gru_ar is not None
-        return from_nhwc(hs)
+        return from_nhwc(hs), from_nhwc(hs[T - 1].clone())
 
     @staticmethod
-    def backward(ctx, dhs):
+    def backward(ctx, dhs, dlast):
         be = K.backend()
         f_op, g_op, order, deltas, saved = ctx.f_op, ctx.g_op, ctx.order, ctx.deltas, ctx.saved
         if saved is None:
             raise RuntimeError("ODEConvGRUCell: this recurrence was already back-propagated through once; its saved "
                                "activations are freed during that pass (no retain_graph) -- run the forward again")
-        d = to_nhwc(dhs.float())
-        if not d.is_contiguous():
-            d = d.contiguous()
+
+        def dense(g):
+            if g is None:
+                return None
+            g = to_nhwc(g.float())
+            return g if g.is_contiguous() else g.contiguous()
+
+        d, dl = dense(dhs), dense(dlast)                      # either may be None: that output was not used
+        ref = d if d is not None else dl
         T, B, H, W, Cx = ctx.x_shape
         C = g_op.C
         sink = GradSink()
         sink.deferred = True                                  # weight gradients of f: batched over the iterations at the end
         Lf = len(f_op.layers)
-        dk_arena = torch.empty((T, B, H, W, C), dtype=torch.float32, device=d.device)
+        dev = ref.device
+        dk_arena = torch.empty((T, B, H, W, C), dtype=torch.float32, device=dev)
         g_arenas = None
         if Lf > 1 and all(c.in_channels == C for c, _ in f_op.layers[1:]):
-            g_arenas = [torch.empty((T, B, H, W, C), dtype=torch.float32, device=d.device) for _ in range(Lf - 1)]
-        DX = torch.empty((T, B, H, W, Cx + C), dtype=torch.float32, device=d.device)   # [dx_i | dh~] per frame
+            g_arenas = [torch.empty((T, B, H, W, C), dtype=torch.float32, device=dev) for _ in range(Lf - 1)]
+        DX = torch.empty((T, B, H, W, Cx + C), dtype=torch.float32, device=dev)   # [dx_i | dh~] per frame
         gru_bw = None
         if ctx.gru_arenas:                                    # dy of the ConvGRU's weight gradients, indexed by frame like x
-            gru_bw = {"dcpre": torch.empty((T, B, H, W, C), dtype=torch.float32, device=d.device),
-                      "dg": torch.empty((T, B, H, W, 2 * C), dtype=torch.float32, device=d.device)}
+            gru_bw = {"dcpre": torch.empty((T, B, H, W, C), dtype=torch.float32, device=dev),
+                      "dg": torch.empty((T, B, H, W, 2 * C), dtype=torch.float32, device=dev)}
         a = None                                              # adjoint of h after iteration n
         for n in range(T - 1, -1, -1):
             i = order[n]
-            if a is None:
-                dh = d[n]
+            parts = [g_ for g_ in (a, d[n] if d is not None else None, dl if n == T - 1 else None) if g_ is not None]
+            if not parts:
+                dh = torch.zeros((B, H, W, C), dtype=torch.float32, device=dev)
+            elif len(parts) == 1:
+                dh = parts[0]
             else:
-                dh = torch.empty_like(a)
-                be.lincomb(dh, [a, d[n]], [1.0, 1.0])
+                dh = torch.empty((B, H, W, C), dtype=torch.float32, device=dev)
+                be.lincomb(dh, parts, [1.0] * len(parts))
             sv_f, sv_g = saved[n]
             D = g_op.bwd(sv_g, dh, sink, out=DX[i],
                          bufs={"dcpre": gru_bw["dcpre"][i], "dg": gru_bw["dg"][i]} if gru_bw is not None else None)
@@ -1070,10 +1083,11 @@ class ODEConvGRUCell(nn.Module):
         deltas = self._deltas(timesteps, inputs.device, tuple(order))
         f_op, g_op = self.ode_func.op(), self.cgru_cell.op()
         params = f_op.params() + g_op.params()
+        h_last = None
         if b == 0:
             hs = _empty_result((t, 0, g_op.C, h, w), inputs, params)
         else:
-            hs = _EncoderFn.apply(f_op, g_op, len(f_op.params()), order, live_input(inputs), deltas, *live(params))   # [T,B,C,H,W]
+            hs, h_last = _EncoderFn.apply(f_op, g_op, len(f_op.params()), order, live_input(inputs), deltas, *live(params))   # [T,B,C,H,W], [B,C,H,W]
             if self.check_nan:
                 if self._flag is None or self._flag.device != hs.device:
                     self._flag = torch.zeros(1, dtype=torch.int32, device=hs.device)
@@ -1081,6 +1095,6 @@ class ODEConvGRUCell(nn.Module):
                 K.backend().nan_flag(last if last.is_contiguous() else last.contiguous(), self._flag, 1)
                 if not (hs.is_cuda and torch.cuda.is_current_stream_capturing()):
                     self.check_errors()
-        yi = hs[t - 1]
+        yi = h_last if h_last is not None else hs[t - 1]
         latent_ys = hs.permute(1, 0, 2, 3, 4)   # (b, t, c, h, w)
         return yi, latent_ys
