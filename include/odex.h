@@ -190,6 +190,10 @@ typedef struct odex_conv16_desc {
     const float* h; int ldh; const float* z_in;
     float* z; float* rh; float* hnew; int ld_hnew; float* cand; float* g_raw; float* stats;
     const int* skip;
+    float* out_hi; int ld_out_hi; int out_split; /* PLAIN, optional (out_split = 0: off): output channels [out_split, N) go to out_hi
+                                               (row stride ld_out_hi, channel c at column c - out_split) instead of out, which
+                                               then holds [0, out_split) only; out_split a multiple of 64.  The ConvGRU data
+                                               gradient [dx | dh] lands in two dense tensors this way instead of one interleaved. */
     float* amax_out;                        /* nullable, B floats: amax_out[b] <- max(max |x0[b]|, max |x1[b]|) (the kernel measures it
                                                for its operand scale anyway).  For odex_conv2d_wgrad_f16_scaled: the sources of a
                                                forward launch are the X of that convolution's weight gradient, the source of its

@@ -85,6 +85,7 @@ class Conv16Desc(C.Structure):
         ("z", C.c_void_p), ("rh", C.c_void_p), ("hnew", C.c_void_p), ("ld_hnew", C.c_int), ("cand", C.c_void_p),
         ("g_raw", C.c_void_p), ("stats", C.c_void_p),
         ("skip", C.c_void_p),
+        ("out_hi", C.c_void_p), ("ld_out_hi", C.c_int), ("out_split", C.c_int),
         ("amax_out", C.c_void_p),
     ]
 

@@ -67,6 +67,7 @@ struct C16Args {
     float* z; float* rh; float* hnew; int ld_hnew; float* cand; float* g_raw; float* stats;
     const int* skip;
     float* amax_out;
+    int out_split;                  // PLAIN: channels >= out_split are stored through C16Maps::ocand at column c - out_split (0: off)
     long long* dbg;
 };
 
@@ -352,8 +353,11 @@ conv16_f16_kernel(const __grid_constant__ C16Maps tm, const C16Args a) {
             fence_proxy_async_smem();
             asm volatile("bar.sync 1, 256;" ::: "memory");
             if (tid == 0) {
-                tma_store_4d(&tm.out, s_base, n_off, 0, 0, img);
-                tma_store_4d(&tm.out, s_base + kF16SHalf, n_off + 32, 0, 0, img);
+                const bool hi_part = a.out_split > 0 && n_off >= a.out_split;
+                const CUtensorMap* mo = hi_part ? &tm.ocand : &tm.out;
+                const int co = hi_part ? n_off - a.out_split : n_off;
+                tma_store_4d(mo, s_base, co, 0, 0, img);
+                tma_store_4d(mo, s_base + kF16SHalf, co + 32, 0, 0, img);
                 tma_store_commit();
                 tma_store_wait_read();
             }
@@ -562,7 +566,7 @@ static const char* c16_check(const odex_conv16_desc* d) {
     if (d->x1 && (d->ld1 % 4 || d->ld1 < 64 || !aligned16(d->x1))) return "x1 alignment or stride";
     if (d->bias && !aligned16(d->bias)) return "bias alignment";
     if (d->mode == ODEX_C16_PLAIN) {
-        if (!d->out || d->ldo % 4 || d->ldo < d->N || !aligned16(d->out)) return "out";
+        if (!d->out || d->ldo % 4 || d->ldo < (d->out_split > 0 ? d->out_split : d->N) || !aligned16(d->out)) return "out";
         if (d->act < 0 || d->act > 2 || d->aux_kind < 0 || d->aux_kind > 3) return "act / aux_kind";
         if (d->act != ODEX_ACT_NONE && (d->aux_kind == 1 || d->aux_kind == 2)) return "activation together with a mask";
         if (d->aux_kind && (!d->aux || d->ld_aux % 4 || d->ld_aux < d->N || !aligned16(d->aux))) return "aux";
@@ -607,7 +611,15 @@ static int c16_launch(const odex_conv16_desc* d, cudaStream_t s) {
     if (d->mode == ODEX_C16_PLAIN) {
         if (d->aux_kind)
             if (int rc = c16_act_map(&tm.aux, d->aux, d->ld_aux, d->N, d->B)) return rc;
-        if (int rc = c16_act_map(&tm.out, d->out, d->ldo, d->N, d->B)) return rc;
+        if (d->out_split > 0) {
+            if (d->out_split % 64 || d->out_split >= d->N || !d->out_hi || d->ld_out_hi % 4 || d->ld_out_hi < d->N - d->out_split ||
+                !aligned16(d->out_hi) || d->ldo < d->out_split)
+                return fail(ODEX_E_ARG, "conv16: bad out_split / out_hi (split=%d N=%d)", d->out_split, d->N);
+            if (int rc = c16_act_map(&tm.out, d->out, d->ldo, d->out_split, d->B)) return rc;
+            if (int rc = c16_act_map(&tm.ocand, d->out_hi, d->ld_out_hi, d->N - d->out_split, d->B)) return rc;
+        } else {
+            if (int rc = c16_act_map(&tm.out, d->out, d->ldo, d->N, d->B)) return rc;
+        }
     } else {
         const int C = d->mode == ODEX_C16_GRU_GATES ? d->N / 2 : d->N;
         if (d->g_raw)
@@ -633,6 +645,7 @@ static int c16_launch(const odex_conv16_desc* d, cudaStream_t s) {
     a.z = d->z; a.rh = d->rh; a.hnew = d->hnew; a.ld_hnew = d->ld_hnew; a.cand = d->cand; a.g_raw = d->g_raw; a.stats = d->stats;
     a.skip = d->skip;
     a.amax_out = d->amax_out;
+    a.out_split = d->mode == ODEX_C16_PLAIN ? d->out_split : 0;
     a.dbg = nullptr;
     static const bool debug = getenv("ODEX_CONV_DEBUG") != nullptr;
     if (debug) {

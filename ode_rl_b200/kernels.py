@@ -223,7 +223,8 @@ class Backend:
                alpha: float = 1.0, alpha_dev: Optional[torch.Tensor] = None, skip: Optional[torch.Tensor] = None,
                amax_out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """odex_conv16(PLAIN): out = act(conv(cat(x0, x1)) + bias), then * act'(aux) (aux_kind 1 / 2) or aux + alpha * v (3).
-        amax_out (all three modes): fp32 tensor [B] <- max |sources| per image."""
+        amax_out (all three modes): fp32 tensor [B] <- max |sources| per image.  out may be a pair (lo [B,16,16,s], hi [B,16,16,N-s])
+        with s a multiple of 64: the output channels land in two tensors (odex_conv16_desc.out_split)."""
         self.require(x0)
         d = self._conv16_desc(x0, x1, w_f16, N, R, bias, skip)
         d.amax_out = _ptr(amax_out)
@@ -234,8 +235,15 @@ class Backend:
             d.aux_kind = aux_kind
         d.alpha = float(alpha)
         d.alpha_dev = _ptr(alpha_dev)
-        assert tuple(out.shape) == (x0.shape[0], 16, 16, N)
-        d.out, d.ldo = _rows(out)
+        if isinstance(out, (tuple, list)):
+            lo, hi = out
+            assert lo.shape[3] % 64 == 0 and lo.shape[3] + hi.shape[3] == N and tuple(lo.shape[:3]) == tuple(hi.shape[:3]) == (x0.shape[0], 16, 16)
+            d.out, d.ldo = _rows(lo)
+            d.out_hi, d.ld_out_hi = _rows(hi)
+            d.out_split = lo.shape[3]
+        else:
+            assert tuple(out.shape) == (x0.shape[0], 16, 16, N)
+            d.out, d.ldo = _rows(out)
         _lib.check(self.lib.odex_conv16(C.byref(d), _stream()), "odex_conv16")
         return out
 

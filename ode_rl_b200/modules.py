@@ -964,7 +964,12 @@ class _EncoderFn(torch.autograd.Function):
         g_arenas = None
         if Lf > 1 and all(c.in_channels == C for c, _ in f_op.layers[1:]):
             g_arenas = [torch.empty((T, B, H, W, C), dtype=torch.float32, device=dev) for _ in range(Lf - 1)]
-        DX = torch.empty((T, B, H, W, Cx + C), dtype=torch.float32, device=dev)   # [dx_i | dh~] per frame
+        split = bool(ctx.gru_arenas) and Cx % 64 == 0        # odex_conv16 writes dx_i and dh~ into two dense tensors
+        if split:
+            DX = torch.empty((T, B, H, W, Cx), dtype=torch.float32, device=dev)
+            DH = torch.empty((T, B, H, W, C), dtype=torch.float32, device=dev)
+        else:
+            DX = torch.empty((T, B, H, W, Cx + C), dtype=torch.float32, device=dev)   # [dx_i | dh~] per frame
         gru_bw = None
         if ctx.gru_arenas:                                    # dy of the ConvGRU's weight gradients, indexed by frame like x
             gru_bw = {"dcpre": torch.empty((T, B, H, W, C), dtype=torch.float32, device=dev),
@@ -981,9 +986,12 @@ class _EncoderFn(torch.autograd.Function):
                 dh = torch.empty((B, H, W, C), dtype=torch.float32, device=dev)
                 be.lincomb(dh, parts, [1.0] * len(parts))
             sv_f, sv_g = saved[n]
-            D = g_op.bwd(sv_g, dh, sink, out=DX[i],
-                         bufs={"dcpre": gru_bw["dcpre"][i], "dg": gru_bw["dg"][i]} if gru_bw is not None else None)
-            dht = D[..., Cx:]                                 # adjoint of h~ (row stride Cx+C)
+            gb_ = {"dcpre": gru_bw["dcpre"][i], "dg": gru_bw["dg"][i]} if gru_bw is not None else None
+            if split:
+                _, dht = g_op.bwd(sv_g, dh, sink, bufs=gb_, split_out=(DX[i], DH[i]))      # adjoint of h~, dense
+            else:
+                D = g_op.bwd(sv_g, dh, sink, out=DX[i], bufs=gb_)
+                dht = D[..., Cx:]                             # adjoint of h~ (row stride Cx+C)
             if n == 0:
                 # h_0 = 0 is a constant: only the parameter gradients of f(0) remain
                 dk = _scaled_copy(be, dht, deltas[n:n + 1], out=dk_arena[n])
@@ -994,7 +1002,7 @@ class _EncoderFn(torch.autograd.Function):
                 a = f_op.bwd(sv_f, dk, sink, res=dht, gbufs=[g_[n] for g_ in g_arenas] if g_arenas is not None else None)
             saved[n] = None
         ctx.saved = None
-        dx = from_nhwc(DX[..., :Cx]) if ctx.needs_input_grad[4] else None
+        dx = from_nhwc(DX if split else DX[..., :Cx]) if ctx.needs_input_grad[4] else None
         return (None, None, None, None, dx, None) + sink.result(ctx.params)
 
 

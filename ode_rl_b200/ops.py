@@ -607,9 +607,10 @@ class GruOp:
         return hnew
 
     def bwd(self, saved, dhnew: torch.Tensor, sink: GradSink, out: Optional[torch.Tensor] = None,
-            bufs: Optional[dict] = None) -> torch.Tensor:
+            bufs: Optional[dict] = None, split_out=None):
         """Returns D = [dx | dh] as one [B,H,W,Cx+C] buffer (channel slices are the two gradients).  bufs (optional): caller-owned
-        {"dcpre": [B,H,W,C], "dg": [B,H,W,2C]} arena slices (see fwd)."""
+        {"dcpre": [B,H,W,C], "dg": [B,H,W,2C]} arena slices (see fwd).  split_out = (dx [B,H,W,Cx], dh [B,H,W,C]) (fused path
+        only): the two gradients land in these two DENSE tensors and the pair is returned instead of D."""
         be = K.backend()
         x, h, g, z, rh, st_g, cpre, cand, st_c = saved[:9]
         mx = saved[9] if len(saved) > 9 else None       # the step's maxima (fused forward only)
@@ -641,7 +642,11 @@ class GruOp:
         drh = D1[..., Cx:]
         be.gru_gates_bwd(dz, drh, dh_a, g, h, self.gn_g.weight, self.gn_g.bias, st_g, dg, drh,
                          grad_or_scratch(self.gn_g.weight), grad_or_scratch(self.gn_g.bias))   # D1[..., Cx:] <- dh_a + drh*r
-        D2 = out if out is not None else torch.empty((B, H, W, Cx + C), dtype=f32, device=dev)
+        if split_out is not None:
+            assert f16 and Cx % 64 == 0, "split_out needs the odex_conv16 path"
+            D2 = tuple(split_out)
+        else:
+            D2 = out if out is not None else torch.empty((B, H, W, Cx + C), dtype=f32, device=dev)
         if f16:
             pgf = self.pc_g.get_f16(True).dgrad_f16
             be.conv16(dg[..., :C], dg[..., C:], pgf, Cx + C, R, None, ACT_NONE, D2, aux=D1, aux_kind=3, alpha=1.0,

@@ -653,6 +653,23 @@ def test_conv16_plain_matches_exact_fp32_conv(be, R, nsrc, N):
     assert float((o2 - 7.0).abs().max()) == 0.0
 
 
+def test_conv16_split_output_equals_the_interleaved_one(be):
+    """odex_conv16_desc.out_split: the N = 128 outputs of the ConvGRU data-gradient convolution in two dense 64-channel tensors
+    (dx | dh) instead of one interleaved [.., 128] -- same bits, residual operand included."""
+    torch.manual_seed(31)
+    B, R = 5, 5
+    dg = torch.randn(B, 16, 16, 128, device="cuda")
+    w = torch.randn(128, 128, R, R, device="cuda") / (8.0 * R)
+    wf = be.pack_weights(w, True, 2)
+    aux = torch.randn(B, 16, 16, 128, device="cuda")
+    one = torch.empty(B, 16, 16, 128, device="cuda")
+    be.conv16(dg[..., :64], dg[..., 64:], wf, 128, R, None, ACT_NONE, one, aux=aux, aux_kind=3, alpha=1.0)
+    lo, hi = torch.full((B, 16, 16, 64), 7.0, device="cuda"), torch.full((B, 16, 16, 64), 7.0, device="cuda")
+    be.conv16(dg[..., :64], dg[..., 64:], wf, 128, R, None, ACT_NONE, (lo, hi), aux=aux, aux_kind=3, alpha=1.0)
+    torch.cuda.synchronize()
+    assert torch.equal(lo, one[..., :64]) and torch.equal(hi, one[..., 64:])
+
+
 @pytest.mark.parametrize("R", [3, 5])
 def test_conv16_amax_out_feeds_the_scaled_weight_gradient(be, R):
     """odex_conv16_desc.amax_out: max |sources| per image, in all three modes; the 5x5 two-source
