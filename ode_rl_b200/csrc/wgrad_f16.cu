@@ -169,13 +169,13 @@ wgrad_f16_kernel(const __grid_constant__ CUtensorMap tmX0, const __grid_constant
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t stage_bytes = 2u * g.xplane + 2u * kW16DyPlane;   // [X c0-31 -> X hi][X c32-63 -> X lo][dy n0-31][dy n32-63]
-    constexpr int S = (R <= 3) ? 4 : 3;            // pipeline stages (shared-memory tiles and TMEM A slots)
+    constexpr int S = (R <= 3) ? 5 : 4;            // pipeline stages (shared-memory tiles and TMEM A slots): all that fit 227 KB
     const uint32_t bars = base + static_cast<uint32_t>(S) * stage_bytes;
-    const uint32_t bar_raw_full = bars;            // [S]
-    const uint32_t bar_split_full = bars + 32;     // [S]
-    const uint32_t bar_stage_empty = bars + 64;    // [S]
-    const uint32_t bar_acc = bars + 96;
-    const uint32_t tmem_slot = bars + 104;
+    const uint32_t bar_raw_full = bars;            // [S <= 6]
+    const uint32_t bar_split_full = bars + 48;     // [S]
+    const uint32_t bar_stage_empty = bars + 96;    // [S]
+    const uint32_t bar_acc = bars + 144;
+    const uint32_t tmem_slot = bars + 152;
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -521,8 +521,8 @@ int launch_wgrad_f16(const float* x0, int ld0, int c0, const float* x1, int ld1,
     g.amax_x = amax_x ? amax_x : scratch2;
     g.amax_dy = amax_x ? amax_dy : scratch2 + 1;
     g.amax_stride = amax_x ? 1 : 0;
-    const int stages = R <= 3 ? 4 : 3;
-    const int smem = 1024 + std::max(stages * (2 * g.xplane + 2 * kW16DyPlane), 32768) + 128;
+    const int stages = R <= 3 ? 5 : 4;
+    const int smem = 1024 + std::max(stages * (2 * g.xplane + 2 * kW16DyPlane), 32768) + 256;
     if (smem > 232448) return fail(ODEX_E_UNSUPPORTED, "wgrad(f16): needs %d bytes of shared memory", smem);
 
     CUtensorMap tmX0, tmX1, tmDY;
