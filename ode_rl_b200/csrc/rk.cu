@@ -36,30 +36,8 @@ __global__ void __launch_bounds__(256) lincomb_kernel(float* __restrict__ out, c
     const float dt = dt_dev ? static_cast<float>(*dt_dev) : 1.f;
 #pragma unroll
     for (int j = 0; j < NIN; ++j) c[j] = (a.dtmask >> j & 1u) ? a.coef[j] * dt : a.coef[j];
-    const long stride = static_cast<long>(gridDim.x) * blockDim.x;
-    long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x;
-    // few operands = few loads in flight per thread: take four grid strides at a time (all loads first; out may alias nothing the
-    // compiler can prove, so it would not hoist them itself) -- 16 KB in flight per SM is a quarter of what HBM3e wants
-    if (NIN <= 2) {
-        for (; i + 3 * stride < n4; i += 4 * stride) {
-            float4 v[4][NIN];
-#pragma unroll
-            for (int u = 0; u < 4; ++u)
-#pragma unroll
-                for (int j = 0; j < NIN; ++j) v[u][j] = ld4(a.in[j] + 4 * (i + u * stride));
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                float4 o = make_float4(v[u][0].x * c[0], v[u][0].y * c[0], v[u][0].z * c[0], v[u][0].w * c[0]);
-#pragma unroll
-                for (int j = 1; j < NIN; ++j) {
-                    o.x = fmaf(v[u][j].x, c[j], o.x); o.y = fmaf(v[u][j].y, c[j], o.y);
-                    o.z = fmaf(v[u][j].z, c[j], o.z); o.w = fmaf(v[u][j].w, c[j], o.w);
-                }
-                st4(out + 4 * (i + u * stride), o);
-            }
-        }
-    }
-    for (; i < n4; i += stride) {
+    for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n4;
+         i += static_cast<long>(gridDim.x) * blockDim.x) {
         float4 v[NIN];
 #pragma unroll
         for (int j = 0; j < NIN; ++j) v[j] = ld4(a.in[j] + 4 * i);
